@@ -1,0 +1,101 @@
+// Device-visible tables of the rigid-body world step.
+//
+// HBM layout: every component of the rigid-body archetype is one allocation
+// [num_worlds][stride][component bytes] in the reference's packed byte layout
+// (Position 12 B, Rotation 16 B w,x,y,z, Velocity 24 B, ... include/madrona/
+// physics.hpp:150-171,402-415, components.hpp:9-29), i.e. the reference's
+// fixed-size-archetype table (include/madrona/state.inl:481-496) made the
+// default: world w's rows are the contiguous tile [w*stride, w*stride+rows).
+// Exported columns are handed out in place (zero copy).
+#pragma once
+#include "phys_math.cuh"
+
+namespace mdr {
+
+// One shared collision object (reference: ObjectManager rows,
+// include/madrona/physics.hpp:243-290). Hull tables are flat arrays indexed by
+// the offsets below (the reference's HalfEdgeMesh, physics.hpp:54-146).
+struct ObjDev {
+    int32_t type;            // 2 hull, 4 plane (CollisionPrimitive::Type)
+    float inv_inertia[3];
+    float inv_mass, mu_s, mu_d;
+    float aabb[6];           // min xyz, max xyz
+    int32_t vert_off, num_verts;
+    int32_t face_off, num_faces;     // planes[] and polys[] share the face index
+    int32_t hedge_off, num_hedges;
+    int32_t edge_off, num_edges;
+};
+
+struct HEdgeDev { uint32_t next, twin, root, poly; };
+
+struct AssetsDev {
+    const ObjDev *objs;
+    const float *verts;        // xyz packed
+    const float *planes;       // nx ny nz d
+    const HEdgeDev *hedges;    // indices local to the object
+    const uint32_t *edges;     // half-edge index of each undirected edge
+    const uint32_t *polys;     // entry half-edge of each face
+    int32_t num_objs;
+    int32_t max_verts, max_faces;   // over all hull objects (sizes the SMEM hull slots)
+};
+
+// The reference's Contact (physics.hpp:185-192) with Loc reduced to a row: 112 B.
+struct ContactDev {
+    int32_t ref, ref_pad, alt, alt_pad;
+    float pts[4][4];
+    int32_t num_points;
+    float normal[3];
+    float lambda_n[4];
+};
+
+struct PhysTables {
+    float *pos, *rot, *scale, *vel;
+    int32_t *obj;
+    uint32_t *resp;
+    float *prev, *prex, *prev_vel;       // SubstepPrevState 28 B, PreSolvePositional 28 B, PreSolveVelocity 24 B
+    float *ext_f, *ext_t;
+    int32_t *leaf_id;
+    int32_t *entity;                     // (gen, id) pairs
+    int32_t *row_count;                  // [W]
+    // broadphase::BVH singleton state, per world
+    float *leaf_aabb;                    // [W][stride][6] current (motion-expanded) leaf boxes
+    float *slot_box;                     // [W][stride][6] grow-only leaf slot boxes
+    uint16_t *order;                     // [W][stride]   leaf at rank r of the reference traversal
+    uint16_t *sorted;                    // [W][stride]   scratch permutation of the rebuild
+    uint8_t *rebuild_flag;               // [W]
+    int32_t stride;
+    int32_t num_worlds;
+};
+
+// Optional per-launch probe of one world (parity tests): pair list and the
+// contact list of every substep, in the reference's order.
+struct ProbeDev {
+    int32_t world;                // -1: off
+    int32_t max_pairs;
+    int32_t max_contacts;
+    int32_t *num_pairs;           // [1]
+    int32_t *pairs;               // [max_pairs][2]
+    int32_t *num_contacts;        // [substeps]
+    ContactDev *contacts;         // [substeps][max_contacts]
+};
+
+struct StepParams {
+    PhysTables t;
+    AssetsDev a;
+    float h;                      // delta_t / substeps
+    float vel_expand, accel_expand;
+    float restitution_threshold;
+    float g[3];
+    int32_t substeps;
+    int32_t max_pairs;            // SMEM pair-list capacity per world
+    int32_t smem_contacts;        // contact slots held in SMEM; the rest go to `overflow`
+    ContactDev *overflow;         // [gridDim.x][max_pairs - smem_contacts]
+    int32_t *world_pairs;         // [W] pairs found in the last step
+    int32_t *world_contacts;      // [W] contacts of the last substep
+    int32_t *error_flags;         // [1] bit 0: pair list overflow
+    ProbeDev probe;
+};
+
+enum { MDR_ERR_PAIR_OVERFLOW = 1 };
+
+}  // namespace mdr

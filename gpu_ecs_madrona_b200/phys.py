@@ -1,0 +1,261 @@
+"""Python host mirror of the rigid-body world-step executor.
+
+Thin ctypes binding of include/madrona_b200.h (libmadrona_b200.so, CUDA,
+sm_100a). The class mirrors how the reference is driven for this path:
+construct an executor from a config + shared collision objects + per-world
+init data (MWCudaExecutor(StateConfig, CompileConfig), include/madrona/
+mw_gpu.hpp:20-76 with RigidBodyPhysicsSystem as the world's systems,
+include/madrona/physics.hpp:419-447), call ``run()`` per step
+(src/mw/cuda_exec.cpp:1777-1794) and read exported columns in place
+(``getExported``). There is no CPU path: importing works anywhere, creating an
+executor without the CUDA library or without a GPU raises.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libmadrona_b200.so")
+
+COL_BYTES = [8, 12, 16, 12, 24, 4, 4, 28, 28, 24, 12, 12, 4]
+(COL_ENTITY, COL_POSITION, COL_ROTATION, COL_SCALE, COL_VELOCITY, COL_OBJECT_ID,
+ COL_RESPONSE_TYPE, COL_SUBSTEP_PREV, COL_PRESOLVE_POS, COL_PRESOLVE_VEL,
+ COL_EXT_FORCE, COL_EXT_TORQUE, COL_LEAF_ID) = range(13)
+
+MDR_OK, MDR_EINVAL, MDR_ENODEVICE, MDR_ECAPACITY, MDR_EOVERFLOW, MDR_ESTATE = 0, -1, -2, -3, -4, -5
+_ERR = {-1: "invalid argument", -2: "no CUDA device", -3: "capacity does not fit the device",
+        -4: "per-world capacity overflowed", -5: "call in the wrong phase"}
+
+
+class MdrObject(C.Structure):
+    _fields_ = [("type", C.c_int32), ("inv_inertia", C.c_float * 3),
+                ("inv_mass", C.c_float), ("mu_s", C.c_float), ("mu_d", C.c_float),
+                ("aabb_min", C.c_float * 3), ("aabb_max", C.c_float * 3),
+                ("vert_offset", C.c_int32), ("num_verts", C.c_int32),
+                ("poly_offset", C.c_int32), ("num_poly_words", C.c_int32)]
+
+
+class MdrPhysConfig(C.Structure):
+    _fields_ = [("num_worlds", C.c_int32), ("max_bodies_per_world", C.c_int32),
+                ("num_substeps", C.c_int32), ("max_contacts", C.c_int32),
+                ("delta_t", C.c_float), ("gravity", C.c_float * 3),
+                ("gpu_id", C.c_int32), ("block_threads", C.c_int32),
+                ("smem_contacts", C.c_int32)]
+
+
+CONTACT_DTYPE = np.dtype([("ref_row", "<i4"), ("ref_pad", "<i4"), ("alt_row", "<i4"),
+                          ("alt_pad", "<i4"), ("points", "<f4", (4, 4)),
+                          ("num_points", "<i4"), ("normal", "<f4", (3,)),
+                          ("lambda_n", "<f4", (4,))])
+assert CONTACT_DTYPE.itemsize == 112
+
+
+class MadronaError(RuntimeError):
+    def __init__(self, code, what):
+        super().__init__(f"{what}: {_ERR.get(code, code)} ({code})")
+        self.code = code
+
+
+def bind(lib):
+    """Declares the C ABI on a loaded library."""
+    vp, i32 = C.c_void_p, C.c_int32
+    lib.mdr_phys_create.argtypes = [vp, vp, i32, vp, vp, C.POINTER(vp)]
+    lib.mdr_phys_destroy.argtypes = [vp]
+    lib.mdr_phys_destroy.restype = None
+    lib.mdr_phys_set_row_counts.argtypes = [vp, vp]
+    lib.mdr_phys_write_column.argtypes = [vp, i32, vp]
+    lib.mdr_phys_read_column.argtypes = [vp, i32, vp]
+    lib.mdr_phys_flag_rebuild.argtypes = [vp]
+    lib.mdr_phys_step.argtypes = [vp, i32]
+    lib.mdr_phys_step_async.argtypes = [vp, i32]
+    lib.mdr_phys_sync.argtypes = [vp]
+    lib.mdr_phys_probe_step.argtypes = [vp, i32, i32, vp, vp, vp, vp]
+    lib.mdr_phys_stats.argtypes = [vp, vp, vp]
+    lib.mdr_phys_read_bvh.argtypes = [vp, vp, vp, vp]
+    lib.mdr_phys_get_hull.argtypes = [vp, i32, vp, vp, vp, vp, vp]
+    lib.mdr_version.restype = C.c_char_p
+    for name in ("mdr_phys_column_ptr", "mdr_phys_stream"):
+        if hasattr(lib, name):
+            getattr(lib, name).restype = vp
+    if hasattr(lib, "mdr_phys_column_ptr"):
+        lib.mdr_phys_column_ptr.argtypes = [vp, i32]
+        lib.mdr_phys_stream.argtypes = [vp]
+        lib.mdr_phys_launch_info.argtypes = [vp, vp]
+        lib.mdr_phys_kernel_ms.argtypes = [vp, vp]
+        lib.mdr_phys_kernel_ms.restype = C.c_float
+    return lib
+
+
+_LIB = None
+
+
+def load_library():
+    """Loads the CUDA library; fails loudly when it has not been built."""
+    global _LIB
+    if _LIB is None:
+        if not os.path.exists(LIB_PATH):
+            raise ImportError(
+                f"{LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; "
+                "g.build()'` (nvcc, sm_100a). There is no CPU fallback.")
+        _LIB = bind(C.CDLL(LIB_PATH))
+    return _LIB
+
+
+def pack_objects(objects):
+    """ObjectDef list (scenes.py) -> (mdr_object array, verts [V,3] f32, polygon words u32)."""
+    verts, words, arr = [], [], (MdrObject * len(objects))()
+    voff = woff = 0
+    for i, o in enumerate(objects):
+        pw = o.poly_words()
+        arr[i].type = o.type
+        arr[i].inv_inertia = (C.c_float * 3)(*o.inv_inertia)
+        arr[i].inv_mass, arr[i].mu_s, arr[i].mu_d = o.inv_mass, o.mu_s, o.mu_d
+        arr[i].aabb_min = (C.c_float * 3)(*o.aabb_min)
+        arr[i].aabb_max = (C.c_float * 3)(*o.aabb_max)
+        arr[i].vert_offset, arr[i].num_verts = voff, len(o.verts)
+        arr[i].poly_offset, arr[i].num_poly_words = woff, len(pw)
+        verts.append(np.asarray(o.verts, np.float32).reshape(-1, 3))
+        words.append(pw)
+        voff += len(o.verts)
+        woff += len(pw)
+    v = np.concatenate(verts) if voff else np.zeros((1, 3), np.float32)
+    w = np.concatenate(words) if woff else np.zeros(1, np.uint32)
+    return arr, np.ascontiguousarray(v, np.float32), np.ascontiguousarray(w, np.uint32)
+
+
+class PhysExecutor:
+    """Batched rigid-body worlds on one GPU. ``scene`` is a ``scenes.Scene``."""
+
+    def __init__(self, scene, gpu_id=0, block_threads=0, smem_contacts=0, lib=None):
+        self.lib = lib if lib is not None else load_library()
+        self.scene = scene
+        self.W, self.N = scene.num_worlds, scene.bodies_per_world
+        cfg = MdrPhysConfig(scene.num_worlds, scene.bodies_per_world, scene.num_substeps,
+                            scene.max_contacts, scene.delta_t, (C.c_float * 3)(*scene.gravity),
+                            gpu_id, block_threads, smem_contacts)
+        objs, verts, words = pack_objects(scene.objects)
+        h = C.c_void_p()
+        rc = self.lib.mdr_phys_create(C.byref(cfg), objs, len(scene.objects),
+                                      verts.ctypes.data, words.ctypes.data, C.byref(h))
+        if rc != MDR_OK:
+            raise MadronaError(rc, "mdr_phys_create")
+        self.h = h
+        rows = getattr(scene, "rows_per_world", None)
+        if rows is None:
+            rows = np.full(self.W, self.N, np.int32)
+        self.set_row_counts(rows)
+        vel = np.ascontiguousarray(scene.vel, np.float32)
+        for col, arr, dt in ((COL_POSITION, scene.pos, np.float32), (COL_ROTATION, scene.rot, np.float32),
+                             (COL_SCALE, scene.scale, np.float32), (COL_VELOCITY, vel, np.float32),
+                             (COL_OBJECT_ID, scene.obj_ids, np.int32),
+                             (COL_RESPONSE_TYPE, scene.response, np.uint32),
+                             (COL_EXT_FORCE, scene.ext_force, np.float32),
+                             (COL_EXT_TORQUE, scene.ext_torque, np.float32)):
+            self.write(col, np.ascontiguousarray(arr, dt))
+
+    def _check(self, rc, what):
+        if rc != MDR_OK:
+            raise MadronaError(rc, what)
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.mdr_phys_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def set_row_counts(self, rows):
+        rows = np.ascontiguousarray(rows, np.int32)
+        assert rows.shape == (self.W,)
+        self._check(self.lib.mdr_phys_set_row_counts(self.h, rows.ctypes.data), "set_row_counts")
+
+    def write(self, col, arr):
+        arr = np.ascontiguousarray(arr)
+        assert arr.nbytes == self.W * self.N * COL_BYTES[col], (col, arr.shape)
+        self._check(self.lib.mdr_phys_write_column(self.h, col, arr.ctypes.data), "write_column")
+
+    def read(self, col):
+        out = np.empty((self.W, self.N, COL_BYTES[col]), np.uint8)
+        self._check(self.lib.mdr_phys_read_column(self.h, col, out.ctypes.data), "read_column")
+        return out
+
+    def read_f32(self, col):
+        return self.read(col).view(np.float32)
+
+    def state(self):
+        """(pos[W,N,3], rot[W,N,4], vel[W,N,6])."""
+        return (self.read_f32(COL_POSITION), self.read_f32(COL_ROTATION),
+                self.read_f32(COL_VELOCITY))
+
+    def run(self, num_steps=1):
+        """MWCudaExecutor::run(): blocking."""
+        self._check(self.lib.mdr_phys_step(self.h, num_steps), "step")
+
+    step = run
+
+    def run_async(self, num_steps=1):
+        self._check(self.lib.mdr_phys_step_async(self.h, num_steps), "step_async")
+
+    def sync(self):
+        self._check(self.lib.mdr_phys_sync(self.h), "sync")
+
+    def flag_rebuild(self):
+        self._check(self.lib.mdr_phys_flag_rebuild(self.h), "flag_rebuild")
+
+    def probe_step(self, world, max_pairs=4096):
+        S, MC = self.scene.num_substeps, self.scene.max_contacts
+        npairs = np.zeros(1, np.int32)
+        pairs = np.zeros((max_pairs, 2), np.int32)
+        ncon = np.zeros(S, np.int32)
+        contacts = np.zeros((S, MC), CONTACT_DTYPE)
+        self._check(self.lib.mdr_phys_probe_step(self.h, world, max_pairs, npairs.ctypes.data,
+                                                 pairs.ctypes.data, ncon.ctypes.data,
+                                                 contacts.ctypes.data), "probe_step")
+        return dict(pairs=pairs[:npairs[0]].copy(), num_contacts=ncon,
+                    contacts=[contacts[s, :ncon[s]].copy() for s in range(S)])
+
+    def stats(self):
+        p = np.zeros(self.W, np.int32)
+        c = np.zeros(self.W, np.int32)
+        self._check(self.lib.mdr_phys_stats(self.h, p.ctypes.data, c.ctypes.data), "stats")
+        return p, c
+
+    def read_bvh(self):
+        slot = np.zeros((self.W, self.N, 6), np.float32)
+        leaf = np.zeros((self.W, self.N, 6), np.float32)
+        order = np.zeros((self.W, self.N), np.uint16)
+        self._check(self.lib.mdr_phys_read_bvh(self.h, slot.ctypes.data, leaf.ctypes.data,
+                                               order.ctypes.data), "read_bvh")
+        return slot, leaf, order
+
+    def get_hull(self, obj):
+        he = np.zeros((1024, 4), np.uint32)
+        ed = np.zeros(1024, np.uint32)
+        po = np.zeros(1024, np.uint32)
+        pl = np.zeros((1024, 4), np.float32)
+        cnt = np.zeros(4, np.int32)
+        self._check(self.lib.mdr_phys_get_hull(self.h, obj, he.ctypes.data, ed.ctypes.data,
+                                               po.ctypes.data, pl.ctypes.data, cnt.ctypes.data),
+                    "get_hull")
+        return dict(half_edges=he[:cnt[0]].copy(), edges=ed[:cnt[1]].copy(),
+                    polys=po[:cnt[2]].copy(), planes=pl[:cnt[2]].copy(), counts=cnt)
+
+    # ---- CUDA-only entry points -------------------------------------------
+    def column_ptr(self, col):
+        return self.lib.mdr_phys_column_ptr(self.h, col)
+
+    def launch_info(self):
+        info = np.zeros(4, np.int32)
+        self._check(self.lib.mdr_phys_launch_info(self.h, info.ctypes.data), "launch_info")
+        return dict(blocks=int(info[0]), threads=int(info[1]), smem_bytes=int(info[2]),
+                    blocks_per_sm=int(info[3]))
+
+    def kernel_ms(self):
+        n = C.c_int32(0)
+        ms = self.lib.mdr_phys_kernel_ms(self.h, C.byref(n))
+        return float(ms), int(n.value)

@@ -1,0 +1,155 @@
+/* madrona_b200 -- C ABI of the B200-native batched world step.
+ *
+ * This is the drop-in boundary for the hot path of shacklettbp/gpu-ecs-madrona
+ * (SURVEY.md section 8b). The reference has no C ABI: its surface is C++20
+ * templates (include/madrona/mw_gpu.hpp:20-76 MWCudaExecutor,
+ * include/madrona/mw_cpu.hpp:9-81 TaskGraphExecutor, include/madrona/state.hpp:
+ * 109-134 ECSRegistry, include/madrona/taskgraph.hpp:15-113 TaskGraph::Builder,
+ * include/madrona/physics.hpp:419-447 RigidBodyPhysicsSystem). Each entry point
+ * below names the reference interface it stands in for. Plain pointers and
+ * sizes only; all functions return MDR_OK (0) or a negative MDR_E* code for
+ * argument errors, and abort on CUDA errors like the reference's REQ_CUDA
+ * (include/madrona/cuda_utils.hpp:46-54). The library is libmadrona_b200.so;
+ * it has no CPU fallback: creation fails with MDR_ENODEVICE without a GPU.
+ */
+#ifndef MADRONA_B200_H
+#define MADRONA_B200_H
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+enum {
+    MDR_OK = 0,
+    MDR_EINVAL = -1,      /* bad argument                                   */
+    MDR_ENODEVICE = -2,   /* no CUDA device / wrong architecture            */
+    MDR_ECAPACITY = -3,   /* a configured capacity does not fit the device  */
+    MDR_EOVERFLOW = -4,   /* a per-world capacity overflowed during a step  */
+    MDR_ESTATE = -5       /* call made in the wrong phase (e.g. after build) */
+};
+
+/* CollisionPrimitive::Type, include/madrona/physics.hpp:251-256 */
+enum { MDR_PRIM_SPHERE = 1, MDR_PRIM_HULL = 2, MDR_PRIM_PLANE = 4 };
+/* ResponseType, include/madrona/physics.hpp:162-166 */
+enum { MDR_RESPONSE_DYNAMIC = 0, MDR_RESPONSE_KINEMATIC = 1, MDR_RESPONSE_STATIC = 2 };
+
+/* One shared collision object: a row of the reference's ObjectManager
+ * (physics.hpp:275-290: metadata, aabbs, primitives) plus the source mesh the
+ * reference's PhysicsLoader::loadObjects consumes (src/physics/
+ * physics_assets.cpp:205-391). Hull polygons use the FastPolygonList encoding
+ * [n, i0 .. i(n-1)]* (physics.hpp:12-35). */
+typedef struct mdr_object {
+    int32_t type;
+    float inv_inertia[3];
+    float inv_mass;
+    float mu_s;
+    float mu_d;
+    float aabb_min[3];
+    float aabb_max[3];
+    int32_t vert_offset;      /* first vertex in the shared vertex array       */
+    int32_t num_verts;
+    int32_t poly_offset;      /* first word in the shared polygon-word array   */
+    int32_t num_poly_words;
+} mdr_object;
+
+/* RigidBodyPhysicsSystem::init arguments (src/physics/physics.cpp:1012-1036)
+ * plus the executor's StateConfig (include/madrona/mw_gpu.hpp:20-34). */
+typedef struct mdr_phys_config {
+    int32_t num_worlds;
+    int32_t max_bodies_per_world;   /* row capacity of the rigid-body archetype  */
+    int32_t num_substeps;
+    int32_t max_contacts;           /* candidate pairs / contacts per world      */
+    float delta_t;
+    float gravity[3];
+    int32_t gpu_id;
+    int32_t block_threads;          /* 0: default                                 */
+    int32_t smem_contacts;          /* contact slots kept in shared memory; 0: default */
+} mdr_phys_config;
+
+/* Columns of the rigid-body archetype: 0 = Entity, 1..12 = phys::Cols
+ * (include/madrona/physics.hpp:449-464), in the reference's packed layout. */
+enum {
+    MDR_COL_ENTITY = 0, MDR_COL_POSITION = 1, MDR_COL_ROTATION = 2, MDR_COL_SCALE = 3,
+    MDR_COL_VELOCITY = 4, MDR_COL_OBJECT_ID = 5, MDR_COL_RESPONSE_TYPE = 6,
+    MDR_COL_SUBSTEP_PREV = 7, MDR_COL_PRESOLVE_POS = 8, MDR_COL_PRESOLVE_VEL = 9,
+    MDR_COL_EXT_FORCE = 10, MDR_COL_EXT_TORQUE = 11, MDR_COL_LEAF_ID = 12,
+    MDR_NUM_PHYS_COLS = 13
+};
+
+/* Contact, include/madrona/physics.hpp:185-192 (Loc reduced to a row). 112 B. */
+typedef struct mdr_contact {
+    int32_t ref_row, ref_pad, alt_row, alt_pad;
+    float points[4][4];
+    int32_t num_points;
+    float normal[3];
+    float lambda_n[4];
+} mdr_contact;
+
+typedef struct mdr_phys mdr_phys;
+
+/* ---- rigid-body world step ------------------------------------------------
+ * Stands in for MWCudaExecutor(StateConfig, CompileConfig) of a world whose
+ * registerTypes/setupTasks are RigidBodyPhysicsSystem::{registerTypes,
+ * setupBroadphaseTasks, setupSubstepTasks, setupCleanupTasks}
+ * (include/madrona/physics.hpp:419-447; src/mw/cuda_exec.cpp:1692-1763). */
+int32_t mdr_phys_create(const mdr_phys_config *cfg, const mdr_object *objs, int32_t num_objs,
+                        const float *verts, const uint32_t *poly_words, mdr_phys **out);
+void mdr_phys_destroy(mdr_phys *p);
+
+/* World constructor work (user WorldT ctor + RigidBodyPhysicsSystem::
+ * registerEntity, physics.cpp:1045-1053): sets how many rows each world has
+ * (host array [num_worlds]); rows get entity ids and leaf ids 0..n-1 in order
+ * and a BVH rebuild is flagged, as bvh.rebuildOnUpdate() does. */
+int32_t mdr_phys_set_row_counts(mdr_phys *p, const int32_t *rows_per_world);
+/* Host <-> device copy of one whole column, [num_worlds][max_bodies][bytes]
+ * world-major in the reference's packed layout (the StateManager export
+ * layout of a fixed-size archetype, src/core/state.cpp:481-483). */
+int32_t mdr_phys_write_column(mdr_phys *p, int32_t col, const void *host_src);
+int32_t mdr_phys_read_column(mdr_phys *p, int32_t col, void *host_dst);
+/* Device pointer of a column: MWCudaExecutor::getExported (mw_gpu.hpp:70). */
+void *mdr_phys_column_ptr(mdr_phys *p, int32_t col);
+int32_t mdr_phys_column_bytes(int32_t col);
+
+/* RigidBodyPhysicsSystem::reset semantics for the BVH (physics.cpp:1038-1043,
+ * include/madrona/physics.inl:109-112): rebuild on the next step. */
+int32_t mdr_phys_flag_rebuild(mdr_phys *p);
+
+/* MWCudaExecutor::run() (src/mw/cuda_exec.cpp:1777-1794), `num_steps` times.
+ * mdr_phys_step blocks like run(); the _async form only enqueues on the
+ * executor's stream (mdr_phys_sync waits). Returns MDR_EOVERFLOW after the
+ * sync if any world overflowed max_contacts pairs. */
+int32_t mdr_phys_step(mdr_phys *p, int32_t num_steps);
+int32_t mdr_phys_step_async(mdr_phys *p, int32_t num_steps);
+int32_t mdr_phys_sync(mdr_phys *p);
+void *mdr_phys_stream(mdr_phys *p);           /* cudaStream_t */
+
+/* One blocking step that also records the intermediates of `world`: the
+ * candidate pair list (reference order) and every substep's contact list.
+ * pairs[2*max_pairs], num_contacts[substeps], contacts[substeps*max_contacts].*/
+int32_t mdr_phys_probe_step(mdr_phys *p, int32_t world, int32_t max_pairs, int32_t *num_pairs,
+                            int32_t *pairs, int32_t *num_contacts, mdr_contact *contacts);
+/* Per-world statistics of the last step: candidate pairs and contacts of the
+ * last substep, host arrays [num_worlds] (either may be NULL). */
+int32_t mdr_phys_stats(mdr_phys *p, int32_t *pairs_per_world, int32_t *contacts_per_world);
+/* BVH singleton state for parity checks: grown slot boxes and current leaf
+ * boxes [W][max_bodies][6], traversal order [W][max_bodies] (any may be NULL). */
+int32_t mdr_phys_read_bvh(mdr_phys *p, float *slot_boxes, float *leaf_aabbs, uint16_t *order);
+/* Half-edge tables built for hull object `obj` (HalfEdgeMesh, physics.hpp:
+ * 54-146): counts[4] = half-edges, edges, faces, vertices. */
+int32_t mdr_phys_get_hull(mdr_phys *p, int32_t obj, uint32_t *half_edges, uint32_t *edges,
+                          uint32_t *polys, float *planes, int32_t *counts);
+/* Launch geometry chosen at creation: [0] blocks, [1] threads, [2] dynamic
+ * shared memory bytes per block, [3] resident blocks per SM. */
+int32_t mdr_phys_launch_info(mdr_phys *p, int32_t info[4]);
+/* Average device time of the step kernel, in ms, over the launches since the
+ * last call (CUDA events on the executor's stream); <0 if none were timed. */
+float mdr_phys_kernel_ms(mdr_phys *p, int32_t *launches);
+
+const char *mdr_version(void);
+int32_t mdr_device_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
