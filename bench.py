@@ -1,0 +1,274 @@
+#!/usr/bin/env python
+"""Benchmark of the batched world step (BASELINE.json: aggregate world-steps/s,
+collisions-64, 16 384 worlds per GPU).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W]        our CUDA path
+  python bench.py --impl reference ...                       the reference's CPU path
+
+A step = one pass of the whole physics task graph over every world of the batch.
+Prints ONE JSON line (rank 0). See DESIGN.md "Measurement" for the definitions.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "aggregate world-steps/sec (collisions-64, device-timed)"
+UNIT = "world-steps/s"
+N_ROWS, SUBSTEPS = 65, 4
+
+
+def algorithmic_bytes(pairs, contacts):
+    """A = 480 N + 32 P + S (272 N + 104 P + 840 C) bytes per world-step."""
+    return 480 * N_ROWS + 32 * pairs + SUBSTEPS * (272 * N_ROWS + 104 * pairs + 840 * contacts)
+
+
+def measured_peak():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        try:
+            return float(json.load(open(path))["hbm_gbs"]), "MEASURED_PEAKS.json hbm_gbs"
+        except Exception:
+            pass
+    return 6650.0, "fallback of B200_PROFILING.md (6.65 TB/s)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu):
+        self.gpu, self.rows, self.proc = gpu, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + self.Q,
+                 "--format=csv,noheader,nounits", "-lms", "100"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        self.t.join(timeout=2)
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[0]))
+                mx.append(float(r[1]))
+            except Exception:
+                continue
+            for n, v in zip(names, r[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        return {"sm_mhz": float(np.median(sm)) if sm else None,
+                "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def dist_env():
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    return rank, world, local
+
+
+def cpu_baseline(steps, warmup, worlds_per_thread=32, kind=None):
+    """Times the reference's CPU implementation of the path on this host's cores:
+    the unmodified reference compiled into oracle/_ref when it travelled here,
+    else the oracle restatement. A bounded sample of the same workload: the same
+    per-world scene and the same step range, fewer worlds."""
+    from gpu_ecs_madrona_b200 import scenes
+    from oracle import orc
+    if kind is None:
+        kind = "reference" if orc.available("reference") else "port"
+    if kind == "port" and not orc.available("port"):
+        orc.build("port")
+    cores = len(os.sched_getaffinity(0))
+    worlds = worlds_per_thread * cores
+    sc = scenes.collisions64(worlds)
+    o = orc.Oracle(sc, kind)
+    o.step(warmup, cores)
+    t0 = time.perf_counter()
+    o.step(steps, cores)
+    dt = time.perf_counter() - t0
+    o.close()
+    return {"value": worlds * steps / dt, "unit": UNIT, "cores": cores, "kind": kind,
+            "sample": f"{worlds} worlds x {steps} steps after {warmup} warm-up steps, "
+                      f"collisions-64, {cores} threads ({dt:.1f} s wall)"}, dt
+
+
+def run_reference(args):
+    rank, world, _ = dist_env()
+    if rank != 0:
+        return
+    base, dt = cpu_baseline(args.steps, args.warmup)
+    line = {"impl": "reference", "metric": METRIC, "value": base["value"], "unit": UNIT,
+            "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": "collisions-64 (64 dynamic unit cubes + 1 static plane per world, "
+                                   "4 substeps, dt 1/60), bounded sample: " + base["sample"]},
+            "cpu_baseline": base,
+            "e2e": {"value": base["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line))
+
+
+def run_ours(args):
+    rank, world, local = dist_env()
+    import torch
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        torch.cuda.set_device(local)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    from gpu_ecs_madrona_b200 import phys, scenes
+    W = args.worlds_per_gpu
+    sc = scenes.collisions64(W, world_offset=rank * W)
+    ex = phys.PhysExecutor(sc, gpu_id=local, block_threads=args.threads)
+    info = ex.launch_info()
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        ex.sync()
+
+    # ---- device-resident throughput -------------------------------------
+    ex.run(args.warmup)
+    ex.kernel_ms()
+    sampler = ClockSampler(local)
+    barrier()
+    sampler.start()
+    t0 = time.perf_counter()
+    ex.run_async(args.steps)
+    ex.sync()
+    wall = time.perf_counter() - t0
+    kms, launches = ex.kernel_ms()           # CUDA events on the executor's stream around the K launches
+    clocks = sampler.stop()
+    assert launches == args.steps
+    dev_ms = kms * launches
+    pairs, contacts = ex.stats()
+    P, C = float(pairs.mean()), float(contacts.mean())
+    if dist is not None:
+        t = torch.tensor([dev_ms], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dev_ms = float(t.item())
+    value = world * W * args.steps / (dev_ms * 1e-3)
+
+    # ---- end to end through the public API with host buffers ------------
+    # per step: actions in (ExternalForce, ExternalTorque) from pinned host memory,
+    # one step, observations out (Position, Rotation, Velocity) to pinned host memory.
+    ins = [(c, ex.pinned(c)) for c in (phys.COL_EXT_FORCE, phys.COL_EXT_TORQUE)]
+    outs = [(c, ex.pinned(c)) for c in (phys.COL_POSITION, phys.COL_ROTATION, phys.COL_VELOCITY)]
+    for _, a in ins:
+        a[:] = 0
+    h2d = sum(a.nbytes for _, a in ins)
+    d2h = sum(a.nbytes for _, a in outs)
+
+    def e2e_step():
+        for c, a in ins:
+            ex.write_raw_async(c, a)
+        ex.run_async(1)
+        for c, a in outs:
+            ex.read_raw_async(c, a)
+        ex.sync()
+
+    for _ in range(3):
+        e2e_step()
+    barrier()
+    e2e_steps = max(10, args.steps // 4)
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        e2e_step()
+    e2e_s = time.perf_counter() - t0
+    if dist is not None:
+        t = torch.tensor([e2e_s], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e2e_s = float(t.item())
+    e2e_value = world * W * e2e_steps / e2e_s
+    finite = bool(np.isfinite(outs[0][1].view(np.float32)[:, :N_ROWS]).all())
+
+    if rank == 0:
+        peak, peak_src = measured_peak()
+        A = algorithmic_bytes(P, C)
+        achieved = A * W / (kms * 1e-3) / 1e9
+        traffic = None
+        tpath = os.path.join(ROOT, "profiles", "traffic.json")
+        if os.path.exists(tpath):
+            try:
+                traffic = json.load(open(tpath)).get("dram_bytes_per_launch")
+            except Exception:
+                traffic = None
+        base, _ = cpu_baseline(min(args.steps, 40), min(args.warmup, 10)) if not args.no_cpu else ({}, 0)
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": dev_ms / args.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": f"collisions-64: {W} worlds per GPU x (64 dynamic unit cubes + 1 static "
+                                   "plane), 4 substeps, dt 1/60 (BASELINE.json configs[2])",
+                       "worlds_per_gpu": W, "bodies_per_world": N_ROWS, "substeps": SUBSTEPS,
+                       "mean_pairs_per_world": P, "mean_contacts_per_world": C,
+                       "l2": "state tables (%.0f MB per GPU) exceed the 126 MB L2; no flush needed"
+                             % (W * ex.row_stride() * 290 / 1e6),
+                       "launch": info, "wall_ms_per_step": 1e3 * wall / args.steps,
+                       "parallelism": f"worlds sharded over {world} GPU(s), no per-step communication"},
+            "gpu_launches": args.steps,
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d,
+                    "d2h_bytes_per_step": d2h, "steps": e2e_steps, "finite": finite},
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                         "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
+                         "algorithmic_bytes_per_world_step": A, "kernel": "physStepKernel",
+                         "kernel_ms": kms},
+            "cpu_baseline": base,
+            "clocks": clocks,
+        }
+        print(json.dumps(line))
+    ex.close()
+    if dist is not None:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=100)
+    ap.add_argument("--warmup", type=int, default=10)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--worlds-per-gpu", type=int, default=16384)
+    ap.add_argument("--threads", type=int, default=0)
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

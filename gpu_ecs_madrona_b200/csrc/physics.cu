@@ -1,0 +1,487 @@
+// CUDA executor of the rigid-body world step: persistent kernel (one block per
+// world at a time, worlds strided over a grid sized to the resident-block
+// capacity of the GPU), the rare BVH rebuild kernel, and the mdr_phys_* C ABI.
+// sm_100a only; compiled with -fmad=false (see phys_math.cuh).
+#include <cuda_runtime.h>
+
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <vector>
+
+#include "phys_step.cuh"
+#include "phys_assets.hpp"
+#include "phys_cols.hpp"
+
+using namespace mdr;
+
+#define REQ_CUDA(expr)                                                                   \
+    do {                                                                                 \
+        cudaError_t e_ = (expr);                                                         \
+        if (e_ != cudaSuccess) {                                                         \
+            fprintf(stderr, "madrona_b200: CUDA error %s at %s:%d: %s\n",                \
+                    cudaGetErrorName(e_), __FILE__, __LINE__, cudaGetErrorString(e_));   \
+            abort();                                                                     \
+        }                                                                                \
+    } while (0)
+
+// ------------------------------------------------------------------ kernels --
+extern __shared__ __align__(16) char mdr_smem[];
+
+template <int kMaxThreads, int kMinBlocks>
+__global__ void __launch_bounds__(kMaxThreads, kMinBlocks)
+physStepKernel(const __grid_constant__ StepParams p, int overflow_per_block)
+{
+    BlockCtx ctx;
+    WorldView v;
+    carveWorld(v, mdr_smem, p.t.stride, p.max_pairs, p.smem_contacts, p.a.max_verts, p.a.max_faces);
+    v.overflow = p.overflow + (size_t)blockIdx.x * overflow_per_block;
+    for (int w = blockIdx.x; w < p.t.num_worlds; w += gridDim.x) stepWorld(ctx, v, p, w);
+}
+
+// One thread per flagged world: current leaf boxes, then the reference's
+// top-down build reduced to traversal order + slot-box reset.
+__global__ void bvhRebuildKernel(const __grid_constant__ StepParams p)
+{
+    const int w = blockIdx.x * blockDim.x + threadIdx.x;
+    if (w >= p.t.num_worlds || !p.t.rebuild_flag[w]) return;
+    p.t.rebuild_flag[w] = 0;
+    const PhysTables &t = p.t;
+    const size_t r0 = (size_t)w * t.stride;
+    const int n = t.row_count[w];
+    for (int i = 0; i < n; i++) {
+        const ObjDev *o = p.a.objs + t.obj[r0 + i];
+        Box wb = applyTRS(objAABB(o), ld3(t.pos + 3 * r0, i), ld4(t.rot + 4 * r0, i), ld3(t.scale + 3 * r0, i));
+        stBox(t.leaf_aabb + 6 * r0, i,
+              expandWithMotion(wb, ldVelLin(t.vel + 6 * r0, i), p.vel_expand, p.accel_expand));
+    }
+    bvhRebuildWorld(t.leaf_aabb + 6 * r0, t.slot_box + 6 * r0, t.order + r0, t.sorted + r0, n);
+}
+
+// -------------------------------------------------------------- host state --
+typedef void (*StepKernel)(const StepParams, int);
+struct KernelVariant { int threads, min_blocks; StepKernel fn; };
+static const KernelVariant kVariants[] = {
+    { 32, 16, physStepKernel<32, 16> },
+    { 64, 8, physStepKernel<64, 8> },
+    { 64, 12, physStepKernel<64, 12> },
+    { 96, 6, physStepKernel<96, 6> },
+    { 128, 4, physStepKernel<128, 4> },
+    { 128, 6, physStepKernel<128, 6> },
+    { 256, 2, physStepKernel<256, 2> },
+};
+
+struct mdr_phys {
+    mdr_phys_config cfg;
+    HostAssets assets;
+    StepParams params;
+    std::vector<void *> allocs;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    bool timing_open = false;
+    int pending_launches = 0;
+    double timed_ms = 0.0;
+    int timed_launches = 0;
+    StepKernel kernel = nullptr;
+    int threads = 0, blocks = 0, blocks_per_sm = 0, overflow_per_block = 0;
+    size_t smem_bytes = 0;
+    bool maybe_rebuild = true;
+    int32_t *d_err = nullptr;
+    ProbeDev d_probe;   // device buffers of the probe
+    int probe_pairs_cap = 0;
+
+    template <typename T> T *dalloc(size_t n, bool zero = true)
+    {
+        void *p = nullptr;
+        size_t bytes = (n ? n : 1) * sizeof(T);
+        REQ_CUDA(cudaMalloc(&p, bytes));
+        if (zero) REQ_CUDA(cudaMemset(p, 0, bytes));
+        allocs.push_back(p);
+        return (T *)p;
+    }
+    template <typename T> T *upload(const std::vector<T> &v)
+    {
+        T *d = dalloc<T>(v.size(), false);
+        REQ_CUDA(cudaMemcpy(d, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice));
+        return d;
+    }
+};
+
+static void closeTiming(mdr_phys *p)
+{
+    if (!p->timing_open) return;
+    float ms = 0.f;
+    REQ_CUDA(cudaEventSynchronize(p->ev1));
+    REQ_CUDA(cudaEventElapsedTime(&ms, p->ev0, p->ev1));
+    p->timed_ms += ms;
+    p->timed_launches += p->pending_launches;
+    p->pending_launches = 0;
+    p->timing_open = false;
+}
+
+extern "C" {
+
+const char *mdr_version(void) { return "madrona_b200 0.1 (sm_100a)"; }
+
+int32_t mdr_device_count(void)
+{
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return n;
+}
+
+int32_t mdr_phys_column_bytes(int32_t col)
+{
+    return col >= 0 && col < MDR_NUM_PHYS_COLS ? kColBytes[col] : 0;
+}
+
+int32_t mdr_phys_create(const mdr_phys_config *cfg, const mdr_object *objs, int32_t num_objs,
+                        const float *verts, const uint32_t *poly_words, mdr_phys **out)
+{
+    if (!cfg || !out || !objs || num_objs <= 0 || cfg->num_worlds <= 0 ||
+        cfg->max_bodies_per_world <= 0 || cfg->max_bodies_per_world > 65535 ||
+        cfg->num_substeps <= 0 || cfg->max_contacts <= 0 || !(cfg->delta_t > 0.f))
+        return MDR_EINVAL;
+    if (cfg->gpu_id < 0 || cfg->gpu_id >= mdr_device_count()) return MDR_ENODEVICE;
+    REQ_CUDA(cudaSetDevice(cfg->gpu_id));
+    cudaDeviceProp prop;
+    REQ_CUDA(cudaGetDeviceProperties(&prop, cfg->gpu_id));
+    if (prop.major != 10) {
+        fprintf(stderr, "madrona_b200: device %d is sm_%d%d; this library is built for sm_100a only\n",
+                cfg->gpu_id, prop.major, prop.minor);
+        return MDR_ENODEVICE;
+    }
+
+    mdr_phys *p = new mdr_phys;
+    p->cfg = *cfg;
+    if (!buildAssets(p->assets, objs, num_objs, verts, poly_words)) {
+        fprintf(stderr, "madrona_b200: %s\n", p->assets.error.c_str());
+        delete p;
+        return MDR_EINVAL;
+    }
+    memset(&p->params, 0, sizeof(p->params));
+    StepParams &sp = p->params;
+    fillStepConstants(sp, *cfg);
+    const int W = cfg->num_worlds;
+    const int stride = (cfg->max_bodies_per_world + 3) / 4 * 4;   // every column tile 16 B aligned
+    const size_t R = (size_t)W * stride;
+    PhysTables &t = sp.t;
+    t.stride = stride;
+    t.num_worlds = W;
+    for (int c = 0; c < MDR_NUM_PHYS_COLS; c++) *colSlot(t, c) = p->dalloc<char>(R * kColBytes[c]);
+    t.row_count = p->dalloc<int32_t>(W);
+    t.leaf_aabb = p->dalloc<float>(R * 6);
+    t.slot_box = p->dalloc<float>(R * 6);
+    t.order = p->dalloc<uint16_t>(R);
+    t.sorted = p->dalloc<uint16_t>(R);
+    t.rebuild_flag = p->dalloc<uint8_t>(W);
+    sp.a.objs = p->upload(p->assets.objs);
+    sp.a.verts = p->upload(p->assets.verts);
+    sp.a.planes = p->upload(p->assets.planes);
+    sp.a.hedges = p->upload(p->assets.hedges);
+    sp.a.edges = p->upload(p->assets.edges);
+    sp.a.polys = p->upload(p->assets.polys);
+    sp.a.num_objs = num_objs;
+    sp.a.max_verts = p->assets.max_verts;
+    sp.a.max_faces = p->assets.max_faces;
+    sp.max_pairs = cfg->max_contacts;
+    sp.smem_contacts = cfg->smem_contacts > 0 ? cfg->smem_contacts : 96;
+    if (sp.smem_contacts > sp.max_pairs) sp.smem_contacts = sp.max_pairs;
+    sp.world_pairs = p->dalloc<int32_t>(W);
+    sp.world_contacts = p->dalloc<int32_t>(W);
+    p->d_err = p->dalloc<int32_t>(1);
+    sp.error_flags = p->d_err;
+    sp.probe.world = -1;
+
+    // Launch geometry: variant by thread count, grid = resident capacity.
+    const int want_threads = cfg->block_threads > 0 ? cfg->block_threads : 64;
+    int want_min_blocks = 0;
+    if (const char *e = getenv("MDR_MIN_BLOCKS")) want_min_blocks = atoi(e);
+    const KernelVariant *var = nullptr;
+    for (const KernelVariant &kv : kVariants) {
+        if (kv.threads != want_threads) continue;
+        if (!var) var = &kv;
+        if (want_min_blocks && kv.min_blocks == want_min_blocks) var = &kv;
+    }
+    if (!var) {
+        fprintf(stderr, "madrona_b200: block_threads must be one of 32, 64, 96, 128, 256\n");
+        mdr_phys_destroy(p);
+        return MDR_EINVAL;
+    }
+    p->kernel = var->fn;
+    p->threads = var->threads;
+    WorldView v;
+    p->smem_bytes = carveWorld(v, nullptr, stride, sp.max_pairs, sp.smem_contacts,
+                               sp.a.max_verts, sp.a.max_faces);
+    if (p->smem_bytes > (size_t)prop.sharedMemPerBlockOptin) {
+        fprintf(stderr, "madrona_b200: one world needs %zu B of shared memory, the device offers %zu B per block\n",
+                p->smem_bytes, (size_t)prop.sharedMemPerBlockOptin);
+        mdr_phys_destroy(p);
+        return MDR_ECAPACITY;
+    }
+    REQ_CUDA(cudaFuncSetAttribute(p->kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p->smem_bytes));
+    REQ_CUDA(cudaFuncSetAttribute(p->kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
+    int per_sm = 0;
+    REQ_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, p->kernel, p->threads, p->smem_bytes));
+    if (per_sm < 1) per_sm = 1;
+    p->blocks_per_sm = per_sm;
+    long long grid = (long long)per_sm * prop.multiProcessorCount;
+    if (grid > W) grid = W;
+    p->blocks = (int)grid;
+    p->overflow_per_block = sp.max_pairs - sp.smem_contacts;
+    sp.overflow = p->dalloc<ContactDev>((size_t)p->blocks * (p->overflow_per_block + 1), false);
+
+    REQ_CUDA(cudaStreamCreateWithFlags(&p->stream, cudaStreamNonBlocking));
+    REQ_CUDA(cudaEventCreate(&p->ev0));
+    REQ_CUDA(cudaEventCreate(&p->ev1));
+    memset(&p->d_probe, 0, sizeof(p->d_probe));
+    *out = p;
+    return MDR_OK;
+}
+
+void mdr_phys_destroy(mdr_phys *p)
+{
+    if (!p) return;
+    cudaSetDevice(p->cfg.gpu_id);
+    if (p->stream) { cudaStreamSynchronize(p->stream); cudaStreamDestroy(p->stream); }
+    if (p->ev0) cudaEventDestroy(p->ev0);
+    if (p->ev1) cudaEventDestroy(p->ev1);
+    for (void *a : p->allocs) cudaFree(a);
+    delete p;
+}
+
+int32_t mdr_phys_set_row_counts(mdr_phys *p, const int32_t *rows)
+{
+    if (!p || !rows) return MDR_EINVAL;
+    REQ_CUDA(cudaSetDevice(p->cfg.gpu_id));
+    PhysTables &t = p->params.t;
+    const int W = t.num_worlds;
+    std::vector<int32_t> ent((size_t)W * t.stride * 2), leaf((size_t)W * t.stride);
+    for (int w = 0; w < W; w++) {
+        if (rows[w] < 0 || rows[w] > p->cfg.max_bodies_per_world) return MDR_EINVAL;
+        for (int i = 0; i < t.stride; i++) {
+            size_t r = (size_t)w * t.stride + i;
+            ent[2 * r] = 0;
+            ent[2 * r + 1] = i < rows[w] ? i : -1;
+            leaf[r] = i < rows[w] ? i : -1;
+        }
+    }
+    REQ_CUDA(cudaStreamSynchronize(p->stream));
+    REQ_CUDA(cudaMemcpy(t.row_count, rows, 4 * (size_t)W, cudaMemcpyHostToDevice));
+    REQ_CUDA(cudaMemcpy(t.entity, ent.data(), ent.size() * 4, cudaMemcpyHostToDevice));
+    REQ_CUDA(cudaMemcpy(t.leaf_id, leaf.data(), leaf.size() * 4, cudaMemcpyHostToDevice));
+    return mdr_phys_flag_rebuild(p);
+}
+
+int32_t mdr_phys_write_column(mdr_phys *p, int32_t col, const void *src)
+{
+    if (!p || !src) return MDR_EINVAL;
+    void **s = colSlot(p->params.t, col);
+    if (!s) return MDR_EINVAL;
+    REQ_CUDA(cudaSetDevice(p->cfg.gpu_id));
+    const size_t nb = kColBytes[col], n = p->cfg.max_bodies_per_world;
+    REQ_CUDA(cudaMemcpy2DAsync(*s, p->params.t.stride * nb, src, n * nb, n * nb, p->cfg.num_worlds,
+                               cudaMemcpyHostToDevice, p->stream));
+    REQ_CUDA(cudaStreamSynchronize(p->stream));
+    return MDR_OK;
+}
+
+int32_t mdr_phys_read_column(mdr_phys *p, int32_t col, void *dst)
+{
+    if (!p || !dst) return MDR_EINVAL;
+    void **s = colSlot(p->params.t, col);
+    if (!s) return MDR_EINVAL;
+    REQ_CUDA(cudaSetDevice(p->cfg.gpu_id));
+    const size_t nb = kColBytes[col], n = p->cfg.max_bodies_per_world;
+    REQ_CUDA(cudaMemcpy2DAsync(dst, n * nb, *s, p->params.t.stride * nb, n * nb, p->cfg.num_worlds,
+                               cudaMemcpyDeviceToHost, p->stream));
+    REQ_CUDA(cudaStreamSynchronize(p->stream));
+    return MDR_OK;
+}
+
+int32_t mdr_phys_row_stride(mdr_phys *p) { return p ? p->params.t.stride : MDR_EINVAL; }
+
+int32_t mdr_phys_write_column_raw_async(mdr_phys *p, int32_t col, const void *src)
+{
+    if (!p || !src) return MDR_EINVAL;
+    void **s = colSlot(p->params.t, col);
+    if (!s) return MDR_EINVAL;
+    REQ_CUDA(cudaSetDevice(p->cfg.gpu_id));
+    const size_t bytes = (size_t)kColBytes[col] * p->params.t.stride * p->cfg.num_worlds;
+    REQ_CUDA(cudaMemcpyAsync(*s, src, bytes, cudaMemcpyHostToDevice, p->stream));
+    return MDR_OK;
+}
+
+int32_t mdr_phys_read_column_raw_async(mdr_phys *p, int32_t col, void *dst)
+{
+    if (!p || !dst) return MDR_EINVAL;
+    void **s = colSlot(p->params.t, col);
+    if (!s) return MDR_EINVAL;
+    REQ_CUDA(cudaSetDevice(p->cfg.gpu_id));
+    const size_t bytes = (size_t)kColBytes[col] * p->params.t.stride * p->cfg.num_worlds;
+    REQ_CUDA(cudaMemcpyAsync(dst, *s, bytes, cudaMemcpyDeviceToHost, p->stream));
+    return MDR_OK;
+}
+
+void *mdr_host_alloc(uint64_t bytes)
+{
+    void *ptr = nullptr;
+    if (cudaHostAlloc(&ptr, bytes ? bytes : 1, cudaHostAllocDefault) != cudaSuccess) {
+        cudaGetLastError();
+        return nullptr;
+    }
+    return ptr;
+}
+
+void mdr_host_free(void *ptr) { if (ptr) cudaFreeHost(ptr); }
+
+void *mdr_phys_column_ptr(mdr_phys *p, int32_t col)
+{
+    if (!p) return nullptr;
+    void **s = colSlot(p->params.t, col);
+    return s ? *s : nullptr;
+}
+
+int32_t mdr_phys_flag_rebuild(mdr_phys *p)
+{
+    if (!p) return MDR_EINVAL;
+    REQ_CUDA(cudaSetDevice(p->cfg.gpu_id));
+    REQ_CUDA(cudaMemsetAsync(p->params.t.rebuild_flag, 1, p->cfg.num_worlds, p->stream));
+    p->maybe_rebuild = true;
+    return MDR_OK;
+}
+
+int32_t mdr_phys_step_async(mdr_phys *p, int32_t num_steps)
+{
+    if (!p || num_steps < 0) return MDR_EINVAL;
+    if (num_steps == 0) return MDR_OK;
+    REQ_CUDA(cudaSetDevice(p->cfg.gpu_id));
+    closeTiming(p);
+    if (p->maybe_rebuild) {
+        const int W = p->cfg.num_worlds;
+        bvhRebuildKernel<<<(W + 63) / 64, 64, 0, p->stream>>>(p->params);
+        REQ_CUDA(cudaGetLastError());
+        p->maybe_rebuild = false;
+    }
+    REQ_CUDA(cudaEventRecord(p->ev0, p->stream));
+    for (int s = 0; s < num_steps; s++) {
+        p->kernel<<<p->blocks, p->threads, p->smem_bytes, p->stream>>>(p->params, p->overflow_per_block);
+    }
+    REQ_CUDA(cudaGetLastError());
+    REQ_CUDA(cudaEventRecord(p->ev1, p->stream));
+    p->timing_open = true;
+    p->pending_launches = num_steps;
+    return MDR_OK;
+}
+
+int32_t mdr_phys_sync(mdr_phys *p)
+{
+    if (!p) return MDR_EINVAL;
+    REQ_CUDA(cudaSetDevice(p->cfg.gpu_id));
+    REQ_CUDA(cudaStreamSynchronize(p->stream));
+    closeTiming(p);
+    int32_t err = 0;
+    REQ_CUDA(cudaMemcpy(&err, p->d_err, 4, cudaMemcpyDeviceToHost));
+    if (err & MDR_ERR_PAIR_OVERFLOW) {
+        REQ_CUDA(cudaMemset(p->d_err, 0, 4));
+        return MDR_EOVERFLOW;
+    }
+    return MDR_OK;
+}
+
+int32_t mdr_phys_step(mdr_phys *p, int32_t num_steps)
+{
+    int32_t rc = mdr_phys_step_async(p, num_steps);
+    if (rc != MDR_OK) return rc;
+    return mdr_phys_sync(p);
+}
+
+void *mdr_phys_stream(mdr_phys *p) { return p ? (void *)p->stream : nullptr; }
+
+int32_t mdr_phys_probe_step(mdr_phys *p, int32_t world, int32_t max_pairs, int32_t *num_pairs,
+                            int32_t *pairs, int32_t *num_contacts, mdr_contact *contacts)
+{
+    static_assert(sizeof(mdr_contact) == sizeof(ContactDev), "contact layout");
+    if (!p || world < 0 || world >= p->cfg.num_worlds || max_pairs <= 0 || !num_pairs || !pairs ||
+        !num_contacts || !contacts)
+        return MDR_EINVAL;
+    REQ_CUDA(cudaSetDevice(p->cfg.gpu_id));
+    const int S = p->cfg.num_substeps, MC = p->cfg.max_contacts;
+    ProbeDev &d = p->d_probe;
+    if (!d.num_pairs || p->probe_pairs_cap < max_pairs) {
+        d.num_pairs = p->dalloc<int32_t>(1);
+        d.pairs = p->dalloc<int32_t>(2 * (size_t)max_pairs);
+        d.num_contacts = p->dalloc<int32_t>(S);
+        d.contacts = p->dalloc<ContactDev>((size_t)S * MC);
+        p->probe_pairs_cap = max_pairs;
+    }
+    d.world = world; d.max_pairs = max_pairs; d.max_contacts = MC;
+    REQ_CUDA(cudaMemset(d.num_contacts, 0, 4 * S));
+    REQ_CUDA(cudaMemset(d.num_pairs, 0, 4));
+    p->params.probe = d;
+    int32_t rc = mdr_phys_step(p, 1);
+    p->params.probe.world = -1;
+    REQ_CUDA(cudaMemcpy(num_pairs, d.num_pairs, 4, cudaMemcpyDeviceToHost));
+    REQ_CUDA(cudaMemcpy(pairs, d.pairs, 8 * (size_t)max_pairs, cudaMemcpyDeviceToHost));
+    REQ_CUDA(cudaMemcpy(num_contacts, d.num_contacts, 4 * S, cudaMemcpyDeviceToHost));
+    REQ_CUDA(cudaMemcpy(contacts, d.contacts, sizeof(ContactDev) * (size_t)S * MC, cudaMemcpyDeviceToHost));
+    return rc;
+}
+
+int32_t mdr_phys_stats(mdr_phys *p, int32_t *pairs, int32_t *contacts)
+{
+    if (!p) return MDR_EINVAL;
+    REQ_CUDA(cudaSetDevice(p->cfg.gpu_id));
+    REQ_CUDA(cudaStreamSynchronize(p->stream));
+    const size_t b = 4 * (size_t)p->cfg.num_worlds;
+    if (pairs) REQ_CUDA(cudaMemcpy(pairs, p->params.world_pairs, b, cudaMemcpyDeviceToHost));
+    if (contacts) REQ_CUDA(cudaMemcpy(contacts, p->params.world_contacts, b, cudaMemcpyDeviceToHost));
+    return MDR_OK;
+}
+
+int32_t mdr_phys_read_bvh(mdr_phys *p, float *slot, float *leaf, uint16_t *order)
+{
+    if (!p) return MDR_EINVAL;
+    REQ_CUDA(cudaSetDevice(p->cfg.gpu_id));
+    REQ_CUDA(cudaStreamSynchronize(p->stream));
+    const size_t n = p->cfg.max_bodies_per_world, st = p->params.t.stride, W = p->cfg.num_worlds;
+    if (slot) REQ_CUDA(cudaMemcpy2D(slot, n * 24, p->params.t.slot_box, st * 24, n * 24, W, cudaMemcpyDeviceToHost));
+    if (leaf) REQ_CUDA(cudaMemcpy2D(leaf, n * 24, p->params.t.leaf_aabb, st * 24, n * 24, W, cudaMemcpyDeviceToHost));
+    if (order) REQ_CUDA(cudaMemcpy2D(order, n * 2, p->params.t.order, st * 2, n * 2, W, cudaMemcpyDeviceToHost));
+    return MDR_OK;
+}
+
+int32_t mdr_phys_get_hull(mdr_phys *p, int32_t obj, uint32_t *half_edges, uint32_t *edges,
+                          uint32_t *polys, float *planes, int32_t *counts)
+{
+    if (!p || !counts || obj < 0 || obj >= (int)p->assets.objs.size()) return MDR_EINVAL;
+    const ObjDev &o = p->assets.objs[obj];
+    counts[0] = o.num_hedges; counts[1] = o.num_edges; counts[2] = o.num_faces; counts[3] = o.num_verts;
+    if (o.type != MDR_PRIM_HULL) return MDR_OK;
+    if (half_edges) memcpy(half_edges, p->assets.hedges.data() + o.hedge_off, 16 * (size_t)o.num_hedges);
+    if (edges) memcpy(edges, p->assets.edges.data() + o.edge_off, 4 * (size_t)o.num_edges);
+    if (polys) memcpy(polys, p->assets.polys.data() + o.face_off, 4 * (size_t)o.num_faces);
+    if (planes) memcpy(planes, p->assets.planes.data() + 4 * (size_t)o.face_off, 16 * (size_t)o.num_faces);
+    return MDR_OK;
+}
+
+int32_t mdr_phys_launch_info(mdr_phys *p, int32_t info[4])
+{
+    if (!p || !info) return MDR_EINVAL;
+    info[0] = p->blocks; info[1] = p->threads; info[2] = (int32_t)p->smem_bytes; info[3] = p->blocks_per_sm;
+    return MDR_OK;
+}
+
+float mdr_phys_kernel_ms(mdr_phys *p, int32_t *launches)
+{
+    if (!p) return -1.f;
+    closeTiming(p);
+    int n = p->timed_launches;
+    double ms = p->timed_ms;
+    p->timed_launches = 0;
+    p->timed_ms = 0.0;
+    if (launches) *launches = n;
+    return n > 0 ? (float)(ms / n) : -1.f;
+}
+
+}  // extern "C"

@@ -84,6 +84,13 @@ def bind(lib):
         lib.mdr_phys_launch_info.argtypes = [vp, vp]
         lib.mdr_phys_kernel_ms.argtypes = [vp, vp]
         lib.mdr_phys_kernel_ms.restype = C.c_float
+        lib.mdr_phys_row_stride.argtypes = [vp]
+        lib.mdr_phys_write_column_raw_async.argtypes = [vp, i32, vp]
+        lib.mdr_phys_read_column_raw_async.argtypes = [vp, i32, vp]
+        lib.mdr_host_alloc.argtypes = [C.c_uint64]
+        lib.mdr_host_alloc.restype = vp
+        lib.mdr_host_free.argtypes = [vp]
+        lib.mdr_host_free.restype = None
     return lib
 
 
@@ -162,6 +169,9 @@ class PhysExecutor:
         if getattr(self, "h", None):
             self.lib.mdr_phys_destroy(self.h)
             self.h = None
+            for ptr in getattr(self, "_pinned", []):
+                self.lib.mdr_host_free(ptr)
+            self._pinned = []
 
     def __del__(self):
         try:
@@ -248,6 +258,26 @@ class PhysExecutor:
     # ---- CUDA-only entry points -------------------------------------------
     def column_ptr(self, col):
         return self.lib.mdr_phys_column_ptr(self.h, col)
+
+    def row_stride(self):
+        return int(self.lib.mdr_phys_row_stride(self.h))
+
+    def pinned(self, col):
+        """A page-locked host staging array [W, row_stride, bytes] for column `col`."""
+        shape = (self.W, self.row_stride(), COL_BYTES[col])
+        n = int(np.prod(shape))
+        ptr = self.lib.mdr_host_alloc(n)
+        if not ptr:
+            raise MemoryError("mdr_host_alloc")
+        self._pinned = getattr(self, "_pinned", [])
+        self._pinned.append(ptr)
+        return np.ctypeslib.as_array((C.c_uint8 * n).from_address(ptr)).reshape(shape)
+
+    def write_raw_async(self, col, arr):
+        self._check(self.lib.mdr_phys_write_column_raw_async(self.h, col, arr.ctypes.data), "write_raw")
+
+    def read_raw_async(self, col, arr):
+        self._check(self.lib.mdr_phys_read_column_raw_async(self.h, col, arr.ctypes.data), "read_raw")
 
     def launch_info(self):
         info = np.zeros(4, np.int32)

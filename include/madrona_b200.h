@@ -107,6 +107,18 @@ int32_t mdr_phys_set_row_counts(mdr_phys *p, const int32_t *rows_per_world);
  * layout of a fixed-size archetype, src/core/state.cpp:481-483). */
 int32_t mdr_phys_write_column(mdr_phys *p, int32_t col, const void *host_src);
 int32_t mdr_phys_read_column(mdr_phys *p, int32_t col, void *host_dst);
+/* The same copy of a whole table tile-for-tile, [num_worlds][row_stride][bytes]
+ * (row_stride >= max_bodies, mdr_phys_row_stride): one contiguous asynchronous
+ * transfer on the executor's stream, meant for pinned host buffers
+ * (mdr_host_alloc) -- the action-in / observation-out path of a trainer, the
+ * reference's exportCopyIn/exportCopyOut nodes (src/mw/cuda_exec.cpp:1562-1579).
+ * Ordered with the steps on the stream; mdr_phys_sync waits for it. */
+int32_t mdr_phys_row_stride(mdr_phys *p);
+int32_t mdr_phys_write_column_raw_async(mdr_phys *p, int32_t col, const void *host_src);
+int32_t mdr_phys_read_column_raw_async(mdr_phys *p, int32_t col, void *host_dst);
+/* Page-locked host memory (cudaHostAlloc / cudaFreeHost). */
+void *mdr_host_alloc(uint64_t bytes);
+void mdr_host_free(void *ptr);
 /* Device pointer of a column: MWCudaExecutor::getExported (mw_gpu.hpp:70). */
 void *mdr_phys_column_ptr(mdr_phys *p, int32_t col);
 int32_t mdr_phys_column_bytes(int32_t col);

@@ -1,0 +1,63 @@
+"""Generates tests/golden/*.npz from the UNMODIFIED reference compiled by
+oracle/Makefile (oracle/_ref/libmadrona_ref.so, needs /root/reference). Run in
+the build container: `python tests/golden/make_golden.py`. The fixtures pin the
+oracle restatement (tests/test_oracle_pin.py) and the CUDA path
+(tests/test_gpu_parity.py) on machines where the reference is not mounted.
+"""
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, ROOT)
+from gpu_ecs_madrona_b200 import scenes  # noqa: E402
+from oracle import orc  # noqa: E402
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+
+CASES = {
+    # name: (scene factory, kwargs, snapshot steps, probed world)
+    "collisions64": (scenes.collisions64, dict(num_worlds=4), (1, 10, 40, 100), 1),
+    "tumble24": (scenes.tumble, dict(num_worlds=6, num_bodies=24), (1, 5, 30), 2),
+    "tumble12_noplane": (scenes.tumble, dict(num_worlds=4, num_bodies=12, seed=7, spread=0.8,
+                                             with_plane=False), (1, 8), 0),
+}
+
+
+def main():
+    orc.build("ref")
+    for name, (fn, kw, snaps, pw) in CASES.items():
+        sc = fn(**kw)
+        ref = orc.Oracle(sc, "reference")
+        # the probe step doubles as step 1
+        out = {}
+        pr = ref.probe_step(pw)
+        out["probe_world"] = np.int32(pw)
+        out["probe_pairs"] = pr["pairs"]
+        out["probe_num_contacts"] = pr["num_contacts"]
+        for s, c in enumerate(pr["contacts"]):
+            out[f"probe_contacts_{s}"] = c
+        out["probe_slot_boxes"] = pr["slot_boxes"]
+        out["probe_leaf_aabbs"] = pr["leaf_aabbs"]
+        out["probe_ref_rank"] = pr["ref_rank"]
+        # every other world takes its first step too
+        rest = orc.Oracle(sc, "reference")
+        rest.step()
+        step = 1
+        for snap in snaps:
+            while step < snap:
+                rest.step()
+                step += 1
+            pos, rot, vel = rest.state()
+            out[f"pos_{snap}"], out[f"rot_{snap}"], out[f"vel_{snap}"] = pos, rot, vel
+        # the probed world of `ref` must agree with the plain run after step 1
+        p1 = ref.state()
+        assert np.array_equal(p1[0][pw].view(np.uint32), out["pos_%d" % snaps[0]][pw].view(np.uint32)) \
+            or snaps[0] != 1
+        np.savez_compressed(os.path.join(HERE, name + ".npz"), **out)
+        print(name, {k: getattr(v, "shape", v) for k, v in out.items() if k.startswith(("pos", "probe_pairs"))})
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,178 @@
+"""Parity of the CUDA world step (through the C ABI) against the oracle, the
+golden fixtures of the compiled reference, and size-independent properties at
+BASELINE.json's full size. Bit-exact: positions, rotations, velocities, pair
+lists, contact manifolds."""
+import numpy as np
+import pytest
+
+from gpu_ecs_madrona_b200 import phys, scenes
+from tests.golden.make_golden import CASES
+from tests.util import assert_state_equal, bits, contacts_equal, load_golden, worlds_equal
+
+pytestmark = pytest.mark.gpu
+
+SCENES = {
+    "collisions64": lambda: scenes.collisions64(64),
+    "collisions16": lambda: scenes.collisions64(33, num_cubes=16),
+    "tumble24": lambda: scenes.tumble(48),
+    "tumble40": lambda: scenes.tumble(16, num_bodies=40, spread=1.0, seed=3),
+    "tumble12_noplane": lambda: scenes.tumble(16, num_bodies=12, seed=7, spread=0.8, with_plane=False),
+}
+
+
+@pytest.mark.parametrize("threads", [32, 64, 128])
+@pytest.mark.parametrize("name", sorted(SCENES))
+def test_cuda_matches_oracle(cuda_lib, port_oracle, name, threads):
+    sc = SCENES[name]()
+    o = port_oracle.Oracle(sc, "port")
+    e = phys.PhysExecutor(sc, block_threads=threads)
+    for st in range(40):
+        o.step(1, 8)
+        e.run()
+        assert_state_equal(e.state(), o.state(), None, f"{name} T={threads} step {st}")
+    for col in (phys.COL_SUBSTEP_PREV, phys.COL_PRESOLVE_POS, phys.COL_PRESOLVE_VEL):
+        assert np.array_equal(e.read(col), o.read(col)), col
+
+
+@pytest.mark.parametrize("name", sorted(CASES))
+def test_cuda_matches_reference_golden(cuda_lib, port_oracle, name):
+    fn, kw, snaps, pw = CASES[name]
+    g = load_golden(name)
+    sc = fn(**kw)
+    o = port_oracle.Oracle(sc, "port")   # only to know which worlds hit the reference's UB
+    e = phys.PhysExecutor(sc)
+    step = 0
+    for snap in snaps:
+        while step < snap:
+            e.run(); o.step()
+            step += 1
+        det = o.indeterminate() == 0
+        assert_state_equal(e.state(), (g[f"pos_{snap}"], g[f"rot_{snap}"], g[f"vel_{snap}"]),
+                           det, f"{name} step {snap}")
+    e2 = phys.PhysExecutor(sc, smem_contacts=8)    # exercises the global overflow slots
+    pr = e2.probe_step(pw)
+    assert np.array_equal(pr["pairs"], g["probe_pairs"])
+    assert np.array_equal(pr["num_contacts"], g["probe_num_contacts"])
+    slot, leaf, order = e2.read_bvh()
+    assert np.array_equal(bits(slot[pw]), bits(g["probe_slot_boxes"]))
+    assert np.array_equal(bits(leaf[pw]), bits(g["probe_leaf_aabbs"]))
+    rank = np.empty(sc.bodies_per_world, np.int32)
+    rank[order[pw].astype(np.int64)] = np.arange(sc.bodies_per_world)
+    assert np.array_equal(rank, g["probe_ref_rank"])
+    o2 = port_oracle.Oracle(sc, "port")
+    o2.probe_step(pw)
+    if o2.indeterminate()[pw] == 0:
+        for s, c in enumerate(pr["contacts"]):
+            assert contacts_equal(c, g[f"probe_contacts_{s}"]), f"substep {s}"
+
+
+def test_cuda_drift_100_steps(cuda_lib, port_oracle):
+    """north_star: within a stated drift bound after 100 steps. The bound here is 0."""
+    sc = scenes.collisions64(32)
+    o = port_oracle.Oracle(sc, "port")
+    e = phys.PhysExecutor(sc)
+    o.step(100, 8)
+    e.run(100)
+    assert_state_equal(e.state(), o.state(), None, "100 steps")
+
+
+def test_cuda_ragged_and_empty_worlds(cuda_lib, port_oracle):
+    full = scenes.tumble(6, num_bodies=15)
+    rows = np.array([16, 9, 1, 0, 5, 16], np.int32)
+    full.rows_per_world = rows
+    e = phys.PhysExecutor(full)
+    e.run(12)
+    got = e.state()
+    for w, n in enumerate(rows):
+        if n == 0:
+            continue
+        sub = scenes.tumble(6, num_bodies=15)
+        sl = slice(w, w + 1)
+        one = scenes.Scene(1, int(n), sub.num_substeps, sub.max_contacts, sub.delta_t, sub.gravity,
+                           sub.objects, sub.pos[sl, :n], sub.rot[sl, :n], sub.scale[sl, :n],
+                           sub.vel[sl, :n], sub.obj_ids[sl, :n], sub.response[sl, :n],
+                           sub.ext_force[sl, :n], sub.ext_torque[sl, :n])
+        o = port_oracle.Oracle(one, "port")
+        o.step(12)
+        if o.indeterminate()[0]:
+            continue
+        for a, b in zip(got, o.state()):
+            assert np.array_equal(bits(a[w, :n]), bits(b[0])), f"world {w}"
+    assert np.array_equal(got[0][3], np.ascontiguousarray(full.pos[3], np.float32))
+
+
+def test_cuda_pair_overflow_reports(cuda_lib):
+    sc = scenes.tumble(2, num_bodies=40, spread=0.6, seed=5, max_contacts=64)
+    e = phys.PhysExecutor(sc)
+    with pytest.raises(phys.MadronaError) as ei:
+        e.run()
+    assert ei.value.code == phys.MDR_EOVERFLOW
+
+
+def test_cuda_rebuild_flag(cuda_lib, port_oracle):
+    sc = scenes.tumble(8, num_bodies=20)
+    o = port_oracle.Oracle(sc, "port")
+    e = phys.PhysExecutor(sc)
+    o.step(10); e.run(10)
+    o.flag_rebuild(); e.flag_rebuild()
+    for st in range(10):
+        o.step(); e.run()
+        assert_state_equal(e.state(), o.state(), None, f"after rebuild step {st}")
+
+
+def test_full_size_properties(cuda_lib, port_oracle):
+    """collisions-64 at 16 384 worlds (BASELINE.json configs[2]): (1) a sample
+    of worlds spread over the whole grid equals the oracle bit for bit, (2) the
+    result does not depend on the block size / which block stepped a world,
+    (3) sharding by world_offset reproduces the same worlds, (4) state stays
+    finite and cubes stay above the plane."""
+    W, steps = 16384, 20
+    sc = scenes.collisions64(W)
+    e = phys.PhysExecutor(sc)
+    e.run(steps)
+    got = e.state()
+    idx = np.unique(np.concatenate([np.arange(0, W, 257), [W - 1]]))
+    for w in idx[:: max(1, len(idx) // 24)]:
+        one = scenes.collisions64(1, world_offset=int(w))
+        o = port_oracle.Oracle(one, "port")
+        o.step(steps)
+        for a, b in zip(got, o.state()):
+            assert np.array_equal(bits(a[w]), bits(b[0])), f"world {w}"
+    e128 = phys.PhysExecutor(sc, block_threads=128)
+    e128.run(steps)
+    assert worlds_equal(got, e128.state()).all()
+    shard = scenes.collisions64(1024, world_offset=8192)
+    es = phys.PhysExecutor(shard)
+    es.run(steps)
+    for a, b in zip(got, es.state()):
+        assert np.array_equal(bits(a[8192:8192 + 1024]), bits(b))
+    assert np.isfinite(got[0]).all() and np.isfinite(got[2]).all()
+    assert (got[0][:, 1:, 2] > 0.4).all()
+    pairs, contacts = e.stats()
+    assert pairs.min() >= 1 and contacts.max() <= sc.max_contacts
+
+
+def test_exported_column_pointer_is_in_place(cuda_lib):
+    """getExported semantics: the device pointer aliases the table (zero copy)."""
+    import torch
+    sc = scenes.collisions64(8)
+    e = phys.PhysExecutor(sc)
+    e.run(2)
+    ptr = e.column_ptr(phys.COL_POSITION)
+    assert ptr
+    stride = (sc.bodies_per_world + 3) // 4 * 4
+    n = sc.num_worlds * stride * 3
+    buf = (torch.empty(0, dtype=torch.float32, device="cuda:0"))
+    import ctypes
+    import glob
+    import os
+    host = np.empty(n, np.float32)
+    cands = glob.glob("/usr/local/cuda/lib64/libcudart.so*") + glob.glob(
+        os.path.join(os.path.dirname(torch.__file__), "..", "nvidia", "cuda_runtime", "lib", "libcudart.so*"))
+    cudart = ctypes.CDLL(sorted(cands)[0])
+    rc = cudart.cudaMemcpy(ctypes.c_void_p(host.ctypes.data), ctypes.c_void_p(ptr),
+                           ctypes.c_size_t(4 * n), ctypes.c_int(2))
+    assert rc == 0
+    pos = host.reshape(sc.num_worlds, stride, 3)[:, :sc.bodies_per_world]
+    assert np.array_equal(bits(pos), bits(e.state()[0]))
+    del buf

@@ -1,0 +1,62 @@
+"""Pins the oracle restatement (oracle/port.cpp): bit-for-bit against the
+compiled reference where it is available, and against the golden fixtures the
+reference produced (tests/golden/make_golden.py) everywhere."""
+import numpy as np
+import pytest
+
+from gpu_ecs_madrona_b200 import scenes
+from tests.golden.make_golden import CASES
+from tests.util import assert_state_equal, bits, contacts_equal, load_golden
+
+
+@pytest.mark.parametrize("name", sorted(CASES))
+def test_port_matches_golden(port_oracle, name):
+    fn, kw, snaps, pw = CASES[name]
+    g = load_golden(name)
+    sc = fn(**kw)
+    o = port_oracle.Oracle(sc, "port")
+    step = 0
+    for snap in snaps:
+        while step < snap:
+            o.step()
+            step += 1
+        det = o.indeterminate() == 0
+        assert det.any()
+        assert_state_equal(o.state(), (g[f"pos_{snap}"], g[f"rot_{snap}"], g[f"vel_{snap}"]),
+                           det, f"{name} step {snap}")
+    o2 = port_oracle.Oracle(sc, "port")
+    pr = o2.probe_step(pw)
+    assert np.array_equal(pr["pairs"], g["probe_pairs"])
+    assert np.array_equal(pr["num_contacts"], g["probe_num_contacts"])
+    assert np.array_equal(pr["ref_rank"], g["probe_ref_rank"])
+    assert np.array_equal(bits(pr["slot_boxes"]), bits(g["probe_slot_boxes"]))
+    assert np.array_equal(bits(pr["leaf_aabbs"]), bits(g["probe_leaf_aabbs"]))
+    if o2.indeterminate()[pw] == 0:
+        for s, c in enumerate(pr["contacts"]):
+            assert contacts_equal(c, g[f"probe_contacts_{s}"]), f"substep {s}"
+
+
+@pytest.mark.parametrize("scene", ["collisions64", "tumble24", "tumble40"])
+def test_port_matches_compiled_reference(port_oracle, ref_oracle, scene):
+    sc = {"collisions64": lambda: scenes.collisions64(6),
+          "tumble24": lambda: scenes.tumble(12),
+          "tumble40": lambda: scenes.tumble(6, num_bodies=40, spread=1.0, seed=3)}[scene]()
+    r = ref_oracle.Oracle(sc, "reference")
+    p = port_oracle.Oracle(sc, "port")
+    for st in range(25):
+        r.step()
+        p.step()
+        det = p.indeterminate() == 0
+        assert_state_equal(p.state(), r.state(), det, f"{scene} step {st}")
+    assert det.any()
+
+
+def test_hull_tables_match_reference(port_oracle, ref_oracle):
+    sc = scenes.tumble(1)
+    r = ref_oracle.Oracle(sc, "reference")
+    p = port_oracle.Oracle(sc, "port")
+    for obj in (0, 1):
+        a, b = r.get_hull(obj), p.get_hull(obj)
+        for k in ("half_edges", "edges", "polys"):
+            assert np.array_equal(a[k], b[k]), k
+        assert np.array_equal(bits(a["planes"]), bits(b["planes"]))
