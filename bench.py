@@ -97,7 +97,7 @@ def dist_env():
     return rank, world, local
 
 
-def cpu_baseline(steps, warmup, worlds_per_thread=32, kind=None):
+def cpu_baseline(steps, warmup, worlds_per_thread=256, kind=None):
     """Times the reference's CPU implementation of the path on this host's cores:
     the unmodified reference compiled into oracle/_ref when it travelled here,
     else the oracle restatement. A bounded sample of the same workload: the same
