@@ -150,7 +150,8 @@ def run_ours(args):
     from gpu_ecs_madrona_b200 import phys, scenes
     W = args.worlds_per_gpu
     sc = scenes.collisions64(W, world_offset=rank * W)
-    ex = phys.PhysExecutor(sc, gpu_id=local, block_threads=args.threads)
+    ex = phys.PhysExecutor(sc, gpu_id=local, block_threads=args.threads,
+                           worlds_per_block=args.worlds_per_block)
     info = ex.launch_info()
 
     def barrier():
@@ -261,7 +262,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--worlds-per-gpu", type=int, default=16384)
-    ap.add_argument("--threads", type=int, default=0)
+    ap.add_argument("--threads", type=int, default=0, help="threads per world (0: library default)")
+    ap.add_argument("--worlds-per-block", type=int, default=0)
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     args = ap.parse_args()
     if args.impl == "reference":

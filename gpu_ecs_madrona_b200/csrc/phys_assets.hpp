@@ -94,6 +94,10 @@ inline bool buildHalfEdgeMesh(HostAssets &out, ObjDev &o, const float *verts, in
     o.num_hedges = (int32_t)hedges.size();
     o.num_edges = (int32_t)out.edges.size() - o.edge_off;
     if (2 * o.num_edges != o.num_hedges) { out.error = "open mesh: an edge has no twin"; return false; }
+    if (num_verts > MDR_MAX_HULL_VERTS || (int)face > MDR_MAX_HULL_FACES) {
+        out.error = "hull exceeds the compiled vertex / face capacity of the narrowphase";
+        return false;
+    }
     out.hedges.insert(out.hedges.end(), hedges.begin(), hedges.end());
     if (num_verts > out.max_verts) out.max_verts = num_verts;
     if ((int)face > out.max_faces) out.max_faces = (int)face;

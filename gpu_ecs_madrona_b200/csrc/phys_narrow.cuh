@@ -1,10 +1,11 @@
 // Narrowphase: hull-hull and hull-plane SAT, clipping, manifold reduction
 // (src/physics/narrowphase.cpp:139-235, 309-393, 418-576, 578-661, 678-1121,
-// 1182-1364, 1515-1728), one thread per candidate pair, hull vertices and face
-// planes pre-transformed once per body per substep into shared memory.
+// 1182-1364, 1515-1728), one thread per candidate pair. Hull vertices and face
+// planes are transformed to world space on the fly (makeHullState, :139-212):
+// streamed for the hull-plane test, into per-thread arrays for hull-hull.
+// Contacts leave in solver form (SolverContact).
 #pragma once
 #include "phys_world.cuh"
-#include "phys_solver.cuh"
 
 namespace mdr {
 
@@ -12,11 +13,57 @@ namespace mdr {
 #define MDR_MAX_POLY 24     // vertices of a clipped contact polygon
 #endif
 
-// World-space hull of one body, in SMEM.
-struct HullRef {
-    const float *v;        // xyz packed
-    const float *pl;       // nx ny nz d
+MDR_HD SolverContact *contactSlot(const WorldView &v, int p)
+{
+    return p < v.smem_contacts ? v.contacts + p : v.overflow + (p - v.smem_contacts);
+}
+
+// Object-to-world transform of one body (makeHullState's matrices).
+struct BodyXf {
+    V3 t;
+    M3 vtx, nrm;
     const ObjDev *o;
+};
+
+MDR_HD BodyXf bodyXf(const WorldView &v, const StepParams &p, int row)
+{
+    BodyXf x;
+    x.o = p.a.objs + (v.meta[row] & 0xffffu);
+    x.t = ld3(v.pos, row);
+    const V3 s = ld3(v.scale, row);
+    M3 rot = matFromQuat(ld4(v.rot, row));
+    x.vtx = matMulDiag(rot, s);
+    x.nrm = matMulDiag(rot, mk3(1.f / s.x, 1.f / s.y, 1.f / s.z));
+    return x;
+}
+
+MDR_HD V3 worldVert(const BodyXf &x, const float *verts, int k)
+{
+    V3 lv = mk3(MDR_LDG(verts + 3 * k), MDR_LDG(verts + 3 * k + 1), MDR_LDG(verts + 3 * k + 2));
+    return matMul(x.vtx, lv) + x.t;
+}
+
+MDR_HD V3 worldNormal(const BodyXf &x, const float *planes, int f)
+{
+    V3 ln = mk3(MDR_LDG(planes + 4 * f), MDR_LDG(planes + 4 * f + 1), MDR_LDG(planes + 4 * f + 2));
+    return normalize(matMul(x.nrm, ln));
+}
+
+MDR_HD Plane worldPlane(const BodyXf &x, const float *planes, int f)
+{
+    V3 ln = mk3(MDR_LDG(planes + 4 * f), MDR_LDG(planes + 4 * f + 1), MDR_LDG(planes + 4 * f + 2));
+    float ld = MDR_LDG(planes + 4 * f + 3);
+    V3 origin = matMul(x.vtx, ln * ld) + x.t;
+    Plane pl;
+    pl.n = normalize(matMul(x.nrm, ln));
+    pl.d = dot(pl.n, origin);
+    return pl;
+}
+
+// World-space hull of one body in per-thread arrays (hull-hull only).
+struct HullRef {
+    const V3 *v;
+    const Plane *pl;
     const HEdgeDev *he;
     const uint32_t *edges;
     const uint32_t *polys;
@@ -24,72 +71,35 @@ struct HullRef {
     V3 center;
 };
 
-MDR_HD V3 hv(const HullRef &h, int i) { return mk3(h.v[3 * i], h.v[3 * i + 1], h.v[3 * i + 2]); }
-MDR_HD Plane hp(const HullRef &h, int f)
-{
-    Plane p;
-    p.n = mk3(h.pl[4 * f], h.pl[4 * f + 1], h.pl[4 * f + 2]);
-    p.d = h.pl[4 * f + 3];
-    return p;
-}
-MDR_HD HEdgeDev ldHE(const HullRef &h, uint32_t i)
+MDR_HD V3 hv(const HullRef &h, int i) { return h.v[i]; }
+MDR_HD Plane hp(const HullRef &h, int f) { return h.pl[f]; }
+MDR_HD HEdgeDev ldHE(const HEdgeDev *he, uint32_t i)
 {
     HEdgeDev e;
-    e.next = MDR_LDG(&h.he[i].next); e.twin = MDR_LDG(&h.he[i].twin);
-    e.root = MDR_LDG(&h.he[i].root); e.poly = MDR_LDG(&h.he[i].poly);
+    e.next = MDR_LDG(&he[i].next); e.twin = MDR_LDG(&he[i].twin);
+    e.root = MDR_LDG(&he[i].root); e.poly = MDR_LDG(&he[i].poly);
     return e;
 }
+MDR_HD HEdgeDev ldHE(const HullRef &h, uint32_t i) { return ldHE(h.he, i); }
 
-MDR_HD HullRef hullRef(const WorldView &v, const StepParams &p, int row)
+MDR_HD HullRef makeHull(const BodyXf &x, const StepParams &p, V3 *dst_v, Plane *dst_p)
 {
     HullRef h;
-    const ObjDev *o = p.a.objs + v.obj[row];
-    h.o = o;
-    h.v = v.hverts + (size_t)row * v.hv_stride;
-    h.pl = v.hplanes + (size_t)row * v.hp_stride;
-    h.he = p.a.hedges + MDR_LDG(&o->hedge_off);
-    h.edges = p.a.edges + MDR_LDG(&o->edge_off);
-    h.polys = p.a.polys + MDR_LDG(&o->face_off);
+    const ObjDev *o = x.o;
+    const float *src_v = p.a.verts + 3 * MDR_LDG(&o->vert_off);
+    const float *src_p = p.a.planes + 4 * MDR_LDG(&o->face_off);
     h.nv = MDR_LDG(&o->num_verts);
     h.nf = MDR_LDG(&o->num_faces);
     h.ne = MDR_LDG(&o->num_edges);
-    h.center = ld3(v.pos, row);
+    for (int k = 0; k < h.nv; k++) dst_v[k] = worldVert(x, src_v, k);
+    for (int f = 0; f < h.nf; f++) dst_p[f] = worldPlane(x, src_p, f);
+    h.v = dst_v;
+    h.pl = dst_p;
+    h.he = p.a.hedges + MDR_LDG(&o->hedge_off);
+    h.edges = p.a.edges + MDR_LDG(&o->edge_off);
+    h.polys = p.a.polys + MDR_LDG(&o->face_off);
+    h.center = x.t;
     return h;
-}
-
-// Per body, per substep: world AABB of the object box (the narrowphase's
-// cheap reject, narrowphase.cpp:1583-1596) and makeHullState (:139-212).
-MDR_HD void transformBodies(const BlockCtx &c, WorldView &v, const StepParams &p)
-{
-    for (int i = c.tid(); i < v.n; i += c.nthreads()) {
-        const ObjDev *o = p.a.objs + v.obj[i];
-        const V3 t = ld3(v.pos, i);
-        const Q4 r = ld4(v.rot, i);
-        const V3 s = ld3(v.scale, i);
-        stBox(v.box, i, applyTRS(objAABB(o), t, r, s));
-        if (MDR_LDG(&o->type) != 2) continue;
-        M3 rot = matFromQuat(r);
-        M3 vtx = matMulDiag(rot, s);
-        M3 nrm = matMulDiag(rot, mk3(1.f / s.x, 1.f / s.y, 1.f / s.z));
-        const float *src_v = p.a.verts + 3 * MDR_LDG(&o->vert_off);
-        const float *src_p = p.a.planes + 4 * MDR_LDG(&o->face_off);
-        float *dv = v.hverts + (size_t)i * v.hv_stride;
-        float *dp = v.hplanes + (size_t)i * v.hp_stride;
-        const int nv = MDR_LDG(&o->num_verts), nf = MDR_LDG(&o->num_faces);
-        for (int k = 0; k < nv; k++) {
-            V3 lv = mk3(MDR_LDG(src_v + 3 * k), MDR_LDG(src_v + 3 * k + 1), MDR_LDG(src_v + 3 * k + 2));
-            V3 wv = matMul(vtx, lv) + t;
-            dv[3 * k] = wv.x; dv[3 * k + 1] = wv.y; dv[3 * k + 2] = wv.z;
-        }
-        for (int f = 0; f < nf; f++) {
-            V3 ln = mk3(MDR_LDG(src_p + 4 * f), MDR_LDG(src_p + 4 * f + 1), MDR_LDG(src_p + 4 * f + 2));
-            float ld = MDR_LDG(src_p + 4 * f + 3);
-            V3 origin = matMul(vtx, ln * ld) + t;
-            V3 wn = normalize(matMul(nrm, ln));
-            dp[4 * f] = wn.x; dp[4 * f + 1] = wn.y; dp[4 * f + 2] = wn.z;
-            dp[4 * f + 3] = dot(wn, origin);
-        }
-    }
 }
 
 // narrowphase.cpp:309-350
@@ -206,69 +216,63 @@ MDR_HD int clipPolygon(V3 *dst, Plane cp, const V3 *in, int n_in)
     return n;
 }
 
-// Writes the manifold of a face contact into `ct` (buildFaceContactManifold,
-// narrowphase.cpp:790-864). The >4-point reduction reproduces the reference as
-// written: `largestArea` is never updated, so point 2 is the LAST candidate of
-// positive signed area and point 3 the LAST of negative area; when
-// none qualifies the reference reads an uninitialised slot -- here the slot
-// repeats point 0, like oracle/port.cpp, and such worlds are excluded from
-// bit-exact comparison by the tests.
-MDR_HD void buildManifold(ContactDev *ct, V3 n, V3 *contacts, float *depths, int num)
+
+// A contact manifold before it is handed to the solver.
+struct Manifold { V3 pts[4]; float depths[4]; int n; V3 normal; };
+
+// buildFaceContactManifold, narrowphase.cpp:790-864. The >4-point reduction
+// reproduces the reference as written: `largestArea` is never updated, so point
+// 2 is the LAST candidate of positive signed area and point 3 the LAST of
+// negative area; when none qualifies the reference reads an
+// uninitialised slot -- here the slot repeats point 0 (point 1: zeros), like
+// the CPU checker, and such worlds are excluded from bit-exact comparison.
+MDR_HD void buildManifold(Manifold &m, V3 n, V3 *contacts, float *depths, int num)
 {
-    V3 pts[4];
-    float dps[4];
-    int cnt;
+    const V3 zero = mk3(0.f, 0.f, 0.f);
+    for (int i = 0; i < 4; i++) { m.pts[i] = zero; m.depths[i] = 0.f; }
     if (num <= 4) {
-        cnt = num;
-        for (int i = 0; i < num; i++) { pts[i] = contacts[i]; dps[i] = depths[i]; }
+        m.n = num;
+        for (int i = 0; i < num; i++) { m.pts[i] = contacts[i]; m.depths[i] = depths[i]; }
     } else {
-        cnt = 4;
-        pts[0] = contacts[0];
-        dps[0] = depths[0];
-        V3 p0 = pts[0];
+        m.n = 4;
+        m.pts[0] = contacts[0];
+        m.depths[0] = depths[0];
+        V3 p0 = m.pts[0];
         float largest_d2 = 0.0f;
         int far_idx = 0;
-        pts[1] = mk3(0.f, 0.f, 0.f); dps[1] = 0.f;
         for (int i = 1; i < num; i++) {
             float d2 = len2(p0 - contacts[i]);
             if (d2 > largest_d2) {
                 largest_d2 = d2;
-                pts[1] = contacts[i];
-                dps[1] = depths[i];
+                m.pts[1] = contacts[i];
+                m.depths[1] = depths[i];
                 far_idx = i;
             }
         }
-        contacts[far_idx] = pts[0];
-        V3 diff0 = pts[1] - p0;
+        contacts[far_idx] = m.pts[0];
+        V3 diff0 = m.pts[1] - p0;
         int area_idx = 0;
-        pts[2] = pts[3] = pts[0];
-        dps[2] = dps[3] = dps[0];
+        m.pts[2] = m.pts[3] = m.pts[0];
+        m.depths[2] = m.depths[3] = m.depths[0];
         for (int i = 1; i < num; i++) {
             float area = dot(n, cross(diff0, contacts[i] - p0));
-            if (area > 0.0f) { pts[2] = contacts[i]; dps[2] = depths[i]; area_idx = i; }
+            if (area > 0.0f) { m.pts[2] = contacts[i]; m.depths[2] = depths[i]; area_idx = i; }
         }
-        contacts[area_idx] = pts[0];
+        contacts[area_idx] = m.pts[0];
         for (int i = 1; i < num; i++) {
             float area = dot(n, cross(diff0, contacts[i] - p0));
-            if (area < 0.0f) { pts[3] = contacts[i]; dps[3] = depths[i]; }
+            if (area < 0.0f) { m.pts[3] = contacts[i]; m.depths[3] = depths[i]; }
         }
     }
-    // Manifold is expressed in world space through an identity transform
+    // The manifold goes to world space through an identity transform
     // (narrowphase.cpp:855-863): kept, it turns -0 into +0.
     const Q4 ident = mk4(1.f, 0.f, 0.f, 0.f);
-    const V3 zero = mk3(0.f, 0.f, 0.f);
-    for (int i = 0; i < 4; i++) {
-        V3 q = i < cnt ? rotate(ident, pts[i]) + zero : zero;
-        ct->pts[i][0] = q.x; ct->pts[i][1] = q.y; ct->pts[i][2] = q.z;
-        ct->pts[i][3] = i < cnt ? dps[i] : 0.f;
-    }
-    V3 wn = rotate(ident, n);
-    ct->normal[0] = wn.x; ct->normal[1] = wn.y; ct->normal[2] = wn.z;
-    ct->num_points = cnt;
+    for (int i = 0; i < m.n; i++) m.pts[i] = rotate(ident, m.pts[i]) + zero;
+    m.normal = rotate(ident, n);
 }
 
 // createFaceContact, narrowphase.cpp:866-972
-MDR_HD void faceContact(ContactDev *ct, Plane ref_plane, int ref_face, int inc_face,
+MDR_HD void faceContact(Manifold &m, Plane ref_plane, int ref_face, int inc_face,
                         const HullRef &ref, const HullRef &other)
 {
     V3 buf_a[MDR_MAX_POLY], buf_b[MDR_MAX_POLY];
@@ -307,32 +311,11 @@ MDR_HD void faceContact(ContactDev *ct, Plane ref_plane, int ref_face, int inc_f
             below++;
         }
     }
-    buildManifold(ct, ref_plane.n, in, depths, below);
-}
-
-// createFacePlaneContact, narrowphase.cpp:974-1017
-MDR_HD void facePlaneContact(ContactDev *ct, Plane plane, int inc_face, const HullRef &h)
-{
-    V3 pts[MDR_MAX_POLY];
-    float depths[MDR_MAX_POLY];
-    uint32_t he = MDR_LDG(h.polys + inc_face), start = he;
-    int n = 0;
-    do {
-        HEdgeDev e = ldHE(h, he);
-        he = e.next;
-        V3 vv = hv(h, e.root);
-        float d = planeDist(plane, vv);
-        if (d < 0.0f && n < MDR_MAX_POLY) {
-            pts[n] = vv - d * plane.n;
-            depths[n] = -d;
-            n++;
-        }
-    } while (he != start);
-    buildManifold(ct, plane.n, pts, depths, n);
+    buildManifold(m, ref_plane.n, in, depths, below);
 }
 
 // shortestSegmentBetween + createEdgeContact, narrowphase.cpp:1020-1121
-MDR_HD void edgeContact(ContactDev *ct, V3 normal, float sep, int ea, int eb,
+MDR_HD void edgeContact(Manifold &m, V3 normal, float sep, int ea, int eb,
                         const HullRef &a, const HullRef &b)
 {
     V3 a1 = hv(a, MDR_LDG(&a.he[ea].root)), a2 = hv(a, MDR_LDG(&a.he[MDR_LDG(&a.he[ea].next)].root));
@@ -348,65 +331,173 @@ MDR_HD void edgeContact(ContactDev *ct, V3 normal, float sep, int ea, int eb,
     V3 contact = a1 + s * v1;
     const Q4 ident = mk4(1.f, 0.f, 0.f, 0.f);
     const V3 zero = mk3(0.f, 0.f, 0.f);
-    V3 q = rotate(ident, contact) + zero;
-    for (int i = 0; i < 4; i++) for (int k = 0; k < 4; k++) ct->pts[i][k] = 0.f;
-    ct->pts[0][0] = q.x; ct->pts[0][1] = q.y; ct->pts[0][2] = q.z; ct->pts[0][3] = -sep;
-    V3 wn = rotate(ident, normal);
-    ct->normal[0] = wn.x; ct->normal[1] = wn.y; ct->normal[2] = wn.z;
-    ct->num_points = 1;
+    for (int i = 0; i < 4; i++) { m.pts[i] = zero; m.depths[i] = 0.f; }
+    m.pts[0] = rotate(ident, contact) + zero;
+    m.depths[0] = -sep;
+    m.n = 1;
+    m.normal = rotate(ident, normal);
+}
+
+// doSATPlane + createFacePlaneContact (narrowphase.cpp:760-788,974-1017) with
+// the hull streamed: separation = min over vertices, incident face = most
+// anti-parallel normal (first strict minimum), contact points = its vertices
+// below the plane, projected onto it.
+MDR_HD bool hullPlaneContact(Manifold &m, const BodyXf &x, const StepParams &p, Plane plane)
+{
+    const ObjDev *o = x.o;
+    const float *src_v = p.a.verts + 3 * MDR_LDG(&o->vert_off);
+    const float *src_p = p.a.planes + 4 * MDR_LDG(&o->face_off);
+    const int nv = MDR_LDG(&o->num_verts), nf = MDR_LDG(&o->num_faces);
+    float mind = FLT_MAX;
+    for (int k = 0; k < nv; k++) {
+        float d = dot(plane.n, worldVert(x, src_v, k));
+        if (d < mind) mind = d;
+    }
+    if (mind - plane.d > 0.0f) return false;
+    float best = FLT_MAX;
+    int inc_face = -1;
+    for (int f = 0; f < nf; f++) {
+        float d = dot(worldNormal(x, src_p, f), plane.n);
+        if (d < best) { best = d; inc_face = f; }
+    }
+    V3 pts[MDR_MAX_POLY];
+    float depths[MDR_MAX_POLY];
+    const HEdgeDev *hes = p.a.hedges + MDR_LDG(&o->hedge_off);
+    uint32_t he = MDR_LDG(p.a.polys + MDR_LDG(&o->face_off) + inc_face), start = he;
+    int n = 0;
+    do {
+        HEdgeDev e = ldHE(hes, he);
+        he = e.next;
+        V3 vv = worldVert(x, src_v, (int)e.root);
+        float d = planeDist(plane, vv);
+        if (d < 0.0f && n < MDR_MAX_POLY) {
+            pts[n] = vv - d * plane.n;
+            depths[n] = -d;
+            n++;
+        }
+    } while (he != start);
+    buildManifold(m, plane.n, pts, depths, n);
+    return true;
+}
+
+// doSAT + generateContacts for two hulls, narrowphase.cpp:678-758,1366-1513.
+// Returns 0 (separated), 1 (contact, a is the reference body) or 2 (b is).
+MDR_HD int hullHullContact(Manifold &m, const BodyXf &xa, const BodyXf &xb, const StepParams &p)
+{
+    V3 va[MDR_MAX_HULL_VERTS], vb[MDR_MAX_HULL_VERTS];
+    Plane pa[MDR_MAX_HULL_FACES], pb[MDR_MAX_HULL_FACES];
+    HullRef ha = makeHull(xa, p, va, pa), hb = makeHull(xb, p, vb, pb);
+    FaceQuery fa = queryFaces(ha, hb);
+    if (fa.sep > 0.0f) return 0;
+    FaceQuery fb = queryFaces(hb, ha);
+    if (fb.sep > 0.0f) return 0;
+    EdgeQuery eq = queryEdges(ha, hb);
+    if (eq.sep > 0.0f) return 0;
+    bool face_a = fa.sep > eq.sep, face_b = fb.sep > eq.sep;
+    if (face_a || face_b) {
+        bool a_ref = fa.sep >= fb.sep;
+        Plane rp = a_ref ? fa.plane : fb.plane;
+        int rf = a_ref ? fa.face : fb.face;
+        if (a_ref) { faceContact(m, rp, rf, incidentFace(hb, rp.n), ha, hb); return 1; }
+        faceContact(m, rp, rf, incidentFace(ha, rp.n), hb, ha);
+        return 2;
+    }
+    edgeContact(m, eq.normal, eq.sep, eq.ea, eq.eb, ha, hb);
+    return 1;
+}
+
+// Hands a manifold to the solver: local arms (getLocalSpaceContacts,
+// physics.cpp:365-382) and pre-solve normal velocities (:902-934) computed once.
+// At this point of the substep pos/rot ARE the pre-solve poses (nothing has
+// moved since substepRigidBodies).
+MDR_HD void emitContact(WorldView &v, const StepParams &p, SolverContact *sc, const Manifold &m,
+                        int ref, int alt)
+{
+    const bool s1 = !(v.meta[ref] & META_DEP), s2 = !(v.meta[alt] & META_DEP);
+    sc->hdr = (uint32_t)ref | ((uint32_t)alt << 10) | ((uint32_t)m.n << 20) |
+              ((uint32_t)s1 << 24) | ((uint32_t)s2 << 25);
+    sc->normal[0] = m.normal.x; sc->normal[1] = m.normal.y; sc->normal[2] = m.normal.z;
+    const V3 x1 = ld3(v.pos, ref), x2 = ld3(v.pos, alt);
+    const Q4 q1 = ld4(v.rot, ref), q2 = ld4(v.rot, alt);
+    const V3 pv1 = ldVelLin(v.prev_vel, ref), po1 = ldVelAng(v.prev_vel, ref);
+    const V3 pv2 = ldVelLin(v.prev_vel, alt), po2 = ldVelAng(v.prev_vel, alt);
+    const V3 zero = mk3(0.f, 0.f, 0.f);
+    for (int i = 0; i < 4; i++) {
+        sc->lambda[i] = 0.f;
+        if (i >= m.n) continue;
+        V3 c1 = m.pts[i];
+        V3 c2 = c1 - m.normal * m.depths[i];
+        V3 r1 = rotate(qinv(q1), c1 - x1);
+        V3 r2 = rotate(qinv(q2), c2 - x2);
+        V3 r1w = rotate(q1, r1), r2w = rotate(q2, r2);
+        // relative pre-solve velocity; a static body's pre-solve velocity is zero
+        V3 va = s1 ? zero : pv1 + cross(po1, r1w);
+        V3 vb = s2 ? zero : pv2 + cross(po2, r2w);
+        sc->vn_bar[i] = dot(m.normal, va - vb);
+        V3 o1 = s1 ? r1w + x1 : r1;
+        V3 o2 = s2 ? r2w + x2 : r2;
+        sc->r1[i][0] = o1.x; sc->r1[i][1] = o1.y; sc->r1[i][2] = o1.z;
+        sc->r2[i][0] = o2.x; sc->r2[i][1] = o2.y; sc->r2[i][2] = o2.z;
+    }
+}
+
+MDR_HD void probeContact(const StepParams &p, int sub, int pi, const Manifold *m, int ref, int alt)
+{
+    if (pi >= p.probe.max_contacts) return;
+    ContactDev o;
+    o.ref = ref; o.ref_pad = 0; o.alt = alt; o.alt_pad = 0;
+    for (int i = 0; i < 4; i++) {
+        const bool on = m && i < m->n;
+        o.pts[i][0] = on ? m->pts[i].x : 0.f; o.pts[i][1] = on ? m->pts[i].y : 0.f;
+        o.pts[i][2] = on ? m->pts[i].z : 0.f; o.pts[i][3] = on ? m->depths[i] : 0.f;
+        o.lambda_n[i] = 0.f;
+    }
+    o.num_points = m ? m->n : 0;
+    o.normal[0] = m ? m->normal.x : 0.f; o.normal[1] = m ? m->normal.y : 0.f; o.normal[2] = m ? m->normal.z : 0.f;
+    p.probe.contacts[(size_t)sub * p.probe.max_contacts + pi] = o;
 }
 
 // runNarrowphase (CPU branch) + narrowphaseDispatch + generateContacts
-// (narrowphase.cpp:1515-1728,1182-1364,1366-1513), doSAT :678-758, doSATPlane
-// :760-788, for pair slot `pi`. A slot without contact gets num_points = 0.
-MDR_HD void narrowphasePair(WorldView &v, const StepParams &p, int pi)
+// (narrowphase.cpp:1515-1728,1182-1364,1366-1513) for pair slot `pi`. A slot
+// without contact gets a zero header.
+MDR_HD void narrowphasePair(WorldView &v, const StepParams &p, int pi, bool probing, int sub)
 {
-    ContactDev *ct = contactSlot(v, pi);
-    ct->num_points = 0;
+    SolverContact *sc = contactSlot(v, pi);
+    sc->hdr = 0;
     const uint32_t pr = v.pairs[pi];
-    int a = pr & 0xffff, b = pr >> 16;
-    int ta = MDR_LDG(&p.a.objs[v.obj[a]].type), tb = MDR_LDG(&p.a.objs[v.obj[b]].type);
-    if ((uint32_t)ta > (uint32_t)tb) { int t = a; a = b; b = t; t = ta; ta = tb; tb = t; }
-    if (!overlaps(ldBox(v.box, a), ldBox(v.box, b))) return;
-    const int test = ta | tb;
-    ct->ref_pad = 0; ct->alt_pad = 0;
-    ct->lambda_n[0] = ct->lambda_n[1] = ct->lambda_n[2] = ct->lambda_n[3] = 0.f;
-    if (test == 2) {
-        HullRef ha = hullRef(v, p, a), hb = hullRef(v, p, b);
-        FaceQuery fa = queryFaces(ha, hb);
-        if (fa.sep > 0.0f) return;
-        FaceQuery fb = queryFaces(hb, ha);
-        if (fb.sep > 0.0f) return;
-        EdgeQuery eq = queryEdges(ha, hb);
-        if (eq.sep > 0.0f) return;
-        bool face_a = fa.sep > eq.sep, face_b = fb.sep > eq.sep;
-        if (face_a || face_b) {
-            bool a_ref = fa.sep >= fb.sep;
-            Plane rp = a_ref ? fa.plane : fb.plane;
-            int rf = a_ref ? fa.face : fb.face;
-            if (a_ref) {
-                faceContact(ct, rp, rf, incidentFace(hb, rp.n), ha, hb);
-                ct->ref = a; ct->alt = b;
-            } else {
-                faceContact(ct, rp, rf, incidentFace(ha, rp.n), hb, ha);
-                ct->ref = b; ct->alt = a;
-            }
-        } else {
-            edgeContact(ct, eq.normal, eq.sep, eq.ea, eq.eb, ha, hb);
-            ct->ref = a; ct->alt = b;
+    int a = pr & 1023, b = (pr >> 10) & 1023;
+    // order by primitive type bits: hull (2) before plane (4)
+    if (!(v.meta[a] & META_HULL) && (v.meta[b] & META_HULL)) { int t = a; a = b; b = t; }
+    const bool a_hull = (v.meta[a] & META_HULL) != 0, b_hull = (v.meta[b] & META_HULL) != 0;
+    Manifold m;
+    int ref = -1, alt = -1;
+    if (overlaps(ldBox(v.box, a), ldBox(v.box, b))) {
+        if (a_hull && b_hull) {
+            int r = hullHullContact(m, bodyXf(v, p, a), bodyXf(v, p, b), p);
+            if (r == 1) { ref = a; alt = b; }
+            else if (r == 2) { ref = b; alt = a; }
+        } else if (a_hull) {
+            Plane plane;
+            plane.n = rotate(ld4(v.rot, b), mk3(0.f, 0.f, 1.f));
+            plane.d = dot(plane.n, ld3(v.pos, b));
+            if (hullPlaneContact(m, bodyXf(v, p, a), p, plane)) { ref = b; alt = a; }
         }
-    } else if (test == 6) {
-        HullRef ha = hullRef(v, p, a);
-        Plane plane;
-        plane.n = rotate(ld4(v.rot, b), mk3(0.f, 0.f, 1.f));
-        plane.d = dot(plane.n, ld3(v.pos, b));
-        float sep = hullDistanceFromPlane(plane, ha);
-        if (sep > 0.0f) return;
-        facePlaneContact(ct, plane, incidentFace(ha, plane.n), ha);
-        ct->ref = b; ct->alt = a;
+        // Other primitive combinations assert in the reference
+        // (narrowphase.cpp:1197-1225,1268-1313): no contact.
     }
-    // Other primitive combinations assert in the reference (narrowphase.cpp:
-    // 1197-1225,1268-1313): no contact.
+    const bool hit = ref >= 0 && m.n > 0;
+    if (hit) emitContact(v, p, sc, m, ref, alt);
+    if (probing) probeContact(p, sub, pi, hit ? &m : nullptr, ref, alt);
+}
+
+// Per body, per substep: world AABB of the object box, the narrowphase's cheap
+// reject (narrowphase.cpp:1583-1596).
+MDR_HD void worldBoxes(const BlockCtx &c, WorldView &v, const StepParams &p)
+{
+    for (int i = c.tid(); i < v.n; i += c.nthreads()) {
+        const ObjDev *o = p.a.objs + (v.meta[i] & 0xffffu);
+        stBox(v.box, i, applyTRS(objAABB(o), ld3(v.pos, i), ld4(v.rot, i), ld3(v.scale, i)));
+    }
 }
 
 }  // namespace mdr

@@ -7,54 +7,49 @@
 
 namespace mdr {
 
-// Copies the contacts of this substep, compacted in pair order, to the probe.
-MDR_HD void probeContacts(const WorldView &v, const StepParams &p, int sub)
+// Steps world `w` in world slot `v`. `group_level` is one int shared by the
+// whole block: the level loops must run the same number of barriers in every
+// world slot, so they run to the block-wide maximum. A slot without a world
+// this round (`!v.active`) walks the same barriers with zero rows.
+MDR_HD void stepWorld(const BlockCtx &c, WorldView &v, const StepParams &p, int w, int *group_level)
 {
-    int out = 0;
-    const int np = v.misc[0];
-    for (int i = 0; i < np; i++) {
-        const ContactDev *ct = contactSlot(v, i);
-        if (ct->num_points <= 0) continue;
-        if (out < p.probe.max_contacts) {
-            ContactDev o = *ct;
-            o.lambda_n[0] = o.lambda_n[1] = o.lambda_n[2] = o.lambda_n[3] = 0.f;
-            p.probe.contacts[(size_t)sub * p.probe.max_contacts + out] = o;
-        }
-        out++;
-    }
-    p.probe.num_contacts[sub] = out;
-}
-
-// Steps world `w`, whose view `v` has been carved for this block.
-MDR_HD void stepWorld(const BlockCtx &c, WorldView &v, const StepParams &p, int w)
-{
-    v.n = p.t.row_count[w];
+    v.n = v.active ? p.t.row_count[w] : 0;
     if (v.n > v.np) v.n = v.np;
-    loadWorld(c, v, p.t, w);
+    if (c.tid() == 0) *group_level = 0;     // every slot writes the same value
+    loadWorld(c, v, p, w);
     c.sync();
     updateLeavesAndRefit(c, v, p);
     c.sync();
     findPairs(c, v, p, w);
+    if (c.tid() == 0 && v.misc[1] > 0) {
+#if defined(__CUDA_ARCH__)
+        atomicMax(group_level, v.misc[1]);
+#else
+        *group_level = v.misc[1];
+#endif
+    }
+    c.sync();
+    const int max_level = *group_level;
+    const bool probing = v.active && p.probe.world == w;
     for (int sub = 0; sub < p.substeps; sub++) {
         substepBodies(c, v, p, w);
         c.sync();
-        transformBodies(c, v, p);
+        worldBoxes(c, v, p);
         c.sync();
         const int np = v.misc[0];
-        for (int i = c.tid(); i < np; i += c.nthreads()) narrowphasePair(v, p, i);
+        for (int i = c.tid(); i < np; i += c.nthreads()) narrowphasePair(v, p, i, probing, sub);
         c.sync();
-        if (p.probe.world == w && c.tid() == 0) probeContacts(v, p, sub);
-        solveLevels<false>(c, v, p);
+        solveLevels<false>(c, v, p, max_level);
         setVelocities(c, v, p);
         c.sync();
-        solveLevels<true>(c, v, p);
+        solveLevels<true>(c, v, p, max_level);
     }
-    if (c.tid() == 0) {
+    if (c.tid() == 0 && v.active) {
         int nc = 0;
-        for (int i = 0; i < v.misc[0]; i++) nc += contactSlot(v, i)->num_points > 0;
+        for (int i = 0; i < v.misc[0]; i++) nc += contactSlot(v, i)->hdr != 0;
         p.world_contacts[w] = nc;
     }
-    updateLeavesAndRefit(c, v, p);
+    updateLeavesAndRefitGlobal(c, v, p, w);
     c.sync();
     storeWorld(c, v, p.t, w);
     c.sync();

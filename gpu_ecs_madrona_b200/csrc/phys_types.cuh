@@ -48,6 +48,22 @@ struct ContactDev {
     float lambda_n[4];
 };
 
+// A contact in the form the solver consumes, produced directly by the
+// narrowphase (the reference's Contact goes to the probe only). Local arms are
+// computed once per substep instead of once per solver pass. For a body that is
+// a stable static (see staticStable) the slot holds the world-space point
+// instead of the local arm: that is all the solver needs of such a body.
+// 36 words: with 16-byte accesses a quarter-warp of consecutive slots is
+// bank-conflict free.
+struct SolverContact {
+    uint32_t hdr;            // ref row | alt row << 10 | points << 20 | s1 << 24 | s2 << 25
+    float normal[3];
+    float lambda[4];
+    float vn_bar[4];
+    float r1[4][3];
+    float r2[4][3];
+};
+
 struct PhysTables {
     float *pos, *rot, *scale, *vel;
     int32_t *obj;
@@ -76,7 +92,8 @@ struct ProbeDev {
     int32_t *num_pairs;           // [1]
     int32_t *pairs;               // [max_pairs][2]
     int32_t *num_contacts;        // [substeps]
-    ContactDev *contacts;         // [substeps][max_contacts]
+    ContactDev *contacts;         // [substeps][max_contacts], indexed by pair slot
+                                  // (num_points 0 where the pair made no contact)
 };
 
 struct StepParams {
@@ -89,7 +106,7 @@ struct StepParams {
     int32_t substeps;
     int32_t max_pairs;            // SMEM pair-list capacity per world
     int32_t smem_contacts;        // contact slots held in SMEM; the rest go to `overflow`
-    ContactDev *overflow;         // [gridDim.x][max_pairs - smem_contacts]
+    SolverContact *overflow;      // [resident world slots][max_pairs - smem_contacts]
     int32_t *world_pairs;         // [W] pairs found in the last step
     int32_t *world_contacts;      // [W] contacts of the last substep
     int32_t *error_flags;         // [1] bit 0: pair list overflow
@@ -97,5 +114,15 @@ struct StepParams {
 };
 
 enum { MDR_ERR_PAIR_OVERFLOW = 1 };
+
+// Compile-time caps of the hull-hull path (per-thread local arrays).
+#ifndef MDR_MAX_HULL_VERTS
+#define MDR_MAX_HULL_VERTS 32
+#endif
+#ifndef MDR_MAX_HULL_FACES
+#define MDR_MAX_HULL_FACES 32
+#endif
+#define MDR_MAX_BODIES 1024      // rows are packed in 10 bits
+#define MDR_MAX_LEVEL 4095
 
 }  // namespace mdr

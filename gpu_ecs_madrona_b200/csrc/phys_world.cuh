@@ -1,8 +1,11 @@
-// One world's rigid-body step, executed by ONE thread block out of shared
+// One world's rigid-body step, executed by a group of threads out of shared
 // memory: the world's rows are staged HBM -> SMEM once, every node of the
 // reference's physics task graph (src/physics/physics.cpp:1142-1205,
 // broadphase.cpp:934-991, narrowphase.cpp:1768-1782) runs out of SMEM with a
 // block barrier where the graph has an edge, and the rows go back once.
+// A thread block steps several worlds side by side (one "world slot" each) in
+// barrier lock-step, so that its warps share instruction fetches: the step is a
+// long instruction stream and the SM's instruction cache is small.
 //
 // What is restructured relative to the reference (results stay bit-identical):
 //  * Broadphase. The reference walks a 4-wide BVH whose boxes only ever grow
@@ -16,97 +19,105 @@
 //    (physics.cpp:650-671,995-1008). Contacts that share no mutable body commute
 //    exactly, so pairs get dependency levels from the reference order once per
 //    step and each level is solved in parallel, one thread per contact.
-//  * Hull transforms (narrowphase.cpp:139-212) are computed once per body per
-//    substep instead of once per pair; same inputs, same bits.
+//  * Stable static bodies (zero inverse mass and inertia, pose a fixed point of
+//    the solver's write-back) contribute exact zeros; their arithmetic is skipped
+//    where the result is provably the same bits (see phys_solver.cuh).
 #pragma once
 #include "phys_types.cuh"
 
 namespace mdr {
 
 // ---------------------------------------------------------------- context ---
-#if defined(__CUDA_ARCH__)
+// The threads that step one world: `nth` threads with index `tid`; sync() is
+// a barrier of the whole block (every world slot of the block takes part).
+#if defined(__CUDACC__)
 struct BlockCtx {
-    __device__ __forceinline__ int tid() const { return threadIdx.x; }
-    __device__ __forceinline__ int nthreads() const { return blockDim.x; }
-    __device__ __forceinline__ void sync() const { __syncthreads(); }
+    int tid_, nth_;
+    __host__ __device__ __forceinline__ int tid() const { return tid_; }
+    __host__ __device__ __forceinline__ int nthreads() const { return nth_; }
+    __host__ __device__ __forceinline__ void sync() const
+    {
+#if defined(__CUDA_ARCH__)
+        __syncthreads();
+#endif
+    }
 };
-#define MDR_LDG(p) __ldg(p)
 #else
-// Host emulation of a 1-thread block (tests/emu only).
+// Host emulation of a 1-thread group (tests/emu only).
 struct BlockCtx {
     int tid() const { return 0; }
     int nthreads() const { return 1; }
     void sync() const {}
 };
+#endif
+#if defined(__CUDA_ARCH__)
+#define MDR_LDG(p) __ldg(p)
+#else
 #define MDR_LDG(p) (*(p))
 #endif
+
+// Per-body flags packed with the object id.
+enum { META_STATIC = 1u << 16, META_DEP = 1u << 17, META_HULL = 1u << 18 };
 
 // SMEM view of one world.
 struct WorldView {
     int n;                 // live rows
     int np;                // row capacity of the arrays below (>= n)
-    float *pos, *rot, *vel, *prev, *prex, *prev_vel, *scale;
-    int32_t *obj;
-    uint32_t *resp;
-    int32_t *ent_id;
+    bool active;           // this slot holds a world in this round
+    float *pos, *rot, *vel, *prev, *prev_vel, *scale;
+    uint32_t *meta;        // object id | META_*
     float *box;            // [np][6] leaf AABBs (broadphase) / world AABBs (narrowphase)
+    uint32_t *pairs;       // [max_pairs] row a | row b << 10 | level << 20
+    int32_t *misc;         // [0] num pairs  [1] max level
+    // --- broadphase scratch, aliased with the contact slots ---
     float *slot;           // [np][6] grow-only slot boxes
-    uint16_t *order;       // [np] leaf at traversal rank r
-    uint16_t *last_level;  // [np]
-    uint8_t *dep;          // [np] body orders the contacts that touch it
+    int32_t *ent_id;       // [np]
     int32_t *cnt;          // [np+1]
     uint32_t *mask;        // [np][mask_words] hit bits in rank order
+    uint16_t *order;       // [np] leaf at traversal rank r
+    uint16_t *last_level;  // [np]
     int mask_words;
-    uint32_t *pairs;       // [max_pairs] a | b << 16 (rows)
-    uint16_t *level;       // [max_pairs]
-    float *hverts;         // [np][hv_stride]
-    float *hplanes;        // [np][hp_stride]
-    int hv_stride, hp_stride;
-    ContactDev *contacts;  // [smem_contacts]
-    ContactDev *overflow;  // this block's global overflow slots
+    // --- substep phase ---
+    SolverContact *contacts;   // [smem_contacts]
+    SolverContact *overflow;   // this slot's global overflow contacts
     int smem_contacts;
-    int32_t *misc;         // [0] num pairs  [1] max level  [2] contacts this substep
 };
 
 MDR_HD size_t alignUp(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
 // Carves the view out of one SMEM (or host) buffer; returns bytes used. With
 // base == nullptr only sizes the buffer.
-MDR_HD size_t carveWorld(WorldView &v, char *base, int np, int max_pairs, int smem_contacts,
-                         int max_verts, int max_faces)
+MDR_HD size_t carveWorld(WorldView &v, char *base, int np, int max_pairs, int smem_contacts)
 {
     size_t off = 0;
 #define MDR_CARVE(field, type, count) \
     off = alignUp(off, 16); v.field = (type *)(base + off); off += sizeof(type) * (size_t)(count);
     v.np = np;
     v.mask_words = (np + 31) / 32;
-    v.hv_stride = (3 * max_verts) | 1;
-    v.hp_stride = (4 * max_faces) | 1;
     v.smem_contacts = smem_contacts;
     MDR_CARVE(rot, float, 4 * np)
-    MDR_CARVE(contacts, ContactDev, smem_contacts)
     MDR_CARVE(pos, float, 3 * np)
     MDR_CARVE(vel, float, 6 * np)
     MDR_CARVE(prev, float, 7 * np)
-    MDR_CARVE(prex, float, 7 * np)
     MDR_CARVE(prev_vel, float, 6 * np)
     MDR_CARVE(scale, float, 3 * np)
-    MDR_CARVE(obj, int32_t, np)
-    MDR_CARVE(resp, uint32_t, np)
-    MDR_CARVE(ent_id, int32_t, np)
+    MDR_CARVE(meta, uint32_t, np)
     MDR_CARVE(box, float, 6 * np)
+    MDR_CARVE(pairs, uint32_t, max_pairs)
+    MDR_CARVE(misc, int32_t, 4)
+    off = alignUp(off, 16);
+    const size_t region = off;
+    MDR_CARVE(contacts, SolverContact, smem_contacts)
+    const size_t end_contacts = off;
+    off = region;
     MDR_CARVE(slot, float, 6 * np)
+    MDR_CARVE(ent_id, int32_t, np)
     MDR_CARVE(cnt, int32_t, np + 1)
     MDR_CARVE(mask, uint32_t, np * v.mask_words)
-    MDR_CARVE(pairs, uint32_t, max_pairs)
-    MDR_CARVE(hverts, float, np * v.hv_stride)
-    MDR_CARVE(hplanes, float, np * v.hp_stride)
-    MDR_CARVE(misc, int32_t, 4)
     MDR_CARVE(order, uint16_t, np)
     MDR_CARVE(last_level, uint16_t, np)
-    MDR_CARVE(level, uint16_t, max_pairs)
-    MDR_CARVE(dep, uint8_t, np)
 #undef MDR_CARVE
+    if (end_contacts > off) off = end_contacts;
     return alignUp(off, 16);
 }
 
@@ -129,7 +140,7 @@ MDR_HD void stBox(float *p, int i, const Box &b)
 // SubstepPrevState / PreSolvePositional: {Vector3, Quat} packed in 28 B.
 MDR_HD V3 ldPoseX(const float *p, int i) { return mk3(p[7 * i], p[7 * i + 1], p[7 * i + 2]); }
 MDR_HD Q4 ldPoseQ(const float *p, int i) { return mk4(p[7 * i + 3], p[7 * i + 4], p[7 * i + 5], p[7 * i + 6]); }
-MDR_HD void stPose(float *p, int i, V3 x, Q4 q)
+MDR_HD void stPose(float *p, size_t i, V3 x, Q4 q)
 {
     p[7 * i] = x.x; p[7 * i + 1] = x.y; p[7 * i + 2] = x.z;
     p[7 * i + 3] = q.w; p[7 * i + 4] = q.x; p[7 * i + 5] = q.y; p[7 * i + 6] = q.z;
@@ -142,73 +153,11 @@ MDR_HD void stVel(float *p, int i, V3 l, V3 a)
     p[6 * i + 3] = a.x; p[6 * i + 4] = a.y; p[6 * i + 5] = a.z;
 }
 
-// Copies `words` 32-bit words between a world tile and SMEM, all threads.
+// Copies `words` 32-bit words between a world tile and SMEM, all threads of the world.
 template <typename T>
 MDR_HD void copyWords(const BlockCtx &c, T *dst, const T *src, int words)
 {
     for (int i = c.tid(); i < words; i += c.nthreads()) dst[i] = src[i];
-}
-
-// ------------------------------------------------------------- load/store ---
-MDR_HD void loadWorld(const BlockCtx &c, WorldView &v, const PhysTables &t, int w)
-{
-    const size_t r0 = (size_t)w * t.stride;
-    const int n = v.n;
-    copyWords(c, v.pos, t.pos + 3 * r0, 3 * n);
-    copyWords(c, v.rot, t.rot + 4 * r0, 4 * n);
-    copyWords(c, v.vel, t.vel + 6 * r0, 6 * n);
-    copyWords(c, v.scale, t.scale + 3 * r0, 3 * n);
-    copyWords(c, v.obj, t.obj + r0, n);
-    copyWords(c, v.resp, t.resp + r0, n);
-    copyWords(c, v.slot, t.slot_box + 6 * r0, 6 * n);
-    for (int i = c.tid(); i < n; i += c.nthreads()) {
-        v.ent_id[i] = t.entity[2 * (r0 + i) + 1];
-        v.order[i] = t.order[r0 + i];
-    }
-}
-
-MDR_HD void storeWorld(const BlockCtx &c, const WorldView &v, const PhysTables &t, int w)
-{
-    const size_t r0 = (size_t)w * t.stride;
-    const int n = v.n;
-    copyWords(c, t.pos + 3 * r0, v.pos, 3 * n);
-    copyWords(c, t.rot + 4 * r0, v.rot, 4 * n);
-    copyWords(c, t.vel + 6 * r0, v.vel, 6 * n);
-    copyWords(c, t.prev + 7 * r0, v.prev, 7 * n);
-    copyWords(c, t.prex + 7 * r0, v.prex, 7 * n);
-    copyWords(c, t.prev_vel + 6 * r0, v.prev_vel, 6 * n);
-    copyWords(c, t.leaf_aabb + 6 * r0, v.box, 6 * n);
-    copyWords(c, t.slot_box + 6 * r0, v.slot, 6 * n);
-}
-
-// ------------------------------------------------------------- broadphase ---
-MDR_HD Box objAABB(const ObjDev *o)
-{
-    Box b;
-    b.lo = mk3(MDR_LDG(&o->aabb[0]), MDR_LDG(&o->aabb[1]), MDR_LDG(&o->aabb[2]));
-    b.hi = mk3(MDR_LDG(&o->aabb[3]), MDR_LDG(&o->aabb[4]), MDR_LDG(&o->aabb[5]));
-    return b;
-}
-
-// updateLeafPositionsEntry -> BVH::updateLeafPosition (broadphase.cpp:858-873,
-// 461-480) followed by refitEntry -> BVH::refitLeaf (:891-895,545-642) reduced
-// to the leaf's own slot box (see the header comment).
-MDR_HD void updateLeavesAndRefit(const BlockCtx &c, WorldView &v, const StepParams &p)
-{
-    for (int i = c.tid(); i < v.n; i += c.nthreads()) {
-        const ObjDev *o = p.a.objs + v.obj[i];
-        Box wb = applyTRS(objAABB(o), ld3(v.pos, i), ld4(v.rot, i), ld3(v.scale, i));
-        Box leaf = expandWithMotion(wb, ldVelLin(v.vel, i), p.vel_expand, p.accel_expand);
-        stBox(v.box, i, leaf);
-        Box s = ldBox(v.slot, i);
-        if (leaf.lo.x < s.lo.x) s.lo.x = leaf.lo.x;
-        if (leaf.lo.y < s.lo.y) s.lo.y = leaf.lo.y;
-        if (leaf.lo.z < s.lo.z) s.lo.z = leaf.lo.z;
-        if (leaf.hi.x > s.hi.x) s.hi.x = leaf.hi.x;
-        if (leaf.hi.y > s.hi.y) s.hi.y = leaf.hi.y;
-        if (leaf.hi.z > s.hi.z) s.hi.z = leaf.hi.z;
-        stBox(v.slot, i, s);
-    }
 }
 
 // A static body whose pose the positional solver's write-back leaves bit-identical
@@ -223,25 +172,113 @@ MDR_HD bool staticStable(V3 x, Q4 q)
     return !neg_zero && qBitsEqual(qnormalize(q), q);
 }
 
-// Exclusive prefix sum of cnt[0..n) in place; cnt[n] = total.
-MDR_HD void blockExclusiveScan(const BlockCtx &c, int32_t *cnt, int n)
+// ------------------------------------------------------------- load/store ---
+MDR_HD void loadWorld(const BlockCtx &c, WorldView &v, const StepParams &p, int w)
+{
+    const PhysTables &t = p.t;
+    const size_t r0 = (size_t)w * t.stride;
+    const int n = v.n;
+    copyWords(c, v.pos, t.pos + 3 * r0, 3 * n);
+    copyWords(c, v.rot, t.rot + 4 * r0, 4 * n);
+    copyWords(c, v.vel, t.vel + 6 * r0, 6 * n);
+    copyWords(c, v.scale, t.scale + 3 * r0, 3 * n);
+    copyWords(c, v.slot, t.slot_box + 6 * r0, 6 * n);
+    for (int i = c.tid(); i < n; i += c.nthreads()) {
+        v.ent_id[i] = t.entity[2 * (r0 + i) + 1];
+        v.order[i] = t.order[r0 + i];
+        const uint32_t obj = (uint32_t)t.obj[r0 + i];
+        uint32_t m = obj & 0xffffu;
+        if (t.resp[r0 + i] == 2u) m |= META_STATIC;
+        if (MDR_LDG(&p.a.objs[obj].type) == 2) m |= META_HULL;
+        v.meta[i] = m;
+    }
+}
+
+MDR_HD void storeWorld(const BlockCtx &c, const WorldView &v, const PhysTables &t, int w)
+{
+    const size_t r0 = (size_t)w * t.stride;
+    const int n = v.n;
+    copyWords(c, t.pos + 3 * r0, v.pos, 3 * n);
+    copyWords(c, t.rot + 4 * r0, v.rot, 4 * n);
+    copyWords(c, t.vel + 6 * r0, v.vel, 6 * n);
+    copyWords(c, t.prev + 7 * r0, v.prev, 7 * n);
+    copyWords(c, t.prev_vel + 6 * r0, v.prev_vel, 6 * n);
+    copyWords(c, t.leaf_aabb + 6 * r0, v.box, 6 * n);
+}
+
+// ------------------------------------------------------------- broadphase ---
+MDR_HD Box objAABB(const ObjDev *o)
+{
+    Box b;
+    b.lo = mk3(MDR_LDG(&o->aabb[0]), MDR_LDG(&o->aabb[1]), MDR_LDG(&o->aabb[2]));
+    b.hi = mk3(MDR_LDG(&o->aabb[3]), MDR_LDG(&o->aabb[4]), MDR_LDG(&o->aabb[5]));
+    return b;
+}
+
+MDR_HD Box growBox(Box s, const Box &leaf)
+{
+    if (leaf.lo.x < s.lo.x) s.lo.x = leaf.lo.x;
+    if (leaf.lo.y < s.lo.y) s.lo.y = leaf.lo.y;
+    if (leaf.lo.z < s.lo.z) s.lo.z = leaf.lo.z;
+    if (leaf.hi.x > s.hi.x) s.hi.x = leaf.hi.x;
+    if (leaf.hi.y > s.hi.y) s.hi.y = leaf.hi.y;
+    if (leaf.hi.z > s.hi.z) s.hi.z = leaf.hi.z;
+    return s;
+}
+
+MDR_HD Box leafBox(const WorldView &v, const StepParams &p, int i)
+{
+    const ObjDev *o = p.a.objs + (v.meta[i] & 0xffffu);
+    Box wb = applyTRS(objAABB(o), ld3(v.pos, i), ld4(v.rot, i), ld3(v.scale, i));
+    return expandWithMotion(wb, ldVelLin(v.vel, i), p.vel_expand, p.accel_expand);
+}
+
+// updateLeafPositionsEntry -> BVH::updateLeafPosition (broadphase.cpp:858-873,
+// 461-480) followed by refitEntry -> BVH::refitLeaf (:891-895,545-642) reduced
+// to the leaf's own slot box (see the header comment). Start-of-step form: the
+// slot boxes are in SMEM for the pair search.
+MDR_HD void updateLeavesAndRefit(const BlockCtx &c, WorldView &v, const StepParams &p)
+{
+    for (int i = c.tid(); i < v.n; i += c.nthreads()) {
+        Box leaf = leafBox(v, p, i);
+        stBox(v.box, i, leaf);
+        stBox(v.slot, i, growBox(ldBox(v.slot, i), leaf));
+    }
+}
+
+// End-of-step form: the SMEM slot boxes have been recycled for contacts, the
+// ones written to HBM after the first refit are grown in place.
+MDR_HD void updateLeavesAndRefitGlobal(const BlockCtx &c, WorldView &v, const StepParams &p, int w)
+{
+    float *gslot = p.t.slot_box + 6 * (size_t)w * p.t.stride;
+    for (int i = c.tid(); i < v.n; i += c.nthreads()) {
+        Box leaf = leafBox(v, p, i);
+        stBox(v.box, i, leaf);
+        stBox(gslot, i, growBox(ldBox(gslot, i), leaf));
+    }
+}
+
+// Exclusive prefix sum of cnt[0..n) in place; cnt[n] = total. Run by the first
+// warp of the world's thread group.
+MDR_HD void groupExclusiveScan(const BlockCtx &c, int32_t *cnt, int n)
 {
 #if defined(__CUDA_ARCH__)
     if (c.tid() < 32) {
+        const int lane = c.tid();
         int carry = 0;
         for (int base = 0; base < n; base += 32) {
-            int i = base + c.tid();
+            int i = base + lane;
             int x = i < n ? cnt[i] : 0;
             int incl = x;
 #pragma unroll
             for (int d = 1; d < 32; d <<= 1) {
                 int y = __shfl_up_sync(0xffffffffu, incl, d);
-                if (c.tid() >= d) incl += y;
+                if (lane >= d) incl += y;
             }
             if (i < n) cnt[i] = carry + incl - x;
             carry += __shfl_sync(0xffffffffu, incl, 31);
         }
-        if (c.tid() == 0) cnt[n] = carry;
+        if (lane == 0) cnt[n] = carry;
     }
 #else
     int carry = 0;
@@ -250,32 +287,44 @@ MDR_HD void blockExclusiveScan(const BlockCtx &c, int32_t *cnt, int n)
 #endif
 }
 
+MDR_HD void raiseError(const StepParams &p, int bit)
+{
+#if defined(__CUDA_ARCH__)
+    atomicOr(p.error_flags, bit);
+#else
+    *p.error_flags |= bit;
+#endif
+}
+
 // findOverlappingEntry + BVH::findOverlaps (broadphase.cpp:897-932,
 // include/madrona/physics.inl:61-100): pairs (a, b) with a's entity id below
 // b's, not both static, a's CURRENT leaf box strictly overlapping b's slot box,
-// ordered by (row a, traversal rank of b). Then dependency levels.
+// ordered by (row a, traversal rank of b). Then dependency levels. The grown
+// slot boxes go back to HBM here (their SMEM is recycled for contacts).
 MDR_HD void findPairs(const BlockCtx &c, WorldView &v, const StepParams &p, int w)
 {
     const int n = v.n;
+    const size_t r0 = (size_t)w * p.t.stride;
     for (int a = c.tid(); a < n; a += c.nthreads()) {
         const Box q = ldBox(v.box, a);
         const int a_id = v.ent_id[a];
-        const bool a_static = v.resp[a] == 2u;
+        const bool a_static = (v.meta[a] & META_STATIC) != 0;
         int count = 0;
         uint32_t word = 0;
         for (int r = 0; r < n; r++) {
             const int b = v.order[r];
-            bool hit = a_id < v.ent_id[b] && !(a_static && v.resp[b] == 2u) &&
+            bool hit = a_id < v.ent_id[b] && !(a_static && (v.meta[b] & META_STATIC)) &&
                        overlaps(q, ldBox(v.slot, b));
             if (hit) { word |= 1u << (r & 31); count++; }
             if ((r & 31) == 31 || r == n - 1) { v.mask[a * v.mask_words + (r >> 5)] = word; word = 0; }
         }
         v.cnt[a] = count;
         v.last_level[a] = 0;
-        v.dep[a] = !(a_static && staticStable(ld3(v.pos, a), ld4(v.rot, a)));
+        if (!(a_static && staticStable(ld3(v.pos, a), ld4(v.rot, a)))) v.meta[a] |= META_DEP;
     }
+    if (v.active) copyWords(c, p.t.slot_box + 6 * r0, v.slot, 6 * n);
     c.sync();
-    blockExclusiveScan(c, v.cnt, n);
+    groupExclusiveScan(c, v.cnt, n);
     c.sync();
     const int total = v.cnt[n];
     for (int a = c.tid(); a < n; a += c.nthreads()) {
@@ -290,7 +339,7 @@ MDR_HD void findPairs(const BlockCtx &c, WorldView &v, const StepParams &p, int 
                 int bit = __builtin_ctz(m);
 #endif
                 m &= m - 1;
-                if (off < p.max_pairs) v.pairs[off] = (uint32_t)a | ((uint32_t)v.order[wd * 32 + bit] << 16);
+                if (off < p.max_pairs) v.pairs[off] = (uint32_t)a | ((uint32_t)v.order[wd * 32 + bit] << 10);
                 off++;
             }
         }
@@ -298,35 +347,32 @@ MDR_HD void findPairs(const BlockCtx &c, WorldView &v, const StepParams &p, int 
     c.sync();
     if (c.tid() == 0) {
         int np = total;
-        if (np > p.max_pairs) {
-            np = p.max_pairs;
-#if defined(__CUDA_ARCH__)
-            atomicOr(p.error_flags, MDR_ERR_PAIR_OVERFLOW);
-#else
-            *p.error_flags |= MDR_ERR_PAIR_OVERFLOW;
-#endif
-        }
+        if (np > p.max_pairs) { np = p.max_pairs; raiseError(p, MDR_ERR_PAIR_OVERFLOW); }
         // Level of a pair = 1 + the latest earlier pair sharing an ordering body.
         int max_level = 0;
         for (int i = 0; i < np; i++) {
             const uint32_t pr = v.pairs[i];
-            const int a = pr & 0xffff, b = pr >> 16;
-            int la = v.dep[a] ? v.last_level[a] : 0;
-            int lb = v.dep[b] ? v.last_level[b] : 0;
+            const int a = pr & 1023, b = (pr >> 10) & 1023;
+            const bool da = (v.meta[a] & META_DEP) != 0, db = (v.meta[b] & META_DEP) != 0;
+            int la = da ? v.last_level[a] : 0;
+            int lb = db ? v.last_level[b] : 0;
             int lv = (la > lb ? la : lb) + 1;
-            if (v.dep[a]) v.last_level[a] = (uint16_t)lv;
-            if (v.dep[b]) v.last_level[b] = (uint16_t)lv;
-            v.level[i] = (uint16_t)lv;
+            if (lv > MDR_MAX_LEVEL) { lv = MDR_MAX_LEVEL; raiseError(p, MDR_ERR_PAIR_OVERFLOW); }
+            if (da) v.last_level[a] = (uint16_t)lv;
+            if (db) v.last_level[b] = (uint16_t)lv;
+            v.pairs[i] = pr | ((uint32_t)lv << 20);
             if (lv > max_level) max_level = lv;
         }
         v.misc[0] = np;
         v.misc[1] = max_level;
-        p.world_pairs[w] = total;
-        if (p.probe.world == w) {
-            *p.probe.num_pairs = total;
-            for (int i = 0; i < np && i < p.probe.max_pairs; i++) {
-                p.probe.pairs[2 * i] = v.pairs[i] & 0xffff;
-                p.probe.pairs[2 * i + 1] = v.pairs[i] >> 16;
+        if (v.active) {
+            p.world_pairs[w] = total;
+            if (p.probe.world == w) {
+                *p.probe.num_pairs = total;
+                for (int i = 0; i < np && i < p.probe.max_pairs; i++) {
+                    p.probe.pairs[2 * i] = v.pairs[i] & 1023;
+                    p.probe.pairs[2 * i + 1] = (v.pairs[i] >> 10) & 1023;
+                }
             }
         }
     }

@@ -30,13 +30,25 @@ extern __shared__ __align__(16) char mdr_smem[];
 
 template <int kMaxThreads, int kMinBlocks>
 __global__ void __launch_bounds__(kMaxThreads, kMinBlocks)
-physStepKernel(const __grid_constant__ StepParams p, int overflow_per_block)
+physStepKernel(const __grid_constant__ StepParams p, int threads_per_world, int slot_bytes,
+               int overflow_per_slot)
 {
+    __shared__ int group_level;
+    const int slots = blockDim.x / threads_per_world;
+    const int slot = threadIdx.x / threads_per_world;
     BlockCtx ctx;
+    ctx.tid_ = threadIdx.x - slot * threads_per_world;
+    ctx.nth_ = threads_per_world;
     WorldView v;
-    carveWorld(v, mdr_smem, p.t.stride, p.max_pairs, p.smem_contacts, p.a.max_verts, p.a.max_faces);
-    v.overflow = p.overflow + (size_t)blockIdx.x * overflow_per_block;
-    for (int w = blockIdx.x; w < p.t.num_worlds; w += gridDim.x) stepWorld(ctx, v, p, w);
+    carveWorld(v, mdr_smem + (size_t)slot * slot_bytes, p.t.stride, p.max_pairs, p.smem_contacts);
+    v.overflow = p.overflow + ((size_t)blockIdx.x * slots + slot) * overflow_per_slot;
+    // Every slot of the block walks the same barriers: the trip count depends on
+    // the block index only; a slot past the last world idles through them.
+    for (int base = blockIdx.x * slots; base < p.t.num_worlds; base += gridDim.x * slots) {
+        const int w = base + slot;
+        v.active = w < p.t.num_worlds;
+        stepWorld(ctx, v, p, v.active ? w : 0, &group_level);
+    }
 }
 
 // One thread per flagged world: current leaf boxes, then the reference's
@@ -59,16 +71,20 @@ __global__ void bvhRebuildKernel(const __grid_constant__ StepParams p)
 }
 
 // -------------------------------------------------------------- host state --
-typedef void (*StepKernel)(const StepParams, int);
+typedef void (*StepKernel)(const StepParams, int, int, int);
+// Compiled register budgets: {max block threads, min resident blocks}.
 struct KernelVariant { int threads, min_blocks; StepKernel fn; };
 static const KernelVariant kVariants[] = {
-    { 32, 16, physStepKernel<32, 16> },
-    { 64, 8, physStepKernel<64, 8> },
-    { 64, 12, physStepKernel<64, 12> },
-    { 96, 6, physStepKernel<96, 6> },
-    { 128, 4, physStepKernel<128, 4> },
-    { 128, 6, physStepKernel<128, 6> },
-    { 256, 2, physStepKernel<256, 2> },
+    { 64, 8, physStepKernel<64, 8> },        // 128 registers
+    { 128, 4, physStepKernel<128, 4> },      // 128
+    { 128, 6, physStepKernel<128, 6> },      // 80
+    { 256, 2, physStepKernel<256, 2> },      // 128
+    { 256, 3, physStepKernel<256, 3> },      // 80
+    { 384, 1, physStepKernel<384, 1> },      // 168
+    { 384, 2, physStepKernel<384, 2> },      // 80
+    { 512, 1, physStepKernel<512, 1> },      // 128
+    { 640, 1, physStepKernel<640, 1> },      // 96
+    { 1024, 1, physStepKernel<1024, 1> },    // 64
 };
 
 struct mdr_phys {
@@ -83,8 +99,9 @@ struct mdr_phys {
     double timed_ms = 0.0;
     int timed_launches = 0;
     StepKernel kernel = nullptr;
-    int threads = 0, blocks = 0, blocks_per_sm = 0, overflow_per_block = 0;
-    size_t smem_bytes = 0;
+    int threads = 0, blocks = 0, blocks_per_sm = 0, overflow_per_slot = 0;
+    int threads_per_world = 0, worlds_per_block = 0;
+    size_t smem_bytes = 0, slot_bytes = 0;
     bool maybe_rebuild = true;
     int32_t *d_err = nullptr;
     ProbeDev d_probe;   // device buffers of the probe
@@ -119,6 +136,23 @@ static void closeTiming(mdr_phys *p)
     p->timing_open = false;
 }
 
+// The device records one contact per PAIR SLOT; the reference's list is the
+// slots that produced a contact, in order.
+static void compactProbeContacts(ContactDev *contacts, int32_t *num_contacts, int substeps, int max_contacts)
+{
+    for (int s = 0; s < substeps; s++) {
+        ContactDev *row = contacts + (size_t)s * max_contacts;
+        int out = 0;
+        for (int i = 0; i < max_contacts; i++) {
+            if (row[i].num_points <= 0) continue;
+            ContactDev c = row[i];
+            row[out++] = c;
+        }
+        for (int i = out; i < max_contacts; i++) memset(&row[i], 0, sizeof(ContactDev));
+        num_contacts[s] = out;
+    }
+}
+
 extern "C" {
 
 const char *mdr_version(void) { return "madrona_b200 0.1 (sm_100a)"; }
@@ -139,7 +173,7 @@ int32_t mdr_phys_create(const mdr_phys_config *cfg, const mdr_object *objs, int3
                         const float *verts, const uint32_t *poly_words, mdr_phys **out)
 {
     if (!cfg || !out || !objs || num_objs <= 0 || cfg->num_worlds <= 0 ||
-        cfg->max_bodies_per_world <= 0 || cfg->max_bodies_per_world > 65535 ||
+        cfg->max_bodies_per_world <= 0 || cfg->max_bodies_per_world > MDR_MAX_BODIES ||
         cfg->num_substeps <= 0 || cfg->max_contacts <= 0 || !(cfg->delta_t > 0.f))
         return MDR_EINVAL;
     if (cfg->gpu_id < 0 || cfg->gpu_id >= mdr_device_count()) return MDR_ENODEVICE;
@@ -185,7 +219,7 @@ int32_t mdr_phys_create(const mdr_phys_config *cfg, const mdr_object *objs, int3
     sp.a.max_verts = p->assets.max_verts;
     sp.a.max_faces = p->assets.max_faces;
     sp.max_pairs = cfg->max_contacts;
-    sp.smem_contacts = cfg->smem_contacts > 0 ? cfg->smem_contacts : 96;
+    sp.smem_contacts = cfg->smem_contacts > 0 ? cfg->smem_contacts : 72;
     if (sp.smem_contacts > sp.max_pairs) sp.smem_contacts = sp.max_pairs;
     sp.world_pairs = p->dalloc<int32_t>(W);
     sp.world_contacts = p->dalloc<int32_t>(W);
@@ -193,32 +227,49 @@ int32_t mdr_phys_create(const mdr_phys_config *cfg, const mdr_object *objs, int3
     sp.error_flags = p->d_err;
     sp.probe.world = -1;
 
-    // Launch geometry: variant by thread count, grid = resident capacity.
-    const int want_threads = cfg->block_threads > 0 ? cfg->block_threads : 64;
-    int want_min_blocks = 0;
-    if (const char *e = getenv("MDR_MIN_BLOCKS")) want_min_blocks = atoi(e);
-    const KernelVariant *var = nullptr;
-    for (const KernelVariant &kv : kVariants) {
-        if (kv.threads != want_threads) continue;
-        if (!var) var = &kv;
-        if (want_min_blocks && kv.min_blocks == want_min_blocks) var = &kv;
-    }
-    if (!var) {
-        fprintf(stderr, "madrona_b200: block_threads must be one of 32, 64, 96, 128, 256\n");
+    // Launch geometry. A block steps `worlds_per_block` worlds side by side with
+    // `threads_per_world` threads each; the grid is the resident capacity of the GPU.
+    auto envInt = [](const char *name, int dflt) {
+        const char *e = getenv(name);
+        return e && *e ? atoi(e) : dflt;
+    };
+    int tpw = envInt("MDR_THREADS_PER_WORLD", cfg->block_threads > 0 ? cfg->block_threads : 64);
+    int wpb = envInt("MDR_WORLDS_PER_BLOCK", cfg->worlds_per_block > 0 ? cfg->worlds_per_block : 4);
+    int want_min_blocks = envInt("MDR_MIN_BLOCKS", 0);
+    if (tpw < 32 || tpw % 32 || wpb < 1 || tpw * wpb > 1024) {
+        fprintf(stderr, "madrona_b200: threads per world must be a multiple of 32 and threads x worlds per block <= 1024\n");
         mdr_phys_destroy(p);
         return MDR_EINVAL;
     }
-    p->kernel = var->fn;
-    p->threads = var->threads;
+    if (wpb > W) wpb = W;
     WorldView v;
-    p->smem_bytes = carveWorld(v, nullptr, stride, sp.max_pairs, sp.smem_contacts,
-                               sp.a.max_verts, sp.a.max_faces);
+    p->slot_bytes = carveWorld(v, nullptr, stride, sp.max_pairs, sp.smem_contacts);
+    p->smem_bytes = p->slot_bytes * wpb;
+    while (wpb > 1 && p->smem_bytes > (size_t)prop.sharedMemPerBlockOptin) {
+        wpb--;
+        p->smem_bytes = p->slot_bytes * wpb;
+    }
     if (p->smem_bytes > (size_t)prop.sharedMemPerBlockOptin) {
         fprintf(stderr, "madrona_b200: one world needs %zu B of shared memory, the device offers %zu B per block\n",
                 p->smem_bytes, (size_t)prop.sharedMemPerBlockOptin);
         mdr_phys_destroy(p);
         return MDR_ECAPACITY;
     }
+    p->threads_per_world = tpw;
+    p->worlds_per_block = wpb;
+    p->threads = tpw * wpb;
+    // How many such blocks fit one SM by shared memory decides the register budget.
+    int fit = (int)((size_t)prop.sharedMemPerMultiprocessor / (p->smem_bytes + 1024));
+    if (fit < 1) fit = 1;
+    const KernelVariant *var = nullptr;
+    for (const KernelVariant &kv : kVariants) {
+        if (kv.threads < p->threads) continue;
+        if (var && kv.threads > var->threads) break;
+        if (!var) var = &kv;
+        if (want_min_blocks ? kv.min_blocks == want_min_blocks : kv.min_blocks <= fit) var = &kv;
+    }
+    if (!var) { mdr_phys_destroy(p); return MDR_EINVAL; }
+    p->kernel = var->fn;
     REQ_CUDA(cudaFuncSetAttribute(p->kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p->smem_bytes));
     REQ_CUDA(cudaFuncSetAttribute(p->kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
     int per_sm = 0;
@@ -226,10 +277,11 @@ int32_t mdr_phys_create(const mdr_phys_config *cfg, const mdr_object *objs, int3
     if (per_sm < 1) per_sm = 1;
     p->blocks_per_sm = per_sm;
     long long grid = (long long)per_sm * prop.multiProcessorCount;
-    if (grid > W) grid = W;
+    const long long need = ((long long)W + wpb - 1) / wpb;
+    if (grid > need) grid = need;
     p->blocks = (int)grid;
-    p->overflow_per_block = sp.max_pairs - sp.smem_contacts;
-    sp.overflow = p->dalloc<ContactDev>((size_t)p->blocks * (p->overflow_per_block + 1), false);
+    p->overflow_per_slot = sp.max_pairs - sp.smem_contacts;
+    sp.overflow = p->dalloc<SolverContact>((size_t)p->blocks * wpb * (p->overflow_per_slot + 1), false);
 
     REQ_CUDA(cudaStreamCreateWithFlags(&p->stream, cudaStreamNonBlocking));
     REQ_CUDA(cudaEventCreate(&p->ev0));
@@ -365,7 +417,8 @@ int32_t mdr_phys_step_async(mdr_phys *p, int32_t num_steps)
     }
     REQ_CUDA(cudaEventRecord(p->ev0, p->stream));
     for (int s = 0; s < num_steps; s++) {
-        p->kernel<<<p->blocks, p->threads, p->smem_bytes, p->stream>>>(p->params, p->overflow_per_block);
+        p->kernel<<<p->blocks, p->threads, p->smem_bytes, p->stream>>>(
+            p->params, p->threads_per_world, (int)p->slot_bytes, p->overflow_per_slot);
     }
     REQ_CUDA(cudaGetLastError());
     REQ_CUDA(cudaEventRecord(p->ev1, p->stream));
@@ -416,15 +469,15 @@ int32_t mdr_phys_probe_step(mdr_phys *p, int32_t world, int32_t max_pairs, int32
         p->probe_pairs_cap = max_pairs;
     }
     d.world = world; d.max_pairs = max_pairs; d.max_contacts = MC;
-    REQ_CUDA(cudaMemset(d.num_contacts, 0, 4 * S));
+    REQ_CUDA(cudaMemset(d.contacts, 0, sizeof(ContactDev) * (size_t)S * MC));
     REQ_CUDA(cudaMemset(d.num_pairs, 0, 4));
     p->params.probe = d;
     int32_t rc = mdr_phys_step(p, 1);
     p->params.probe.world = -1;
     REQ_CUDA(cudaMemcpy(num_pairs, d.num_pairs, 4, cudaMemcpyDeviceToHost));
     REQ_CUDA(cudaMemcpy(pairs, d.pairs, 8 * (size_t)max_pairs, cudaMemcpyDeviceToHost));
-    REQ_CUDA(cudaMemcpy(num_contacts, d.num_contacts, 4 * S, cudaMemcpyDeviceToHost));
     REQ_CUDA(cudaMemcpy(contacts, d.contacts, sizeof(ContactDev) * (size_t)S * MC, cudaMemcpyDeviceToHost));
+    compactProbeContacts((ContactDev *)contacts, num_contacts, S, MC);
     return rc;
 }
 
@@ -465,10 +518,11 @@ int32_t mdr_phys_get_hull(mdr_phys *p, int32_t obj, uint32_t *half_edges, uint32
     return MDR_OK;
 }
 
-int32_t mdr_phys_launch_info(mdr_phys *p, int32_t info[4])
+int32_t mdr_phys_launch_info(mdr_phys *p, int32_t info[6])
 {
     if (!p || !info) return MDR_EINVAL;
     info[0] = p->blocks; info[1] = p->threads; info[2] = (int32_t)p->smem_bytes; info[3] = p->blocks_per_sm;
+    info[4] = p->threads_per_world; info[5] = p->worlds_per_block;
     return MDR_OK;
 }
 

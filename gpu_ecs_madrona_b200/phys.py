@@ -41,7 +41,7 @@ class MdrPhysConfig(C.Structure):
                 ("num_substeps", C.c_int32), ("max_contacts", C.c_int32),
                 ("delta_t", C.c_float), ("gravity", C.c_float * 3),
                 ("gpu_id", C.c_int32), ("block_threads", C.c_int32),
-                ("smem_contacts", C.c_int32)]
+                ("smem_contacts", C.c_int32), ("worlds_per_block", C.c_int32)]
 
 
 CONTACT_DTYPE = np.dtype([("ref_row", "<i4"), ("ref_pad", "<i4"), ("alt_row", "<i4"),
@@ -134,13 +134,13 @@ def pack_objects(objects):
 class PhysExecutor:
     """Batched rigid-body worlds on one GPU. ``scene`` is a ``scenes.Scene``."""
 
-    def __init__(self, scene, gpu_id=0, block_threads=0, smem_contacts=0, lib=None):
+    def __init__(self, scene, gpu_id=0, block_threads=0, smem_contacts=0, worlds_per_block=0, lib=None):
         self.lib = lib if lib is not None else load_library()
         self.scene = scene
         self.W, self.N = scene.num_worlds, scene.bodies_per_world
         cfg = MdrPhysConfig(scene.num_worlds, scene.bodies_per_world, scene.num_substeps,
                             scene.max_contacts, scene.delta_t, (C.c_float * 3)(*scene.gravity),
-                            gpu_id, block_threads, smem_contacts)
+                            gpu_id, block_threads, smem_contacts, worlds_per_block)
         objs, verts, words = pack_objects(scene.objects)
         h = C.c_void_p()
         rc = self.lib.mdr_phys_create(C.byref(cfg), objs, len(scene.objects),
@@ -280,10 +280,11 @@ class PhysExecutor:
         self._check(self.lib.mdr_phys_read_column_raw_async(self.h, col, arr.ctypes.data), "read_raw")
 
     def launch_info(self):
-        info = np.zeros(4, np.int32)
+        info = np.zeros(6, np.int32)
         self._check(self.lib.mdr_phys_launch_info(self.h, info.ctypes.data), "launch_info")
         return dict(blocks=int(info[0]), threads=int(info[1]), smem_bytes=int(info[2]),
-                    blocks_per_sm=int(info[3]))
+                    blocks_per_sm=int(info[3]), threads_per_world=int(info[4]),
+                    worlds_per_block=int(info[5]))
 
     def kernel_ms(self):
         n = C.c_int32(0)

@@ -63,8 +63,9 @@ typedef struct mdr_phys_config {
     float delta_t;
     float gravity[3];
     int32_t gpu_id;
-    int32_t block_threads;          /* 0: default                                 */
+    int32_t block_threads;          /* threads stepping one world; 0: default     */
     int32_t smem_contacts;          /* contact slots kept in shared memory; 0: default */
+    int32_t worlds_per_block;       /* worlds stepped side by side by one block; 0: default */
 } mdr_phys_config;
 
 /* Columns of the rigid-body archetype: 0 = Entity, 1..12 = phys::Cols
@@ -151,9 +152,10 @@ int32_t mdr_phys_read_bvh(mdr_phys *p, float *slot_boxes, float *leaf_aabbs, uin
  * 54-146): counts[4] = half-edges, edges, faces, vertices. */
 int32_t mdr_phys_get_hull(mdr_phys *p, int32_t obj, uint32_t *half_edges, uint32_t *edges,
                           uint32_t *polys, float *planes, int32_t *counts);
-/* Launch geometry chosen at creation: [0] blocks, [1] threads, [2] dynamic
- * shared memory bytes per block, [3] resident blocks per SM. */
-int32_t mdr_phys_launch_info(mdr_phys *p, int32_t info[4]);
+/* Launch geometry chosen at creation: [0] blocks, [1] threads per block,
+ * [2] dynamic shared memory bytes per block, [3] resident blocks per SM,
+ * [4] threads per world, [5] worlds per block. */
+int32_t mdr_phys_launch_info(mdr_phys *p, int32_t info[6]);
 /* Average device time of the step kernel, in ms, over the launches since the
  * last call (CUDA events on the executor's stream); <0 if none were timed. */
 float mdr_phys_kernel_ms(mdr_phys *p, int32_t *launches);

@@ -23,7 +23,7 @@ struct mdr_phys {
     HostAssets assets;
     StepParams params;
     std::vector<char> smem;
-    std::vector<ContactDev> overflow;
+    std::vector<SolverContact> overflow;
     std::vector<void *> allocs;
     int32_t err = 0;
     int stride = 0;
@@ -45,7 +45,7 @@ int32_t mdr_phys_create(const mdr_phys_config *cfg, const mdr_object *objs, int3
                         const float *verts, const uint32_t *poly_words, mdr_phys **out)
 {
     if (!cfg || !out || cfg->num_worlds <= 0 || cfg->max_bodies_per_world <= 0 ||
-        cfg->max_bodies_per_world > 65535 || cfg->num_substeps <= 0 || cfg->max_contacts <= 0)
+        cfg->max_bodies_per_world > MDR_MAX_BODIES || cfg->num_substeps <= 0 || cfg->max_contacts <= 0)
         return MDR_EINVAL;
     mdr_phys *p = new mdr_phys;
     p->cfg = *cfg;
@@ -85,8 +85,7 @@ int32_t mdr_phys_create(const mdr_phys_config *cfg, const mdr_object *objs, int3
     sp.error_flags = &p->err;
     sp.probe.world = -1;
     WorldView v;
-    size_t bytes = carveWorld(v, nullptr, stride, sp.max_pairs, sp.smem_contacts,
-                              sp.a.max_verts, sp.a.max_faces);
+    size_t bytes = carveWorld(v, nullptr, stride, sp.max_pairs, sp.smem_contacts);
     p->smem.resize(bytes + 16);
     *out = p;
     return MDR_OK;
@@ -168,9 +167,11 @@ static void stepAll(mdr_phys *p)
     BlockCtx ctx;
     for (int w = 0; w < sp.t.num_worlds; w++) {
         WorldView v;
-        carveWorld(v, base, p->stride, sp.max_pairs, sp.smem_contacts, sp.a.max_verts, sp.a.max_faces);
+        carveWorld(v, base, p->stride, sp.max_pairs, sp.smem_contacts);
         v.overflow = sp.overflow;
-        stepWorld(ctx, v, sp, w);
+        v.active = true;
+        int group_level = 0;
+        stepWorld(ctx, v, sp, w, &group_level);
     }
 }
 
@@ -190,8 +191,20 @@ int32_t mdr_phys_probe_step(mdr_phys *p, int32_t world, int32_t max_pairs, int32
     pr.world = world; pr.max_pairs = max_pairs; pr.max_contacts = p->cfg.max_contacts;
     pr.num_pairs = num_pairs; pr.pairs = pairs; pr.num_contacts = num_contacts;
     pr.contacts = (ContactDev *)contacts;
+    memset(contacts, 0, sizeof(ContactDev) * (size_t)p->cfg.num_substeps * p->cfg.max_contacts);
     int32_t rc = mdr_phys_step(p, 1);
     pr.world = -1;
+    for (int s = 0; s < p->cfg.num_substeps; s++) {
+        ContactDev *row = (ContactDev *)contacts + (size_t)s * p->cfg.max_contacts;
+        int out = 0;
+        for (int i = 0; i < p->cfg.max_contacts; i++) {
+            if (row[i].num_points <= 0) continue;
+            ContactDev c = row[i];
+            row[out++] = c;
+        }
+        for (int i = out; i < p->cfg.max_contacts; i++) memset(&row[i], 0, sizeof(ContactDev));
+        num_contacts[s] = out;
+    }
     return rc;
 }
 
