@@ -271,9 +271,27 @@ MDR_HD void buildManifold(Manifold &m, V3 n, V3 *contacts, float *depths, int nu
     m.normal = rotate(ident, n);
 }
 
+// Where contact generation takes hull vertices from: the per-thread arrays of
+// the serial path, or recomputed from the body transform (same bits) on the
+// warp-cooperative path, which keeps no per-thread copy of the hull.
+struct ArrayVerts {
+    const V3 *v;
+    MDR_HD V3 at(int k) const { return v[k]; }
+};
+struct XfVerts {
+    BodyXf x;
+    const float *src;
+    MDR_HD V3 at(int k) const { return worldVert(x, src, k); }
+};
+struct HullTopo {
+    const HEdgeDev *he;
+    const uint32_t *polys;
+};
+
 // createFaceContact, narrowphase.cpp:866-972
+template <typename VR, typename VO>
 MDR_HD void faceContact(Manifold &m, Plane ref_plane, int ref_face, int inc_face,
-                        const HullRef &ref, const HullRef &other)
+                        const HullTopo &ref, const VR &ref_v, const HullTopo &other, const VO &other_v)
 {
     V3 buf_a[MDR_MAX_POLY], buf_b[MDR_MAX_POLY];
     V3 *in = buf_a, *dst = buf_b;
@@ -281,16 +299,16 @@ MDR_HD void faceContact(Manifold &m, Plane ref_plane, int ref_face, int inc_face
     {
         uint32_t he = MDR_LDG(other.polys + inc_face), start = he;
         do {
-            HEdgeDev e = ldHE(other, he);
+            HEdgeDev e = ldHE(other.he, he);
             he = e.next;
-            if (n < MDR_MAX_POLY) in[n++] = hv(other, e.root);
+            if (n < MDR_MAX_POLY) in[n++] = other_v.at((int)e.root);
         } while (he != start);
     }
     uint32_t he = MDR_LDG(ref.polys + ref_face), start = he;
-    V3 cur = hv(ref, MDR_LDG(&ref.he[he].root));
+    V3 cur = ref_v.at((int)MDR_LDG(&ref.he[he].root));
     do {
         he = MDR_LDG(&ref.he[he].next);
-        V3 next = hv(ref, MDR_LDG(&ref.he[he].root));
+        V3 next = ref_v.at((int)MDR_LDG(&ref.he[he].root));
         V3 edge = next - cur;
         Plane cp;
         cp.n = cross(edge, ref_plane.n);
@@ -315,11 +333,12 @@ MDR_HD void faceContact(Manifold &m, Plane ref_plane, int ref_face, int inc_face
 }
 
 // shortestSegmentBetween + createEdgeContact, narrowphase.cpp:1020-1121
+template <typename VA, typename VB>
 MDR_HD void edgeContact(Manifold &m, V3 normal, float sep, int ea, int eb,
-                        const HullRef &a, const HullRef &b)
+                        const HullTopo &a, const VA &a_v, const HullTopo &b, const VB &b_v)
 {
-    V3 a1 = hv(a, MDR_LDG(&a.he[ea].root)), a2 = hv(a, MDR_LDG(&a.he[MDR_LDG(&a.he[ea].next)].root));
-    V3 b1 = hv(b, MDR_LDG(&b.he[eb].root)), b2 = hv(b, MDR_LDG(&b.he[MDR_LDG(&b.he[eb].next)].root));
+    V3 a1 = a_v.at((int)MDR_LDG(&a.he[ea].root)), a2 = a_v.at((int)MDR_LDG(&a.he[MDR_LDG(&a.he[ea].next)].root));
+    V3 b1 = b_v.at((int)MDR_LDG(&b.he[eb].root)), b2 = b_v.at((int)MDR_LDG(&b.he[MDR_LDG(&b.he[eb].next)].root));
     V3 v1 = a2 - a1, v2 = b2 - b1, v21 = b1 - a1;
     float d22 = dot(v2, v2), d11 = dot(v1, v1), d21 = dot(v2, v1);
     float d211 = dot(v21, v1), d212 = dot(v21, v2);
@@ -398,11 +417,21 @@ MDR_HD int hullHullContact(Manifold &m, const BodyXf &xa, const BodyXf &xb, cons
         bool a_ref = fa.sep >= fb.sep;
         Plane rp = a_ref ? fa.plane : fb.plane;
         int rf = a_ref ? fa.face : fb.face;
-        if (a_ref) { faceContact(m, rp, rf, incidentFace(hb, rp.n), ha, hb); return 1; }
-        faceContact(m, rp, rf, incidentFace(ha, rp.n), hb, ha);
+        HullTopo ta, tb;
+        ta.he = ha.he; ta.polys = ha.polys; tb.he = hb.he; tb.polys = hb.polys;
+        ArrayVerts ava, avb;
+        ava.v = va; avb.v = vb;
+        if (a_ref) { faceContact(m, rp, rf, incidentFace(hb, rp.n), ta, ava, tb, avb); return 1; }
+        faceContact(m, rp, rf, incidentFace(ha, rp.n), tb, avb, ta, ava);
         return 2;
     }
-    edgeContact(m, eq.normal, eq.sep, eq.ea, eq.eb, ha, hb);
+    {
+        HullTopo ta, tb;
+        ta.he = ha.he; ta.polys = ha.polys; tb.he = hb.he; tb.polys = hb.polys;
+        ArrayVerts ava, avb;
+        ava.v = va; avb.v = vb;
+        edgeContact(m, eq.normal, eq.sep, eq.ea, eq.eb, ta, ava, tb, avb);
+    }
     return 1;
 }
 

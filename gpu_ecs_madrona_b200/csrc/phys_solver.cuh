@@ -106,11 +106,14 @@ MDR_HD float generalizedInvMass(const BodyMass &m, V3 ta, V3 &ra)
 MDR_HD V3 ldArm(const float (*r)[3], int i) { return mk3(r[i][0], r[i][1], r[i][2]); }
 
 // handleContact + handleContactConstraint, physics.cpp:281-363,387-476.
-MDR_HD void solveContactPositions(WorldView &v, const StepParams &p, SolverContact *ct)
+// kS1 / kS2: body 1 / body 2 is a stable static (compile-time specialization:
+// the skipped arithmetic must not even be issued).
+template <bool kS1, bool kS2>
+MDR_HD void solveContactPositionsT(WorldView &v, const StepParams &p, SolverContact *ct)
 {
     const uint32_t hdr = ct->hdr;
     const int a = hdr & 1023, b = (hdr >> 10) & 1023, npts = (hdr >> 20) & 7;
-    const bool s1 = (hdr >> 24) & 1, s2 = (hdr >> 25) & 1;
+    constexpr bool s1 = kS1, s2 = kS2;
     const V3 nrm = mk3(ct->normal[0], ct->normal[1], ct->normal[2]);
     const V3 zero = mk3(0.f, 0.f, 0.f);
     V3 x1 = ld3(v.pos, a), x2 = ld3(v.pos, b);
@@ -160,8 +163,16 @@ MDR_HD void solveContactPositions(WorldView &v, const StepParams &p, SolverConta
     }
     // Written back unless the body does not order contacts (stable static:
     // unchanged, and possibly shared by other contacts of this level).
-    if (v.meta[a] & META_DEP) { st3(v.pos, a, x1); st4(v.rot, a, q1); }
-    if (v.meta[b] & META_DEP) { st3(v.pos, b, x2); st4(v.rot, b, q2); }
+    if (!s1) { st3(v.pos, a, x1); st4(v.rot, a, q1); }
+    if (!s2) { st3(v.pos, b, x2); st4(v.rot, b, q2); }
+}
+
+MDR_HD void solveContactPositions(WorldView &v, const StepParams &p, SolverContact *ct)
+{
+    const uint32_t hdr = ct->hdr;
+    if ((hdr >> 24) & 1) solveContactPositionsT<true, false>(v, p, ct);
+    else if ((hdr >> 25) & 1) solveContactPositionsT<false, true>(v, p, ct);
+    else solveContactPositionsT<false, false>(v, p, ct);
 }
 
 // solver::setVelocities, physics.cpp:673-714
@@ -192,21 +203,23 @@ MDR_HD void applyVelSide(V3 &vl, V3 &om, Q4 q, V3 ra, float inv_m, V3 dv, float 
 
 // Relative velocity of the two contact points (physics.cpp:716-728); a stable
 // static body's term is the zero vector.
-MDR_HD V3 relVelAt(bool s1, bool s2, V3 v1, V3 o1, V3 r1w, V3 v2, V3 o2, V3 r2w)
+template <bool kS1, bool kS2>
+MDR_HD V3 relVelAt(V3 v1, V3 o1, V3 r1w, V3 v2, V3 o2, V3 r2w)
 {
-    const V3 zero = mk3(0.f, 0.f, 0.f);
-    V3 va = s1 ? zero : v1 + cross(o1, r1w);
-    V3 vb = s2 ? zero : v2 + cross(o2, r2w);
+    V3 va = mk3(0.f, 0.f, 0.f), vb = mk3(0.f, 0.f, 0.f);
+    if (!kS1) va = v1 + cross(o1, r1w);
+    if (!kS2) vb = v2 + cross(o2, r2w);
     return va - vb;
 }
 
 // solveVelocitiesForContact, physics.cpp:865-993 (+ :752-863).
-MDR_HD void solveContactVelocities(WorldView &v, const StepParams &p, const SolverContact *ct)
+template <bool kS1, bool kS2>
+MDR_HD void solveContactVelocitiesT(WorldView &v, const StepParams &p, const SolverContact *ct)
 {
     const float h = p.h;
     const uint32_t hdr = ct->hdr;
     const int a = hdr & 1023, b = (hdr >> 10) & 1023, npts = (hdr >> 20) & 7;
-    const bool s1 = (hdr >> 24) & 1, s2 = (hdr >> 25) & 1;
+    constexpr bool s1 = kS1, s2 = kS2;
     const V3 nrm = mk3(ct->normal[0], ct->normal[1], ct->normal[2]);
     const V3 zero = mk3(0.f, 0.f, 0.f);
     V3 v1 = ldVelLin(v.vel, a), o1 = ldVelAng(v.vel, a);
@@ -225,7 +238,7 @@ MDR_HD void solveContactVelocities(WorldView &v, const StepParams &p, const Solv
             V3 r1w = zero, r2w = zero;
             if (!s1) r1w = rotate(q1, r1);
             if (!s2) r2w = rotate(q2, r2);
-            V3 vr = relVelAt(s1, s2, v1, o1, r1w, v2, o2, r2w);
+            V3 vr = relVelAt<kS1, kS2>(v1, o1, r1w, v2, o2, r2w);
             float vn = dot(nrm, vr);
             V3 dir, ta1 = zero, ta2 = zero;
             float mag;
@@ -256,8 +269,16 @@ MDR_HD void solveContactVelocities(WorldView &v, const StepParams &p, const Solv
             if (!s2) applyVelSide<-1>(v2, o2, q2, ra2, m2.inv_m, dir, mag);
         }
     }
-    if (v.meta[a] & META_DEP) stVel(v.vel, a, v1, o1);
-    if (v.meta[b] & META_DEP) stVel(v.vel, b, v2, o2);
+    if (!s1) stVel(v.vel, a, v1, o1);
+    if (!s2) stVel(v.vel, b, v2, o2);
+}
+
+MDR_HD void solveContactVelocities(WorldView &v, const StepParams &p, const SolverContact *ct)
+{
+    const uint32_t hdr = ct->hdr;
+    if ((hdr >> 24) & 1) solveContactVelocitiesT<true, false>(v, p, ct);
+    else if ((hdr >> 25) & 1) solveContactVelocitiesT<false, true>(v, p, ct);
+    else solveContactVelocitiesT<false, false>(v, p, ct);
 }
 
 // One Gauss-Seidel sweep in the reference's contact order: level by level,

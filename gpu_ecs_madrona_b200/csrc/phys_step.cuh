@@ -15,13 +15,14 @@ MDR_HD void stepWorld(const BlockCtx &c, WorldView &v, const StepParams &p, int 
 {
     v.n = v.active ? p.t.row_count[w] : 0;
     if (v.n > v.np) v.n = v.np;
+    c.syncBlock();                           // world slots re-align once per step
     if (c.tid() == 0) *group_level = 0;     // every slot writes the same value
     loadWorld(c, v, p, w);
     c.sync();
     updateLeavesAndRefit(c, v, p);
     c.sync();
     findPairs(c, v, p, w);
-    if (c.tid() == 0 && v.misc[1] > 0) {
+    if (c.lockstep() && c.tid() == 0 && v.misc[1] > 0) {
 #if defined(__CUDA_ARCH__)
         atomicMax(group_level, v.misc[1]);
 #else
@@ -29,7 +30,7 @@ MDR_HD void stepWorld(const BlockCtx &c, WorldView &v, const StepParams &p, int 
 #endif
     }
     c.sync();
-    const int max_level = *group_level;
+    const int max_level = c.lockstep() ? *group_level : v.misc[1];
     const bool probing = v.active && p.probe.world == w;
     for (int sub = 0; sub < p.substeps; sub++) {
         substepBodies(c, v, p, w);

@@ -33,9 +33,19 @@ namespace mdr {
 #if defined(__CUDACC__)
 struct BlockCtx {
     int tid_, nth_;
+    int bar_;     // 0: barriers are block-wide (world slots in lock-step); else this slot's named barrier
     __host__ __device__ __forceinline__ int tid() const { return tid_; }
     __host__ __device__ __forceinline__ int nthreads() const { return nth_; }
+    __host__ __device__ __forceinline__ bool lockstep() const { return bar_ == 0; }
     __host__ __device__ __forceinline__ void sync() const
+    {
+#if defined(__CUDA_ARCH__)
+        if (bar_ == 0) __syncthreads();
+        else asm volatile("bar.sync %0, %1;" ::"r"(bar_), "r"(nth_) : "memory");
+#endif
+    }
+    // barrier of the whole block regardless of the mode
+    __host__ __device__ __forceinline__ void syncBlock() const
     {
 #if defined(__CUDA_ARCH__)
         __syncthreads();
@@ -47,7 +57,9 @@ struct BlockCtx {
 struct BlockCtx {
     int tid() const { return 0; }
     int nthreads() const { return 1; }
+    bool lockstep() const { return true; }
     void sync() const {}
+    void syncBlock() const {}
 };
 #endif
 #if defined(__CUDA_ARCH__)

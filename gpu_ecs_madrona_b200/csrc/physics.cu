@@ -31,7 +31,7 @@ extern __shared__ __align__(16) char mdr_smem[];
 template <int kMaxThreads, int kMinBlocks>
 __global__ void __launch_bounds__(kMaxThreads, kMinBlocks)
 physStepKernel(const __grid_constant__ StepParams p, int threads_per_world, int slot_bytes,
-               int overflow_per_slot)
+               int overflow_per_slot, int lockstep)
 {
     __shared__ int group_level;
     const int slots = blockDim.x / threads_per_world;
@@ -39,6 +39,7 @@ physStepKernel(const __grid_constant__ StepParams p, int threads_per_world, int 
     BlockCtx ctx;
     ctx.tid_ = threadIdx.x - slot * threads_per_world;
     ctx.nth_ = threads_per_world;
+    ctx.bar_ = lockstep ? 0 : slot + 1;
     WorldView v;
     carveWorld(v, mdr_smem + (size_t)slot * slot_bytes, p.t.stride, p.max_pairs, p.smem_contacts);
     v.overflow = p.overflow + ((size_t)blockIdx.x * slots + slot) * overflow_per_slot;
@@ -71,7 +72,7 @@ __global__ void bvhRebuildKernel(const __grid_constant__ StepParams p)
 }
 
 // -------------------------------------------------------------- host state --
-typedef void (*StepKernel)(const StepParams, int, int, int);
+typedef void (*StepKernel)(const StepParams, int, int, int, int);
 // Compiled register budgets: {max block threads, min resident blocks}.
 struct KernelVariant { int threads, min_blocks; StepKernel fn; };
 static const KernelVariant kVariants[] = {
@@ -100,7 +101,7 @@ struct mdr_phys {
     int timed_launches = 0;
     StepKernel kernel = nullptr;
     int threads = 0, blocks = 0, blocks_per_sm = 0, overflow_per_slot = 0;
-    int threads_per_world = 0, worlds_per_block = 0;
+    int threads_per_world = 0, worlds_per_block = 0, lockstep = 1;
     size_t smem_bytes = 0, slot_bytes = 0;
     bool maybe_rebuild = true;
     int32_t *d_err = nullptr;
@@ -236,6 +237,8 @@ int32_t mdr_phys_create(const mdr_phys_config *cfg, const mdr_object *objs, int3
     int tpw = envInt("MDR_THREADS_PER_WORLD", cfg->block_threads > 0 ? cfg->block_threads : 64);
     int wpb = envInt("MDR_WORLDS_PER_BLOCK", cfg->worlds_per_block > 0 ? cfg->worlds_per_block : 4);
     int want_min_blocks = envInt("MDR_MIN_BLOCKS", 0);
+    p->lockstep = envInt("MDR_LOCKSTEP", 1);
+    if (!p->lockstep && wpb > 15) wpb = 15;     // one named barrier per world slot
     if (tpw < 32 || tpw % 32 || wpb < 1 || tpw * wpb > 1024) {
         fprintf(stderr, "madrona_b200: threads per world must be a multiple of 32 and threads x worlds per block <= 1024\n");
         mdr_phys_destroy(p);
@@ -418,7 +421,7 @@ int32_t mdr_phys_step_async(mdr_phys *p, int32_t num_steps)
     REQ_CUDA(cudaEventRecord(p->ev0, p->stream));
     for (int s = 0; s < num_steps; s++) {
         p->kernel<<<p->blocks, p->threads, p->smem_bytes, p->stream>>>(
-            p->params, p->threads_per_world, (int)p->slot_bytes, p->overflow_per_slot);
+            p->params, p->threads_per_world, (int)p->slot_bytes, p->overflow_per_slot, p->lockstep);
     }
     REQ_CUDA(cudaGetLastError());
     REQ_CUDA(cudaEventRecord(p->ev1, p->stream));
