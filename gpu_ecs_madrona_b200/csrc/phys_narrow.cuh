@@ -502,6 +502,15 @@ MDR_HD void narrowphasePair(WorldView &v, const StepParams &p, int pi, bool prob
     int ref = -1, alt = -1;
     if (overlaps(ldBox(v.box, a), ldBox(v.box, b))) {
         if (a_hull && b_hull) {
+#if defined(__CUDA_ARCH__)
+            // hand the pair to a whole warp (phys_sat_warp.cuh); the serial
+            // path below only takes what does not fit the queue
+            const int k = atomicAdd(&v.misc[2], 1);
+            if (k < MDR_SAT_QUEUE) {
+                v.sat_queue[k] = (uint16_t)pi;
+                return;
+            }
+#endif
             int r = hullHullContact(m, bodyXf(v, p, a), bodyXf(v, p, b), p);
             if (r == 1) { ref = a; alt = b; }
             else if (r == 2) { ref = b; alt = a; }
@@ -527,6 +536,7 @@ MDR_HD void worldBoxes(const BlockCtx &c, WorldView &v, const StepParams &p)
         const ObjDev *o = p.a.objs + (v.meta[i] & 0xffffu);
         stBox(v.box, i, applyTRS(objAABB(o), ld3(v.pos, i), ld4(v.rot, i), ld3(v.scale, i)));
     }
+    if (c.tid() == 0) v.misc[2] = 0;
 }
 
 }  // namespace mdr

@@ -1,0 +1,197 @@
+// Warp-cooperative hull-hull SAT (device only). The thread-per-pair narrowphase
+// queues the hull-hull pairs that pass the AABB reject; here one warp takes one
+// queued pair: lane k holds world vertex k and world face plane k of both hulls
+// (MDR_MAX_HULL_VERTS / FACES = 32), face queries run one face per lane, the
+// edge-edge query one edge pair per lane, and warp arg-max reductions pick the
+// same winner as the reference's sequential scans (first strict maximum =
+// largest value, lowest index; src/physics/narrowphase.cpp:352-378,474-576).
+// The reference's early-outs only ever trigger on a positive separation, whose
+// outcome (no contact) does not depend on which axis found it. Contact
+// generation for the surviving pair is done by lane 0 with the serial code.
+#pragma once
+#include "phys_narrow.cuh"
+
+#if defined(__CUDACC__)
+namespace mdr {
+
+#define MDR_FULL 0xffffffffu
+
+__device__ __forceinline__ V3 shfl3(V3 v, int src)
+{
+    return mk3(__shfl_sync(MDR_FULL, v.x, src), __shfl_sync(MDR_FULL, v.y, src),
+               __shfl_sync(MDR_FULL, v.z, src));
+}
+
+// Arg-max over the warp: largest value, lowest index on ties. All lanes get it.
+__device__ __forceinline__ void warpArgMax(float &val, int &idx)
+{
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) {
+        float ov = __shfl_xor_sync(MDR_FULL, val, d);
+        int oi = __shfl_xor_sync(MDR_FULL, idx, d);
+        if (ov > val || (ov == val && oi < idx)) { val = ov; idx = oi; }
+    }
+}
+
+// One lane per face of `a`: distance of the other hull (vertices in `vb`, one
+// per lane, nvb of them) from the face plane held by this lane.
+__device__ __forceinline__ float faceSeparationLane(Plane pl, bool lane_has_face, V3 vb, int nvb)
+{
+    float m = FLT_MAX;
+    for (int k = 0; k < nvb; k++) {
+        float d = dot(pl.n, shfl3(vb, k));
+        if (d < m) m = d;
+    }
+    return lane_has_face ? m - pl.d : -FLT_MAX;
+}
+
+// Edge-edge query, one (edge of a, edge of b) pair per lane and round
+// (queryEdgeDirections CPU branch, narrowphase.cpp:474-576; buildsMinkowskiFace
+// :418-426; edgeDistance :433-472). Returns the warp-wide winner.
+struct EdgeWin { float sep; V3 normal; int ea, eb; };
+
+__device__ __forceinline__ EdgeWin edgeQueryWarp(int lane, V3 va, Plane pa, const HEdgeDev *hea_tab,
+                                                 const uint32_t *edges_a, int nea, V3 centre_a,
+                                                 V3 vb, Plane pb, const HEdgeDev *heb_tab,
+                                                 const uint32_t *edges_b, int neb)
+{
+    const int total = nea * neb;
+    float best = -FLT_MAX;
+    int best_e = 0x7fffffff;
+    V3 best_n = mk3(0.f, 0.f, 0.f);
+    for (int base = 0; base < total; base += 32) {
+        const int e = base + lane;
+        const bool valid = e < total;
+        const int ia = valid ? e / neb : 0, ib = valid ? e % neb : 0;
+        const uint32_t ha = MDR_LDG(edges_a + ia), hb = MDR_LDG(edges_b + ib);
+        const HEdgeDev ea = ldHE(hea_tab, ha), eb = ldHE(heb_tab, hb);
+        const int ea_twin_poly = (int)MDR_LDG(&hea_tab[ea.twin].poly);
+        const int eb_twin_poly = (int)MDR_LDG(&heb_tab[eb.twin].poly);
+        const int ea_next_root = (int)MDR_LDG(&hea_tab[ea.next].root);
+        const int eb_next_root = (int)MDR_LDG(&heb_tab[eb.next].root);
+        // every lane takes part in every shuffle
+        const V3 an1 = shfl3(pa.n, (int)ea.poly), an2 = shfl3(pa.n, ea_twin_poly);
+        const V3 bn1 = shfl3(pb.n, (int)eb.poly), bn2 = shfl3(pb.n, eb_twin_poly);
+        const V3 a1 = shfl3(va, (int)ea.root), a2 = shfl3(va, ea_next_root);
+        const V3 b1 = shfl3(vb, (int)eb.root), b2 = shfl3(vb, eb_next_root);
+        float sep = -FLT_MAX;
+        V3 normal = mk3(0.f, 0.f, 0.f);
+        if (valid && minkowskiFace(an1, an2, -bn1, -bn2)) {
+            V3 da = a2 - a1, db = b2 - b1;
+            V3 cr = cross(da, db);
+            float l2 = len2(cr);
+            if (l2 != 0) {
+                float inv = 1.f / sqrtf(l2);
+                normal = cr * inv;
+                if (dot(normal, a1 - centre_a) < 0.0f) normal = -normal;
+                sep = dot(normal, b1 - a1);
+            }
+        }
+        if (valid && sep > best) { best = sep; best_e = e; best_n = normal; }
+    }
+    float wv = best;
+    int we = best_e;
+    warpArgMax(wv, we);
+    EdgeWin r;
+    r.sep = wv;
+    if (we == 0x7fffffff || wv == -FLT_MAX) {
+        // nothing beat the reference's initial (-FLT_MAX, zero normal, 0, 0)
+        r.normal = mk3(0.f, 0.f, 0.f); r.ea = 0; r.eb = 0;
+        return r;
+    }
+    const int owner = we & 31;       // lane that evaluated pair `we`
+    r.normal = shfl3(best_n, owner);
+    r.ea = (int)MDR_LDG(edges_a + we / neb);
+    r.eb = (int)MDR_LDG(edges_b + we % neb);
+    return r;
+}
+
+// One queued hull-hull pair, one warp. doSAT + generateContacts for two hulls
+// (narrowphase.cpp:678-758,1366-1513).
+__device__ __forceinline__ void hullHullWarp(WorldView &v, const StepParams &p, int pi, int lane,
+                                             bool probing, int sub)
+{
+    const uint32_t pr = v.pairs[pi];
+    const int a = pr & 1023, b = (pr >> 10) & 1023;     // both hulls: no reordering by type
+    const BodyXf xa = bodyXf(v, p, a), xb = bodyXf(v, p, b);
+    const ObjDev *oa = xa.o, *ob = xb.o;
+    const float *src_va = p.a.verts + 3 * MDR_LDG(&oa->vert_off), *src_vb = p.a.verts + 3 * MDR_LDG(&ob->vert_off);
+    const float *src_pa = p.a.planes + 4 * MDR_LDG(&oa->face_off), *src_pb = p.a.planes + 4 * MDR_LDG(&ob->face_off);
+    const int nva = MDR_LDG(&oa->num_verts), nvb = MDR_LDG(&ob->num_verts);
+    const int nfa = MDR_LDG(&oa->num_faces), nfb = MDR_LDG(&ob->num_faces);
+    const int nea = MDR_LDG(&oa->num_edges), neb = MDR_LDG(&ob->num_edges);
+    HullTopo ta, tb;
+    ta.he = p.a.hedges + MDR_LDG(&oa->hedge_off); ta.polys = p.a.polys + MDR_LDG(&oa->face_off);
+    tb.he = p.a.hedges + MDR_LDG(&ob->hedge_off); tb.polys = p.a.polys + MDR_LDG(&ob->face_off);
+    const uint32_t *edges_a = p.a.edges + MDR_LDG(&oa->edge_off), *edges_b = p.a.edges + MDR_LDG(&ob->edge_off);
+
+    const V3 zero = mk3(0.f, 0.f, 0.f);
+    Plane none;
+    none.n = zero; none.d = 0.f;
+    const V3 va = lane < nva ? worldVert(xa, src_va, lane) : zero;
+    const V3 vb = lane < nvb ? worldVert(xb, src_vb, lane) : zero;
+    const Plane pa = lane < nfa ? worldPlane(xa, src_pa, lane) : none;
+    const Plane pb = lane < nfb ? worldPlane(xb, src_pb, lane) : none;
+
+    Manifold m;
+    int ref = -1, alt = -1;
+    bool hit = false;
+    do {
+        float fa_sep = faceSeparationLane(pa, lane < nfa, vb, nvb);
+        int fa_face = lane;
+        warpArgMax(fa_sep, fa_face);
+        if (fa_sep > 0.0f) break;
+        float fb_sep = faceSeparationLane(pb, lane < nfb, va, nva);
+        int fb_face = lane;
+        warpArgMax(fb_sep, fb_face);
+        if (fb_sep > 0.0f) break;
+        const EdgeWin eq = edgeQueryWarp(lane, va, pa, ta.he, edges_a, nea, xa.t, vb, pb, tb.he, edges_b, neb);
+        if (eq.sep > 0.0f) break;
+        const bool face_a = fa_sep > eq.sep, face_b = fb_sep > eq.sep;
+        XfVerts xva, xvb;
+        xva.x = xa; xva.src = src_va; xvb.x = xb; xvb.src = src_vb;
+        if (face_a || face_b) {
+            const bool a_ref = fa_sep >= fb_sep;
+            const int rf = a_ref ? fa_face : fb_face;
+            Plane rp;
+            rp.n = a_ref ? shfl3(pa.n, rf) : shfl3(pb.n, rf);
+            rp.d = a_ref ? __shfl_sync(MDR_FULL, pa.d, rf) : __shfl_sync(MDR_FULL, pb.d, rf);
+            // incident face: most anti-parallel normal of the other hull, first
+            // strict minimum (narrowphase.cpp:578-624) = arg-max of the negation
+            const Plane po = a_ref ? pb : pa;
+            const int nfo = a_ref ? nfb : nfa;
+            float neg = lane < nfo ? -dot(po.n, rp.n) : -FLT_MAX;
+            int inc = lane;
+            warpArgMax(neg, inc);
+            if (lane == 0) {
+                if (a_ref) faceContact(m, rp, rf, inc, ta, xva, tb, xvb);
+                else faceContact(m, rp, rf, inc, tb, xvb, ta, xva);
+            }
+            ref = a_ref ? a : b;
+            alt = a_ref ? b : a;
+        } else {
+            if (lane == 0) edgeContact(m, eq.normal, eq.sep, eq.ea, eq.eb, ta, xva, tb, xvb);
+            ref = a; alt = b;
+        }
+        hit = true;
+    } while (false);
+    if (lane == 0) {
+        SolverContact *sc = contactSlot(v, pi);
+        const bool emit = hit && m.n > 0;
+        if (emit) emitContact(v, p, sc, m, ref, alt);
+        if (probing) probeContact(p, sub, pi, emit ? &m : nullptr, ref, alt);
+    }
+}
+
+// The queue: all warps of the world's thread group take queued pairs in turn.
+__device__ __forceinline__ void satQueueWarp(const BlockCtx &c, WorldView &v, const StepParams &p,
+                                             bool probing, int sub)
+{
+    int count = v.misc[2];
+    if (count > MDR_SAT_QUEUE) count = MDR_SAT_QUEUE;
+    const int warp = c.tid() >> 5, nwarps = c.nthreads() >> 5, lane = c.tid() & 31;
+    for (int k = warp; k < count; k += nwarps) hullHullWarp(v, p, v.sat_queue[k], lane, probing, sub);
+}
+
+}  // namespace mdr
+#endif

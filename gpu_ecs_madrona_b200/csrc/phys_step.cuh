@@ -4,6 +4,7 @@
 #include "phys_world.cuh"
 #include "phys_solver.cuh"
 #include "phys_narrow.cuh"
+#include "phys_sat_warp.cuh"
 
 namespace mdr {
 
@@ -40,6 +41,10 @@ MDR_HD void stepWorld(const BlockCtx &c, WorldView &v, const StepParams &p, int 
         const int np = v.misc[0];
         for (int i = c.tid(); i < np; i += c.nthreads()) narrowphasePair(v, p, i, probing, sub);
         c.sync();
+#if defined(__CUDA_ARCH__)
+        satQueueWarp(c, v, p, probing, sub);
+        c.sync();
+#endif
         solveLevels<false>(c, v, p, max_level);
         setVelocities(c, v, p);
         c.sync();

@@ -80,7 +80,8 @@ struct WorldView {
     uint32_t *meta;        // object id | META_*
     float *box;            // [np][6] leaf AABBs (broadphase) / world AABBs (narrowphase)
     uint32_t *pairs;       // [max_pairs] row a | row b << 10 | level << 20
-    int32_t *misc;         // [0] num pairs  [1] max level
+    int32_t *misc;         // [0] num pairs  [1] max level  [2] queued hull-hull pairs
+    uint16_t *sat_queue;   // [MDR_SAT_QUEUE] pair slots awaiting the warp-cooperative SAT
     // --- broadphase scratch, aliased with the contact slots ---
     float *slot;           // [np][6] grow-only slot boxes
     int32_t *ent_id;       // [np]
@@ -117,6 +118,7 @@ MDR_HD size_t carveWorld(WorldView &v, char *base, int np, int max_pairs, int sm
     MDR_CARVE(box, float, 6 * np)
     MDR_CARVE(pairs, uint32_t, max_pairs)
     MDR_CARVE(misc, int32_t, 4)
+    MDR_CARVE(sat_queue, uint16_t, MDR_SAT_QUEUE)
     off = alignUp(off, 16);
     const size_t region = off;
     MDR_CARVE(contacts, SolverContact, smem_contacts)
