@@ -220,6 +220,29 @@ MDR_HD int clipPolygon(V3 *dst, Plane cp, const V3 *in, int n_in)
 // A contact manifold before it is handed to the solver.
 struct Manifold { V3 pts[4]; float depths[4]; int n; V3 normal; };
 
+// The manifold goes to world space through an identity transform
+// (narrowphase.cpp:855-863): point = rotate(identity, p) + (0,0,0), normal =
+// rotate(identity, n). For finite p, rotate(identity, p) is p plus a signed
+// zero, and adding the +0 translation leaves p when p != 0 and +0 when p is
+// either zero: exactly `p + 0.f`. The normal has no translation, so the sign of
+// a zero component depends on the zeros inside rotate(): it is evaluated as is.
+MDR_HD void finishManifold(Manifold &m, V3 n)
+{
+    for (int i = 0; i < 4; i++) {
+        if (i < m.n) m.pts[i] = mk3(m.pts[i].x + 0.f, m.pts[i].y + 0.f, m.pts[i].z + 0.f);
+    }
+    m.normal = rotate(mk4(1.f, 0.f, 0.f, 0.f), n);
+}
+
+// Register-resident insertion of the first four manifold points.
+MDR_HD void setManifoldPoint(Manifold &m, int idx, V3 pt, float depth)
+{
+    if (idx == 0) { m.pts[0] = pt; m.depths[0] = depth; }
+    else if (idx == 1) { m.pts[1] = pt; m.depths[1] = depth; }
+    else if (idx == 2) { m.pts[2] = pt; m.depths[2] = depth; }
+    else if (idx == 3) { m.pts[3] = pt; m.depths[3] = depth; }
+}
+
 // buildFaceContactManifold, narrowphase.cpp:790-864. The >4-point reduction
 // reproduces the reference as written: `largestArea` is never updated, so point
 // 2 is the LAST candidate of positive signed area and point 3 the LAST of
@@ -264,11 +287,7 @@ MDR_HD void buildManifold(Manifold &m, V3 n, V3 *contacts, float *depths, int nu
             if (area < 0.0f) { m.pts[3] = contacts[i]; m.depths[3] = depths[i]; }
         }
     }
-    // The manifold goes to world space through an identity transform
-    // (narrowphase.cpp:855-863): kept, it turns -0 into +0.
-    const Q4 ident = mk4(1.f, 0.f, 0.f, 0.f);
-    for (int i = 0; i < m.n; i++) m.pts[i] = rotate(ident, m.pts[i]) + zero;
-    m.normal = rotate(ident, n);
+    finishManifold(m, n);
 }
 
 // Where contact generation takes hull vertices from: the per-thread arrays of
@@ -351,7 +370,7 @@ MDR_HD void edgeContact(Manifold &m, V3 normal, float sep, int ea, int eb,
     const Q4 ident = mk4(1.f, 0.f, 0.f, 0.f);
     const V3 zero = mk3(0.f, 0.f, 0.f);
     for (int i = 0; i < 4; i++) { m.pts[i] = zero; m.depths[i] = 0.f; }
-    m.pts[0] = rotate(ident, contact) + zero;
+    m.pts[0] = mk3(contact.x + 0.f, contact.y + 0.f, contact.z + 0.f);   // see finishManifold
     m.depths[0] = -sep;
     m.n = 1;
     m.normal = rotate(ident, normal);
@@ -379,8 +398,12 @@ MDR_HD bool hullPlaneContact(Manifold &m, const BodyXf &x, const StepParams &p, 
         float d = dot(worldNormal(x, src_p, f), plane.n);
         if (d < best) { best = d; inc_face = f; }
     }
-    V3 pts[MDR_MAX_POLY];
-    float depths[MDR_MAX_POLY];
+    // Up to four points stay in registers (every quad face); a fifth sends the
+    // whole list through the generic reduction.
+    const V3 zero = mk3(0.f, 0.f, 0.f);
+    for (int i = 0; i < 4; i++) { m.pts[i] = zero; m.depths[i] = 0.f; }
+    V3 more[MDR_MAX_POLY - 4];
+    float more_d[MDR_MAX_POLY - 4];
     const HEdgeDev *hes = p.a.hedges + MDR_LDG(&o->hedge_off);
     uint32_t he = MDR_LDG(p.a.polys + MDR_LDG(&o->face_off) + inc_face), start = he;
     int n = 0;
@@ -390,12 +413,24 @@ MDR_HD bool hullPlaneContact(Manifold &m, const BodyXf &x, const StepParams &p, 
         V3 vv = worldVert(x, src_v, (int)e.root);
         float d = planeDist(plane, vv);
         if (d < 0.0f && n < MDR_MAX_POLY) {
-            pts[n] = vv - d * plane.n;
-            depths[n] = -d;
+            V3 pt = vv - d * plane.n;
+            if (n < 4) setManifoldPoint(m, n, pt, -d);
+            else { more[n - 4] = pt; more_d[n - 4] = -d; }
             n++;
         }
     } while (he != start);
-    buildManifold(m, plane.n, pts, depths, n);
+    if (n <= 4) {
+        m.n = n;
+        finishManifold(m, plane.n);
+    } else {
+        V3 pts[MDR_MAX_POLY];
+        float depths[MDR_MAX_POLY];
+        for (int i = 0; i < n; i++) {
+            pts[i] = i < 4 ? m.pts[i] : more[i - 4];
+            depths[i] = i < 4 ? m.depths[i] : more_d[i - 4];
+        }
+        buildManifold(m, plane.n, pts, depths, n);
+    }
     return true;
 }
 
