@@ -1,0 +1,908 @@
+// ECS state layer + task-graph executor: host half (registration, query
+// resolution, graph lowering, table allocation) and the kernels
+//   ecsStepKernel        persistent megakernel: one warp walks the task graph of one world
+//   ecsScriptKernel      immediate-mode create / destroy / clear (world constructors, tests)
+//   ecsExportOffsets / ecsExportCopyOut / ecsExportCopyIn   exported-column staging
+// behind the mdr_ecs_* C ABI of include/madrona_b200.h. sm_100a only.
+//
+// Reference interfaces restated: ECSRegistry (include/madrona/state.hpp:109-134,
+// state.inl:17-215), StateManager::makeQuery (src/core/state.cpp:270-361),
+// TaskGraph::Builder (src/core/taskgraph.cpp:11-122), export copy kernels
+// (src/mw/device/consts.cpp:92-273), MWCudaExecutor::run (src/mw/cuda_exec.cpp:1777-1794).
+#include <cuda_runtime.h>
+
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <vector>
+
+#include "../../include/madrona_b200.h"
+#include "ecs_apps.cuh"
+
+using namespace mdr::ecs;
+
+#define REQ_CUDA(expr)                                                                   \
+    do {                                                                                 \
+        cudaError_t e_ = (expr);                                                         \
+        if (e_ != cudaSuccess) {                                                         \
+            fprintf(stderr, "madrona_b200: CUDA error %s at %s:%d: %s\n",                \
+                    cudaGetErrorName(e_), __FILE__, __LINE__, cudaGetErrorString(e_));   \
+            abort();                                                                     \
+        }                                                                                \
+    } while (0)
+
+namespace {
+
+constexpr int kWarpsPerBlock = 8;
+
+// ------------------------------------------------------------------ kernels --
+__global__ void __launch_bounds__(32 * kWarpsPerBlock)
+ecsStepKernel(const EcsDev *__restrict__ E)
+{
+    __shared__ WarpShared shared[kWarpsPerBlock];
+    WarpShared *ws = &shared[threadIdx.x >> 5];
+    const int warps = gridDim.x * kWarpsPerBlock;
+    const int num_nodes = E->num_nodes;
+    Context ctx;
+    for (int w = blockIdx.x * kWarpsPerBlock + (threadIdx.x >> 5); w < E->num_worlds; w += warps) {
+        loadWorld(ctx, E, ws, w);
+        // TaskGraph::run (src/core/taskgraph.cpp:117-122): nodes in sorted order
+        for (int ni = 0; ni < num_nodes; ni++) {
+            const NodeDev &nd = E->node[ni];
+            switch (nd.kind) {
+            case kNodeParallelFor: apps::dispatchParallelFor(ctx, nd); break;
+            case kNodeClearTmp: clearArchetype(ctx, nd.arch, true); break;      // taskgraph.inl:88-92
+            case kNodeSort: sortArchetype(ctx, nd.arch, nd.key_col, nd.remap != 0); break;
+            default: break;                                                     // ResetTmpAllocNode: no bump allocator to reset
+            }
+            __syncwarp();
+        }
+        storeWorld(ctx);
+    }
+}
+
+// ops of world w are ops[offsets[w] .. offsets[w + 1]) or, with offsets == null,
+// the same ops[0 .. num_shared) for every world.
+__global__ void __launch_bounds__(32 * kWarpsPerBlock)
+ecsScriptKernel(const EcsDev *__restrict__ E, const mdr_script_op *__restrict__ ops,
+                const int32_t *__restrict__ offsets, int32_t num_shared)
+{
+    __shared__ WarpShared shared[kWarpsPerBlock];
+    WarpShared *ws = &shared[threadIdx.x >> 5];
+    const int warps = gridDim.x * kWarpsPerBlock;
+    const int lane = laneId();
+    const bool script_app = E->app == MDR_APP_SCRIPT;
+    Context ctx;
+    for (int w = blockIdx.x * kWarpsPerBlock + (threadIdx.x >> 5); w < E->num_worlds; w += warps) {
+        loadWorld(ctx, E, ws, w);
+        const int32_t begin = offsets ? offsets[w] : 0, end = offsets ? offsets[w + 1] : num_shared;
+        Entity *handles = E->handles ? E->handles + (size_t)w * E->max_handles : nullptr;
+        int32_t nh = handles ? E->num_handles[w] : 0;
+        int32_t pos = begin;
+        while (pos < end) {
+            const int32_t i = pos + lane;
+            mdr_script_op op { 0, 0, 0 };
+            if (i < end) op = ops[i];
+            const unsigned special = __ballot_sync(kFull, op.op >= MDR_OP_CLEAR);
+            int len = special ? __ffs(special) - 1 : 32;
+            if (len == 0) {
+                const int32_t kind = __shfl_sync(kFull, op.op, 0), a = __shfl_sync(kFull, op.a, 0),
+                              b = __shfl_sync(kFull, op.b, 0);
+                if (kind == MDR_OP_CLEAR) {
+                    if (a >= 0 && a < E->num_arch) clearArchetype(ctx, a, false);
+                } else if (kind == MDR_OP_CLEAR_TMP) {
+                    clearArchetype(ctx, 3, true);
+                } else if (kind == MDR_OP_TMP) {
+                    if (lane == 0) {
+                        const Loc l = ctx.makeTemporary(3);
+                        if (l.archetype != kNoArch) ctx.column<uint32_t>(3, 1)[l.row] = (uint32_t)b;
+                    }
+                    __syncwarp();
+                }
+                pos += 1;
+                continue;
+            }
+            bool in = lane < len && i < end;
+            bool is_create = in && op.op == MDR_OP_CREATE && op.a >= 0 && op.a < E->num_arch;
+            int before = __popc(__ballot_sync(kFull, is_create) & lowMask(lane));
+            // a destroy naming a handle that an earlier op of this slice creates ends the slice
+            const unsigned split = __ballot_sync(kFull, in && op.op == MDR_OP_DESTROY && op.a >= nh && op.a < nh + before);
+            if (split) {
+                len = __ffs(split) - 1;
+                in = lane < len;
+                is_create = is_create && in;
+            }
+            const bool is_destroy = in && op.op == MDR_OP_DESTROY && op.a >= 0 && op.a < nh;
+            if (is_destroy) ctx.destroyEntityNow(handles[op.a]);
+            if (is_create) {
+                float pb[3], pc[4];
+                mdr_script_payload(op.b, pb, pc);
+                if (script_app) {
+                    struct { uint32_t v; float b[3]; float c[4]; } row { (uint32_t)op.b, { pb[0], pb[1], pb[2] },
+                                                                      { pc[0], pc[1], pc[2], pc[3] } };
+                    ctx.makeEntityNowIn(op.a, row);
+                } else {
+                    struct { uint32_t z[kMaxPayloadWords]; } row {};
+                    ctx.makeEntityNowIn(op.a, row);
+                }
+            }
+            __syncwarp();
+            applyPending(ctx);
+            const unsigned creates = __ballot_sync(kFull, is_create);
+            if (is_create && handles) {
+                const int32_t h = nh + before;
+                if (h < E->max_handles) handles[h] = ctx.created;
+                else atomicOr(E->error, kErrHandleOverflow);
+            }
+            nh += __popc(creates);
+            if (nh > E->max_handles && handles) nh = E->max_handles;
+            pos += len < end - pos ? len : end - pos;
+            __syncwarp();
+        }
+        if (handles && lane == 0) E->num_handles[w] = nh;
+        storeWorld(ctx);
+    }
+}
+
+// StateManager::copyOutExportedColumns (src/core/state.cpp:516-563) /
+// madronaMWGPUExportBlockSums + ExportCopyOut (src/mw/device/consts.cpp:137-273):
+// offsets[w] = rows of the export's archetype in worlds < w. One block per slot.
+__global__ void __launch_bounds__(1024) ecsExportOffsets(const EcsDev *__restrict__ E)
+{
+    __shared__ int64_t warp_sums[32];
+    __shared__ int64_t carry;
+    const ExportDev &x = E->exports[blockIdx.x];
+    if (x.fixed) return;
+    const int32_t *counts = E->arch[x.arch].row_count;
+    const int W = E->num_worlds, lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    if (threadIdx.x == 0) carry = 0;
+    __syncthreads();
+    for (int base = 0; base < W; base += 1024) {
+        const int w = base + threadIdx.x;
+        const int64_t v = w < W ? counts[w] : 0;
+        int64_t incl = v;
+        for (int o = 1; o < 32; o <<= 1) {
+            const int64_t t = __shfl_up_sync(kFull, incl, o);
+            if (lane >= o) incl += t;
+        }
+        if (lane == 31) warp_sums[wid] = incl;
+        __syncthreads();
+        if (wid == 0) {
+            int64_t s = warp_sums[lane], si = s;
+            for (int o = 1; o < 32; o <<= 1) {
+                const int64_t t = __shfl_up_sync(kFull, si, o);
+                if (lane >= o) si += t;
+            }
+            warp_sums[lane] = si - s;
+        }
+        __syncthreads();
+        const int64_t c = carry;
+        if (w < W) x.offsets[w] = c + warp_sums[wid] + incl - v;
+        __syncthreads();
+        if (threadIdx.x == 1023) carry = c + warp_sums[wid] + incl;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) x.offsets[W] = carry;
+}
+
+// One warp per world; every non-fixed export: tile rows -> contiguous buffer
+// (to_buffer) or back (the reference's copy-in of actions before the step).
+__global__ void __launch_bounds__(256) ecsExportCopy(const EcsDev *__restrict__ E, int to_buffer)
+{
+    const int w = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (w >= E->num_worlds) return;
+    for (int s = 0; s < E->num_exports; s++) {
+        const ExportDev &x = E->exports[s];
+        if (x.fixed) continue;
+        const ArchDev &A = E->arch[x.arch];
+        const int64_t off = x.offsets[w];
+        const int32_t n = (int32_t)(x.offsets[w + 1] - off);
+        const int words = x.bytes >> 2;
+        uint32_t *tile = (uint32_t *)(A.col[x.col] + (size_t)w * A.stride * x.bytes);
+        uint32_t *buf = (uint32_t *)x.buffer + off * words;
+        const int64_t total = (int64_t)n * words;
+        if (to_buffer) for (int64_t i = lane; i < total; i += 32) buf[i] = tile[i];
+        else for (int64_t i = lane; i < total; i += 32) tile[i] = buf[i];
+    }
+}
+
+// Replicates the id nodes every world starts with (singleton entities).
+__global__ void ecsBroadcastNodes(IdNode *dst, int32_t id_cap, const IdNode *src, int32_t n, int32_t num_worlds)
+{
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= (int64_t)num_worlds * n) return;
+    const int32_t w = (int32_t)(i / n), k = (int32_t)(i - (int64_t)w * n);
+    dst[(size_t)w * id_cap + k] = src[k];
+}
+
+// ---------------------------------------------------------------- host side --
+struct HostComponent { int32_t bytes, align; };
+struct HostArchetype { std::vector<int32_t> comps; int32_t max_rows, flags; bool singleton; };
+struct HostNode { int32_t kind, func, arch, key_comp, remap; std::vector<int32_t> comps, deps; };
+struct HostExport { int32_t arch, comp; };
+
+}  // namespace
+
+struct mdr_ecs {
+    mdr_ecs_config cfg;
+    std::vector<HostComponent> comps;
+    std::vector<HostArchetype> archs;
+    std::vector<HostNode> nodes;
+    std::vector<HostExport> exports;    // by slot
+    bool built = false;
+    EcsDev host {};                     // host copy of the device descriptor
+    EcsDev *dev = nullptr;
+    std::vector<void *> allocs;
+    cudaStream_t stream = nullptr;
+    cudaGraphExec_t graph = nullptr;
+    bool exports_dirty = true;
+    int blocks = 0;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    double timed_ms = 0;
+    int timed_steps = 0, pending_steps = 0;
+    bool timing_open = false;
+
+    template <typename T> T *dalloc(size_t n, bool zero = true)
+    {
+        void *p = nullptr;
+        const size_t bytes = (n ? n : 1) * sizeof(T);
+        REQ_CUDA(cudaMalloc(&p, bytes));
+        if (zero) REQ_CUDA(cudaMemset(p, 0, bytes));
+        allocs.push_back(p);
+        return (T *)p;
+    }
+};
+
+namespace {
+
+int colOf(const HostArchetype &a, int32_t comp)
+{
+    if (comp == 0) return 0;   // Entity is column 0 of every table (src/core/state.cpp:383-385)
+    for (size_t i = 0; i < a.comps.size(); i++)
+        if (a.comps[i] == comp) return (int)i + 1;
+    return -1;
+}
+
+bool depsOk(const mdr_ecs *e, const int32_t *deps, int32_t ndeps)
+{
+    // Builder::build (src/core/taskgraph.cpp:39-109) emits nodes in insertion order
+    // and spins if a dependency is not yet emitted: only earlier nodes are valid.
+    if (ndeps < 0 || (ndeps > 0 && !deps)) return false;
+    for (int i = 0; i < ndeps; i++)
+        if (deps[i] < 0 || deps[i] >= (int32_t)e->nodes.size()) return false;
+    return true;
+}
+
+void closeTiming(mdr_ecs *e)
+{
+    if (!e->timing_open) return;
+    float ms = 0.f;
+    REQ_CUDA(cudaEventSynchronize(e->ev1));
+    REQ_CUDA(cudaEventElapsedTime(&ms, e->ev0, e->ev1));
+    e->timed_ms += ms;
+    e->timed_steps += e->pending_steps;
+    e->pending_steps = 0;
+    e->timing_open = false;
+}
+
+void refreshExports(mdr_ecs *e)
+{
+    if (e->host.num_exports > 0) {
+        ecsExportOffsets<<<e->host.num_exports, 1024, 0, e->stream>>>(e->dev);
+        ecsExportCopy<<<(e->host.num_worlds + 7) / 8, 256, 0, e->stream>>>(e->dev, 1);
+        REQ_CUDA(cudaGetLastError());
+    }
+    e->exports_dirty = false;
+}
+
+void runScript(mdr_ecs *e, const mdr_script_op *d_ops, const int32_t *d_offsets, int32_t num_shared)
+{
+    ecsScriptKernel<<<e->blocks, 32 * kWarpsPerBlock, 0, e->stream>>>(e->dev, d_ops, d_offsets, num_shared);
+    REQ_CUDA(cudaGetLastError());
+    e->exports_dirty = true;
+}
+
+int32_t checkError(mdr_ecs *e)
+{
+    int32_t err = 0;
+    REQ_CUDA(cudaMemcpy(&err, e->host.error, 4, cudaMemcpyDeviceToHost));
+    if (err) {
+        REQ_CUDA(cudaMemset(e->host.error, 0, 4));
+        return MDR_EOVERFLOW;
+    }
+    return MDR_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int32_t mdr_ecs_create(const mdr_ecs_config *cfg, mdr_ecs **out)
+{
+    if (!cfg || !out || cfg->num_worlds <= 0 || cfg->first_world < 0) return MDR_EINVAL;
+    if (cfg->gpu_id < 0 || cfg->gpu_id >= mdr_device_count()) return MDR_ENODEVICE;
+    REQ_CUDA(cudaSetDevice(cfg->gpu_id));
+    cudaDeviceProp prop;
+    REQ_CUDA(cudaGetDeviceProperties(&prop, cfg->gpu_id));
+    if (prop.major != 10) {
+        fprintf(stderr, "madrona_b200: device %d is sm_%d%d; this library is built for sm_100a only\n",
+                cfg->gpu_id, prop.major, prop.minor);
+        return MDR_ENODEVICE;
+    }
+    mdr_ecs *e = new mdr_ecs;
+    e->cfg = *cfg;
+    e->comps.push_back({ 8, 4 });   // Entity is component 0 (StateManager ctor, src/core/state.cpp:148-162)
+    REQ_CUDA(cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking));
+    REQ_CUDA(cudaEventCreate(&e->ev0));
+    REQ_CUDA(cudaEventCreate(&e->ev1));
+    *out = e;
+    return MDR_OK;
+}
+
+void mdr_ecs_destroy(mdr_ecs *e)
+{
+    if (!e) return;
+    cudaSetDevice(e->cfg.gpu_id);
+    if (e->stream) cudaStreamSynchronize(e->stream);
+    if (e->graph) cudaGraphExecDestroy(e->graph);
+    if (e->stream) cudaStreamDestroy(e->stream);
+    if (e->ev0) cudaEventDestroy(e->ev0);
+    if (e->ev1) cudaEventDestroy(e->ev1);
+    for (void *a : e->allocs) cudaFree(a);
+    delete e;
+}
+
+int32_t mdr_ecs_register_component(mdr_ecs *e, int32_t bytes, int32_t align)
+{
+    if (!e || bytes <= 0 || bytes % 4 != 0 || align <= 0 || align > 16) return MDR_EINVAL;
+    if (e->built) return MDR_ESTATE;
+    e->comps.push_back({ bytes, align });
+    return (int32_t)e->comps.size() - 1;
+}
+
+static int32_t addArchetype(mdr_ecs *e, const int32_t *comps, int32_t n, int32_t max_rows, int32_t flags, bool singleton)
+{
+    if (!e || n <= 0 || n + 1 > kMaxCols || !comps || max_rows <= 0) return MDR_EINVAL;
+    if (e->built) return MDR_ESTATE;
+    if ((int)e->archs.size() >= kMaxArch) return MDR_ECAPACITY;
+    HostArchetype a;
+    for (int i = 0; i < n; i++) {
+        if (comps[i] <= 0 || comps[i] >= (int32_t)e->comps.size()) return MDR_EINVAL;
+        a.comps.push_back(comps[i]);
+    }
+    a.max_rows = max_rows; a.flags = flags; a.singleton = singleton;
+    e->archs.push_back(a);
+    return (int32_t)e->archs.size() - 1;
+}
+
+int32_t mdr_ecs_register_archetype(mdr_ecs *e, const int32_t *comps, int32_t n, int32_t max_rows, int32_t flags)
+{
+    return addArchetype(e, comps, n, max_rows, flags, false);
+}
+
+int32_t mdr_ecs_register_singleton(mdr_ecs *e, int32_t bytes, int32_t align)
+{
+    int32_t c = mdr_ecs_register_component(e, bytes, align);
+    if (c < 0) return c;
+    return addArchetype(e, &c, 1, 1, MDR_ARCH_FIXED, true);
+}
+
+int32_t mdr_ecs_export_column(mdr_ecs *e, int32_t arch, int32_t comp, int32_t slot)
+{
+    if (!e || arch < 0 || arch >= (int32_t)e->archs.size() || slot < 0 || slot >= kMaxExports) return MDR_EINVAL;
+    if (e->built) return MDR_ESTATE;
+    if (colOf(e->archs[arch], comp) < 0) return MDR_EINVAL;
+    if ((int)e->exports.size() <= slot) e->exports.resize(slot + 1, HostExport { -1, -1 });
+    e->exports[slot] = { arch, comp };
+    return MDR_OK;
+}
+
+static int32_t addNode(mdr_ecs *e, HostNode n, const int32_t *deps, int32_t ndeps)
+{
+    if (!e) return MDR_EINVAL;
+    if (e->built) return MDR_ESTATE;
+    if (!depsOk(e, deps, ndeps)) return MDR_EINVAL;
+    if ((int)e->nodes.size() >= kMaxNodes) return MDR_ECAPACITY;
+    n.deps.assign(deps, deps + ndeps);
+    e->nodes.push_back(n);
+    return (int32_t)e->nodes.size() - 1;
+}
+
+int32_t mdr_ecs_add_parallel_for(mdr_ecs *e, int32_t func, const int32_t *comps, int32_t n, const int32_t *deps,
+                                 int32_t ndeps)
+{
+    if (!e || !comps || n <= 0 || n > kMaxQueryComps || func <= 0) return MDR_EINVAL;
+    HostNode node { kNodeParallelFor, func, -1, -1, 0, {}, {} };
+    for (int i = 0; i < n; i++) {
+        if (comps[i] < 0 || comps[i] >= (int32_t)e->comps.size()) return MDR_EINVAL;
+        node.comps.push_back(comps[i]);
+    }
+    return addNode(e, node, deps, ndeps);
+}
+
+int32_t mdr_ecs_add_clear_tmp(mdr_ecs *e, int32_t arch, const int32_t *deps, int32_t ndeps)
+{
+    if (!e || arch < 0 || arch >= (int32_t)e->archs.size()) return MDR_EINVAL;
+    return addNode(e, HostNode { kNodeClearTmp, 0, arch, -1, 0, {}, {} }, deps, ndeps);
+}
+
+int32_t mdr_ecs_add_reset_tmp_alloc(mdr_ecs *e, const int32_t *deps, int32_t ndeps)
+{
+    return addNode(e, HostNode { kNodeResetTmpAlloc, 0, -1, -1, 0, {}, {} }, deps, ndeps);
+}
+
+int32_t mdr_ecs_add_sort(mdr_ecs *e, int32_t arch, int32_t key_comp, int32_t remap_entities, const int32_t *deps,
+                         int32_t ndeps)
+{
+    if (!e || arch < 0 || arch >= (int32_t)e->archs.size()) return MDR_EINVAL;
+    const int col = colOf(e->archs[arch], key_comp);
+    if (col <= 0 || e->comps[key_comp].bytes != 4) return MDR_EINVAL;
+    return addNode(e, HostNode { kNodeSort, 0, arch, key_comp, remap_entities, {}, {} }, deps, ndeps);
+}
+
+int32_t mdr_ecs_build(mdr_ecs *e)
+{
+    if (!e) return MDR_EINVAL;
+    if (e->built) return MDR_ESTATE;
+    if (e->archs.empty()) return MDR_EINVAL;
+    REQ_CUDA(cudaSetDevice(e->cfg.gpu_id));
+    EcsDev &H = e->host;
+    memset(&H, 0, sizeof(H));
+    const int W = e->cfg.num_worlds;
+    H.num_worlds = W;
+    H.first_world = e->cfg.first_world;
+    H.num_arch = (int32_t)e->archs.size();
+    H.app = e->cfg.app;
+    int64_t total_rows = 0;
+    int num_singletons = 0;
+    for (int a = 0; a < H.num_arch; a++) {
+        const HostArchetype &ha = e->archs[a];
+        ArchDev &A = H.arch[a];
+        A.num_cols = (int32_t)ha.comps.size() + 1;
+        A.max_rows = ha.max_rows;
+        A.stride = (ha.max_rows + 15) / 16 * 16;
+        A.flags = ha.flags;
+        A.row_count = e->dalloc<int32_t>(W);
+        for (int c = 0; c < A.num_cols; c++) {
+            A.col_bytes[c] = c == 0 ? 8 : e->comps[ha.comps[c - 1]].bytes;
+            A.col[c] = e->dalloc<char>((size_t)W * A.stride * A.col_bytes[c]);
+        }
+        total_rows += ha.max_rows;
+        num_singletons += ha.singleton;
+    }
+    H.id_cap = e->cfg.ids_per_world > 0 ? (e->cfg.ids_per_world + 63) / 64 * 64
+                                        : (int32_t)((total_rows + 63) / 64 * 64 + 64 * (4 + (num_singletons ? 1 : 0)));
+    H.id_nodes = e->dalloc<IdNode>((size_t)W * H.id_cap);
+    H.id_state = e->dalloc<IdState>(W);
+    H.error = e->dalloc<int32_t>(1);
+    H.max_handles = e->cfg.max_script_handles;
+    if (H.max_handles > 0) {
+        H.handles = e->dalloc<Entity>((size_t)W * H.max_handles);
+        H.num_handles = e->dalloc<int32_t>(W);
+    }
+
+    // Initial id state of every world. registerSingleton (include/madrona/state.inl:
+    // 171-187) makes one entity per singleton through the StateManager's own init cache.
+    std::vector<IdNode> nodes0(H.id_cap, IdNode { 0, 0, 0u });
+    IdState st0;
+    st0.init_cache = IdCache { kSentinel, 0, kSentinel, 0 };
+    st0.cache = st0.init_cache;
+    st0.global_head = kSentinel;
+    st0.num_ids = 0;
+    int32_t herr = 0;
+    for (int a = 0; a < H.num_arch; a++) {
+        if (!e->archs[a].singleton) continue;
+        Entity ent = idAcquire(nodes0.data(), st0, st0.init_cache, H.id_cap, &herr);
+        if (ent.id < 0) return MDR_ECAPACITY;
+        nodes0[ent.id].a = a;
+        nodes0[ent.id].b = 0;
+        std::vector<Entity> col((size_t)W * H.arch[a].stride, Entity { 0u, 0 });
+        std::vector<int32_t> ones(W, 1);
+        for (int w = 0; w < W; w++) col[(size_t)w * H.arch[a].stride] = ent;
+        REQ_CUDA(cudaMemcpy(H.arch[a].col[0], col.data(), col.size() * 8, cudaMemcpyHostToDevice));
+        REQ_CUDA(cudaMemcpy(H.arch[a].row_count, ones.data(), 4 * (size_t)W, cudaMemcpyHostToDevice));
+    }
+    if (st0.num_ids > 0) {
+        IdNode *d0 = e->dalloc<IdNode>(st0.num_ids, false);
+        REQ_CUDA(cudaMemcpy(d0, nodes0.data(), sizeof(IdNode) * (size_t)st0.num_ids, cudaMemcpyHostToDevice));
+        const int64_t total = (int64_t)W * st0.num_ids;
+        ecsBroadcastNodes<<<(unsigned)((total + 255) / 256), 256>>>(H.id_nodes, H.id_cap, d0, st0.num_ids, W);
+        REQ_CUDA(cudaGetLastError());
+        REQ_CUDA(cudaDeviceSynchronize());
+    }
+    {
+        std::vector<IdState> states(W, st0);
+        REQ_CUDA(cudaMemcpy(H.id_state, states.data(), sizeof(IdState) * (size_t)W, cudaMemcpyHostToDevice));
+    }
+
+    // Lower the graph: insertion order is the sorted order (see depsOk); resolve every
+    // query the way StateManager::makeQuery does (archetypes in id order).
+    H.num_nodes = (int32_t)e->nodes.size();
+    for (int ni = 0; ni < H.num_nodes; ni++) {
+        const HostNode &hn = e->nodes[ni];
+        NodeDev &N = H.node[ni];
+        N.kind = hn.kind; N.func = hn.func; N.arch = hn.arch; N.remap = hn.remap;
+        if (hn.kind == kNodeSort) {
+            N.key_col = colOf(e->archs[hn.arch], hn.key_comp);
+            SortScratch &S = H.sort[hn.arch];
+            if (!S.key[0]) {
+                const ArchDev &A = H.arch[hn.arch];
+                const size_t R = (size_t)W * A.stride;
+                int mb = 0;
+                for (int c = 0; c < A.num_cols; c++) mb = A.col_bytes[c] > mb ? A.col_bytes[c] : mb;
+                S.staging_bytes = (mb + 15) / 16 * 16;
+                S.key[0] = e->dalloc<uint32_t>(R, false); S.key[1] = e->dalloc<uint32_t>(R, false);
+                S.idx[0] = e->dalloc<int32_t>(R, false); S.idx[1] = e->dalloc<int32_t>(R, false);
+                S.staging = e->dalloc<char>(R * S.staging_bytes, false);
+            }
+        }
+        if (hn.kind != kNodeParallelFor) continue;
+        for (int a = 0; a < H.num_arch; a++) {
+            bool has = true;
+            for (int32_t c : hn.comps) has = has && colOf(e->archs[a], c) >= 0;
+            if (!has) continue;
+            if (N.num_match >= kMaxMatch) return MDR_ECAPACITY;
+            MatchDev &M = N.match[N.num_match++];
+            M.arch = a;
+            for (size_t k = 0; k < hn.comps.size(); k++) M.col[k] = colOf(e->archs[a], hn.comps[k]);
+        }
+    }
+    H.num_exports = (int32_t)e->exports.size();
+    for (int s = 0; s < H.num_exports; s++) {
+        const HostExport &hx = e->exports[s];
+        if (hx.arch < 0) return MDR_EINVAL;
+        ExportDev &X = H.exports[s];
+        const ArchDev &A = H.arch[hx.arch];
+        X.arch = hx.arch; X.col = colOf(e->archs[hx.arch], hx.comp); X.bytes = A.col_bytes[X.col];
+        X.fixed = (A.flags & MDR_ARCH_FIXED) ? 1 : 0;
+        if (X.fixed) {
+            X.buffer = A.col[X.col];   // fixed-size archetypes export in place (src/core/state.cpp:481-483)
+        } else {
+            X.buffer = e->dalloc<char>((size_t)W * A.stride * X.bytes);
+            X.offsets = e->dalloc<int64_t>((size_t)W + 1);
+        }
+    }
+    e->dev = e->dalloc<EcsDev>(1, false);
+    REQ_CUDA(cudaMemcpy(e->dev, &H, sizeof(H), cudaMemcpyHostToDevice));
+
+    int per_sm = 0;
+    REQ_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, ecsStepKernel, 32 * kWarpsPerBlock, 0));
+    cudaDeviceProp prop;
+    REQ_CUDA(cudaGetDeviceProperties(&prop, e->cfg.gpu_id));
+    long long grid = (long long)(per_sm > 0 ? per_sm : 1) * prop.multiProcessorCount;
+    const long long need = ((long long)W + kWarpsPerBlock - 1) / kWarpsPerBlock;
+    e->blocks = (int)(grid < need ? grid : need);
+    e->built = true;
+    e->exports_dirty = true;
+    return MDR_OK;
+}
+
+int32_t mdr_ecs_make_entities(mdr_ecs *e, int32_t arch, int32_t count)
+{
+    if (!e || !e->built) return e ? MDR_ESTATE : MDR_EINVAL;
+    if (arch < 0 || arch >= e->host.num_arch || count < 0) return MDR_EINVAL;
+    if (count == 0) return MDR_OK;
+    REQ_CUDA(cudaSetDevice(e->cfg.gpu_id));
+    std::vector<mdr_script_op> ops(count, mdr_script_op { MDR_OP_CREATE, arch, 0 });
+    mdr_script_op *d = nullptr;
+    REQ_CUDA(cudaMalloc(&d, sizeof(mdr_script_op) * ops.size()));
+    REQ_CUDA(cudaMemcpyAsync(d, ops.data(), sizeof(mdr_script_op) * ops.size(), cudaMemcpyHostToDevice, e->stream));
+    runScript(e, d, nullptr, count);
+    REQ_CUDA(cudaStreamSynchronize(e->stream));
+    REQ_CUDA(cudaFree(d));
+    return checkError(e);
+}
+
+int32_t mdr_ecs_script(mdr_ecs *e, const mdr_script_op *ops, const int32_t *offsets)
+{
+    if (!e || !ops || !offsets) return MDR_EINVAL;
+    if (!e->built) return MDR_ESTATE;
+    REQ_CUDA(cudaSetDevice(e->cfg.gpu_id));
+    const int W = e->host.num_worlds;
+    const int32_t total = offsets[W];
+    if (total <= 0) return MDR_OK;
+    mdr_script_op *d = nullptr;
+    int32_t *doff = nullptr;
+    REQ_CUDA(cudaMalloc(&d, sizeof(mdr_script_op) * (size_t)total));
+    REQ_CUDA(cudaMalloc(&doff, 4 * ((size_t)W + 1)));
+    REQ_CUDA(cudaMemcpyAsync(d, ops, sizeof(mdr_script_op) * (size_t)total, cudaMemcpyHostToDevice, e->stream));
+    REQ_CUDA(cudaMemcpyAsync(doff, offsets, 4 * ((size_t)W + 1), cudaMemcpyHostToDevice, e->stream));
+    runScript(e, d, doff, 0);
+    REQ_CUDA(cudaStreamSynchronize(e->stream));
+    REQ_CUDA(cudaFree(d));
+    REQ_CUDA(cudaFree(doff));
+    return checkError(e);
+}
+
+static int32_t columnCopy(mdr_ecs *e, int32_t arch, int32_t col, int32_t rows, void *host, bool to_device)
+{
+    if (!e || !host) return MDR_EINVAL;
+    if (!e->built) return MDR_ESTATE;
+    if (arch < 0 || arch >= e->host.num_arch) return MDR_EINVAL;
+    const ArchDev &A = e->host.arch[arch];
+    if (col < 0 || col >= A.num_cols || rows < 0 || rows > A.stride) return MDR_EINVAL;
+    if (rows == 0) return MDR_OK;
+    REQ_CUDA(cudaSetDevice(e->cfg.gpu_id));
+    const size_t nb = A.col_bytes[col];
+    if (to_device) {
+        REQ_CUDA(cudaMemcpy2DAsync(A.col[col], A.stride * nb, host, rows * nb, rows * nb, e->host.num_worlds,
+                                   cudaMemcpyHostToDevice, e->stream));
+        e->exports_dirty = true;
+    } else {
+        REQ_CUDA(cudaMemcpy2DAsync(host, rows * nb, A.col[col], A.stride * nb, rows * nb, e->host.num_worlds,
+                                   cudaMemcpyDeviceToHost, e->stream));
+    }
+    REQ_CUDA(cudaStreamSynchronize(e->stream));
+    return MDR_OK;
+}
+
+int32_t mdr_ecs_write_column(mdr_ecs *e, int32_t arch, int32_t col, int32_t rows, const void *host)
+{
+    return columnCopy(e, arch, col, rows, (void *)host, true);
+}
+
+int32_t mdr_ecs_read_column(mdr_ecs *e, int32_t arch, int32_t col, int32_t rows, void *host)
+{
+    return columnCopy(e, arch, col, rows, host, false);
+}
+
+int32_t mdr_ecs_row_counts(mdr_ecs *e, int32_t arch, int32_t *host)
+{
+    if (!e || !host) return MDR_EINVAL;
+    if (!e->built) return MDR_ESTATE;
+    if (arch < 0 || arch >= e->host.num_arch) return MDR_EINVAL;
+    REQ_CUDA(cudaSetDevice(e->cfg.gpu_id));
+    REQ_CUDA(cudaStreamSynchronize(e->stream));
+    REQ_CUDA(cudaMemcpy(host, e->host.arch[arch].row_count, 4 * (size_t)e->host.num_worlds, cudaMemcpyDeviceToHost));
+    return MDR_OK;
+}
+
+int32_t mdr_ecs_num_archetypes(mdr_ecs *e) { return e ? (int32_t)e->archs.size() : MDR_EINVAL; }
+int32_t mdr_ecs_num_columns(mdr_ecs *e, int32_t arch)
+{
+    return e && arch >= 0 && arch < (int32_t)e->archs.size() ? (int32_t)e->archs[arch].comps.size() + 1 : MDR_EINVAL;
+}
+int32_t mdr_ecs_column_bytes(mdr_ecs *e, int32_t arch, int32_t col)
+{
+    if (!e || arch < 0 || arch >= (int32_t)e->archs.size()) return MDR_EINVAL;
+    if (col == 0) return 8;
+    if (col < 0 || col > (int32_t)e->archs[arch].comps.size()) return MDR_EINVAL;
+    return e->comps[e->archs[arch].comps[col - 1]].bytes;
+}
+int32_t mdr_ecs_row_stride(mdr_ecs *e, int32_t arch)
+{
+    return e && e->built && arch >= 0 && arch < e->host.num_arch ? e->host.arch[arch].stride : MDR_EINVAL;
+}
+void *mdr_ecs_column_ptr(mdr_ecs *e, int32_t arch, int32_t col)
+{
+    if (!e || !e->built || arch < 0 || arch >= e->host.num_arch || col < 0 || col >= e->host.arch[arch].num_cols)
+        return nullptr;
+    return e->host.arch[arch].col[col];
+}
+
+int32_t mdr_ecs_id_capacity(mdr_ecs *e) { return e && e->built ? e->host.id_cap : MDR_EINVAL; }
+
+int32_t mdr_ecs_read_idmap(mdr_ecs *e, int32_t world, int32_t *a, int32_t *b, uint32_t *gen, int32_t state[10])
+{
+    if (!e || !a || !b || !gen || !state) return MDR_EINVAL;
+    if (!e->built) return MDR_ESTATE;
+    if (world < 0 || world >= e->host.num_worlds) return MDR_EINVAL;
+    REQ_CUDA(cudaSetDevice(e->cfg.gpu_id));
+    REQ_CUDA(cudaStreamSynchronize(e->stream));
+    IdState st;
+    REQ_CUDA(cudaMemcpy(&st, e->host.id_state + world, sizeof(st), cudaMemcpyDeviceToHost));
+    std::vector<IdNode> nodes(st.num_ids > 0 ? st.num_ids : 1);
+    if (st.num_ids > 0)
+        REQ_CUDA(cudaMemcpy(nodes.data(), e->host.id_nodes + (size_t)world * e->host.id_cap,
+                            sizeof(IdNode) * (size_t)st.num_ids, cudaMemcpyDeviceToHost));
+    for (int i = 0; i < st.num_ids; i++) { a[i] = nodes[i].a; b[i] = nodes[i].b; gen[i] = nodes[i].gen; }
+    memcpy(state, &st, sizeof(st));
+    return st.num_ids;
+}
+
+int32_t mdr_ecs_step_async(mdr_ecs *e, int32_t num_steps)
+{
+    if (!e || num_steps < 0) return MDR_EINVAL;
+    if (!e->built) return MDR_ESTATE;
+    if (num_steps == 0) return MDR_OK;
+    REQ_CUDA(cudaSetDevice(e->cfg.gpu_id));
+    closeTiming(e);
+    if (e->exports_dirty) refreshExports(e);
+    const bool staged = [&] {
+        for (int s = 0; s < e->host.num_exports; s++)
+            if (!e->host.exports[s].fixed) return true;
+        return false;
+    }();
+    if (!e->graph) {
+        // MWCudaExecutor's run graph (src/mw/cuda_exec.cpp:1519-1690):
+        // exportCopyIn -> megakernel -> exportBlockSums -> exportCopyOut
+        cudaGraph_t g = nullptr;
+        REQ_CUDA(cudaStreamBeginCapture(e->stream, cudaStreamCaptureModeThreadLocal));
+        if (staged) ecsExportCopy<<<(e->host.num_worlds + 7) / 8, 256, 0, e->stream>>>(e->dev, 0);
+        ecsStepKernel<<<e->blocks, 32 * kWarpsPerBlock, 0, e->stream>>>(e->dev);
+        if (staged) {
+            ecsExportOffsets<<<e->host.num_exports, 1024, 0, e->stream>>>(e->dev);
+            ecsExportCopy<<<(e->host.num_worlds + 7) / 8, 256, 0, e->stream>>>(e->dev, 1);
+        }
+        REQ_CUDA(cudaStreamEndCapture(e->stream, &g));
+        REQ_CUDA(cudaGraphInstantiate(&e->graph, g, 0));
+        REQ_CUDA(cudaGraphDestroy(g));
+    }
+    REQ_CUDA(cudaEventRecord(e->ev0, e->stream));
+    for (int s = 0; s < num_steps; s++) REQ_CUDA(cudaGraphLaunch(e->graph, e->stream));
+    REQ_CUDA(cudaEventRecord(e->ev1, e->stream));
+    e->timing_open = true;
+    e->pending_steps = num_steps;
+    return MDR_OK;
+}
+
+int32_t mdr_ecs_sync(mdr_ecs *e)
+{
+    if (!e) return MDR_EINVAL;
+    if (!e->built) return MDR_ESTATE;
+    REQ_CUDA(cudaSetDevice(e->cfg.gpu_id));
+    REQ_CUDA(cudaStreamSynchronize(e->stream));
+    closeTiming(e);
+    return checkError(e);
+}
+
+int32_t mdr_ecs_step(mdr_ecs *e, int32_t num_steps)
+{
+    int32_t rc = mdr_ecs_step_async(e, num_steps);
+    if (rc != MDR_OK) return rc;
+    return mdr_ecs_sync(e);
+}
+
+void *mdr_ecs_stream(mdr_ecs *e) { return e ? (void *)e->stream : nullptr; }
+
+float mdr_ecs_step_ms(mdr_ecs *e, int32_t *steps)
+{
+    if (!e) return -1.f;
+    closeTiming(e);
+    const int n = e->timed_steps;
+    const double ms = e->timed_ms;
+    e->timed_steps = 0;
+    e->timed_ms = 0;
+    if (steps) *steps = n;
+    return n > 0 ? (float)(ms / n) : -1.f;
+}
+
+int32_t mdr_ecs_launches_per_step(mdr_ecs *e)
+{
+    if (!e || !e->built) return MDR_EINVAL;
+    for (int s = 0; s < e->host.num_exports; s++)
+        if (!e->host.exports[s].fixed) return 4;
+    return 1;
+}
+
+void *mdr_ecs_get_exported(mdr_ecs *e, int32_t slot)
+{
+    if (!e || !e->built || slot < 0 || slot >= e->host.num_exports) return nullptr;
+    return e->host.exports[slot].buffer;
+}
+
+int64_t mdr_ecs_export_rows(mdr_ecs *e, int32_t slot)
+{
+    if (!e || !e->built || slot < 0 || slot >= e->host.num_exports) return MDR_EINVAL;
+    REQ_CUDA(cudaSetDevice(e->cfg.gpu_id));
+    const ExportDev &X = e->host.exports[slot];
+    if (X.fixed) return (int64_t)e->host.num_worlds * e->host.arch[X.arch].stride;
+    if (e->exports_dirty) refreshExports(e);
+    REQ_CUDA(cudaStreamSynchronize(e->stream));
+    int64_t total = 0;
+    REQ_CUDA(cudaMemcpy(&total, X.offsets + e->host.num_worlds, 8, cudaMemcpyDeviceToHost));
+    return total;
+}
+
+int64_t mdr_ecs_read_exported(mdr_ecs *e, int32_t slot, void *host, int64_t max_bytes)
+{
+    if (!e || !host) return MDR_EINVAL;
+    const int64_t rows = mdr_ecs_export_rows(e, slot);
+    if (rows < 0) return rows;
+    const int64_t bytes = rows * e->host.exports[slot].bytes;
+    if (bytes > max_bytes) return MDR_ECAPACITY;
+    REQ_CUDA(cudaStreamSynchronize(e->stream));
+    if (bytes) REQ_CUDA(cudaMemcpy(host, e->host.exports[slot].buffer, (size_t)bytes, cudaMemcpyDeviceToHost));
+    return bytes;
+}
+
+int32_t mdr_ecs_export_bytes_per_row(mdr_ecs *e, int32_t slot)
+{
+    if (!e || !e->built || slot < 0 || slot >= e->host.num_exports) return MDR_EINVAL;
+    return e->host.exports[slot].bytes;
+}
+
+// ---- the built-in worlds: what a user's registerTypes / setupTasks / world
+// constructor do, expressed through the C ABI above --------------------------------
+int32_t mdr_app_setup(mdr_ecs *e, int32_t app, const int32_t *params, int32_t nparams)
+{
+    if (!e || app < 0 || app >= MDR_NUM_APPS) return MDR_EINVAL;
+    if (e->built) return MDR_ESTATE;
+    auto P = [&](int i, int32_t dflt) { return params && i < nparams ? params[i] : dflt; };
+    using namespace mdr::ecs::apps;
+    e->cfg.app = app;
+    int32_t rc = MDR_OK;
+    auto ok = [&](int32_t v) { if (v < 0 && rc == MDR_OK) rc = v; return v; };
+    switch (app) {
+    case MDR_APP_SCRIPT: {
+        const int32_t cap = P(1, 4096);
+        const int32_t A = ok(mdr_ecs_register_component(e, 4, 4)), B = ok(mdr_ecs_register_component(e, 12, 4)),
+                      C = ok(mdr_ecs_register_component(e, 16, 16));
+        const int32_t x[] = { A }, y[] = { A, B }, z[] = { A, B, C };
+        ok(mdr_ecs_register_archetype(e, x, 1, cap, 0));
+        ok(mdr_ecs_register_archetype(e, y, 2, cap, 0));
+        ok(mdr_ecs_register_archetype(e, z, 3, cap, 0));
+        ok(mdr_ecs_register_archetype(e, x, 1, cap, 0));
+        if (P(0, 1)) ok(mdr_ecs_register_singleton(e, 4, 4));
+        if (e->cfg.max_script_handles <= 0) e->cfg.max_script_handles = P(2, 1 << 16);
+        if (rc == MDR_OK) rc = mdr_ecs_build(e);
+    } break;
+    case MDR_APP_TASKGRAPH: {
+        const int32_t n = P(0, 100);
+        const int32_t pos = ok(mdr_ecs_register_component(e, 12, 4)), rot = ok(mdr_ecs_register_component(e, 16, 4));
+        const int32_t pr[] = { pos, rot };
+        const int32_t sphere = ok(mdr_ecs_register_archetype(e, pr, 2, n, 0));
+        const int32_t agent = ok(mdr_ecs_register_archetype(e, pr, 2, 1, 0));
+        ok(mdr_ecs_export_column(e, agent, pos, 0));    // simple.cpp:46-47
+        ok(mdr_ecs_export_column(e, agent, rot, 1));
+        const int32_t q[] = { pos };
+        const int32_t n0 = ok(mdr_ecs_add_parallel_for(e, kTgDrift, q, 1, nullptr, 0));
+        ok(mdr_ecs_add_parallel_for(e, kTgClamp, q, 1, &n0, 1));
+        if (rc == MDR_OK) rc = mdr_ecs_build(e);
+        if (rc == MDR_OK) rc = mdr_ecs_make_entities(e, sphere, n);
+        if (rc == MDR_OK) rc = mdr_ecs_make_entities(e, agent, 1);
+    } break;
+    case MDR_APP_FANOUT: {
+        const int32_t n = P(0, 100), max_cand = P(1, n * (n - 1) / 2 < 4096 ? n * (n - 1) / 2 : 4096);
+        const int32_t pos = ok(mdr_ecs_register_component(e, 12, 4)), rot = ok(mdr_ecs_register_component(e, 16, 4)),
+                      box = ok(mdr_ecs_register_component(e, 24, 4)), hit = ok(mdr_ecs_register_component(e, 4, 4)),
+                      cand = ok(mdr_ecs_register_component(e, 16, 4)), key = ok(mdr_ecs_register_component(e, 4, 4));
+        const int32_t oc[] = { pos, rot, box, hit }, cc[] = { cand, key };
+        const int32_t obj = ok(mdr_ecs_register_archetype(e, oc, 4, n, 0));
+        const int32_t tmp = ok(mdr_ecs_register_archetype(e, cc, 2, max_cand > 0 ? max_cand : 1, 0));
+        ok(mdr_ecs_export_column(e, obj, hit, 0));
+        const int32_t q1[] = { pos }, q2[] = { pos, rot, box }, q3[] = { 0, box }, q4[] = { cand };
+        int32_t d = ok(mdr_ecs_add_clear_tmp(e, tmp, nullptr, 0));
+        d = ok(mdr_ecs_add_parallel_for(e, kFanMove, q1, 1, &d, 1));
+        d = ok(mdr_ecs_add_parallel_for(e, kFanBox, q2, 3, &d, 1));
+        d = ok(mdr_ecs_add_parallel_for(e, kFanOverlap, q3, 2, &d, 1));
+        d = ok(mdr_ecs_add_sort(e, tmp, key, 0, &d, 1));
+        ok(mdr_ecs_add_parallel_for(e, kFanConsume, q4, 1, &d, 1));
+        if (rc == MDR_OK) rc = mdr_ecs_build(e);
+        if (rc == MDR_OK) rc = mdr_ecs_make_entities(e, obj, n);
+    } break;
+    case MDR_APP_FVS: {
+        const int32_t nd = P(0, 50), nk = P(1, 200);
+        const int32_t pos = ok(mdr_ecs_register_component(e, 12, 4)), hp = ok(mdr_ecs_register_component(e, 4, 4)),
+                      act = ok(mdr_ecs_register_component(e, 4, 4)), mana = ok(mdr_ecs_register_component(e, 4, 4)),
+                      quiv = ok(mdr_ecs_register_component(e, 4, 4)), cl = ok(mdr_ecs_register_component(e, 12, 4)),
+                      key = ok(mdr_ecs_register_component(e, 4, 4));
+        const int32_t dc[] = { pos, hp, act, mana }, kc[] = { pos, hp, act, quiv }, tc[] = { cl, key };
+        // respawning keeps the totals constant; leave head-room for a custom graph
+        const int32_t dragon = ok(mdr_ecs_register_archetype(e, dc, 4, nd + 16, 0));
+        const int32_t knight = ok(mdr_ecs_register_archetype(e, kc, 4, nk + 16, 0));
+        const int32_t tracker = ok(mdr_ecs_register_archetype(e, tc, 2, nd + nk, 0));
+        const int32_t game = ok(mdr_ecs_register_singleton(e, 4, 4));
+        ok(mdr_ecs_export_column(e, dragon, hp, 0));
+        ok(mdr_ecs_export_column(e, knight, pos, 1));
+        const int32_t q0[] = { 0, pos, act }, q1[] = { 0, act, mana }, q2[] = { 0, act, quiv }, q3[] = { 0, hp },
+                      q4[] = { cl }, q5[] = { (int32_t)e->comps.size() - 1 };
+        int32_t d = ok(mdr_ecs_add_parallel_for(e, kFvsAction, q0, 3, nullptr, 0));
+        d = ok(mdr_ecs_add_parallel_for(e, kFvsCaster, q1, 3, &d, 1));
+        d = ok(mdr_ecs_add_parallel_for(e, kFvsArcher, q2, 3, &d, 1));
+        d = ok(mdr_ecs_add_parallel_for(e, kFvsMark, q3, 2, &d, 1));
+        d = ok(mdr_ecs_add_sort(e, tracker, key, 0, &d, 1));
+        d = ok(mdr_ecs_add_parallel_for(e, kFvsDestroy, q4, 1, &d, 1));
+        d = ok(mdr_ecs_add_parallel_for(e, kFvsRespawn, q4, 1, &d, 1));
+        d = ok(mdr_ecs_add_clear_tmp(e, tracker, &d, 1));
+        ok(mdr_ecs_add_parallel_for(e, kFvsTick, q5, 1, &d, 1));
+        (void)game;
+        if (rc == MDR_OK) rc = mdr_ecs_build(e);
+        if (rc == MDR_OK) rc = mdr_ecs_make_entities(e, dragon, nd);
+        if (rc == MDR_OK) rc = mdr_ecs_make_entities(e, knight, nk);
+    } break;
+    }
+    return rc;
+}
+
+}  // extern "C"

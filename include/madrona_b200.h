@@ -16,6 +16,8 @@
 #define MADRONA_B200_H
 #include <stdint.h>
 
+#include "madrona_b200_apps.h"
+
 #ifdef __cplusplus
 extern "C" {
 #endif
@@ -159,6 +161,95 @@ int32_t mdr_phys_launch_info(mdr_phys *p, int32_t info[6]);
 /* Average device time of the step kernel, in ms, over the launches since the
  * last call (CUDA events on the executor's stream); <0 if none were timed. */
 float mdr_phys_kernel_ms(mdr_phys *p, int32_t *launches);
+
+/* ---- ECS state layer + task graph -------------------------------------------
+ * Stands in for the registration / graph-building / executor surface a world
+ * reaches through ECSRegistry (include/madrona/state.hpp:109-134), TaskGraph::
+ * Builder (include/madrona/taskgraph.hpp:15-97) and MWCudaExecutor
+ * (include/madrona/mw_gpu.hpp:55-76). Every world has its own entity id space
+ * (one StateManager per world, src/mw/device/include/madrona/mw_gpu_entry.hpp:
+ * 29-31). Archetype tables are [num_worlds][row_stride][bytes] per column in
+ * HBM; ids, generations, row order and row counts follow the reference's
+ * sequential semantics exactly. System functions are compiled ahead of time
+ * and named by func id (gpu_ecs_madrona_b200/csrc/ecs_apps.cuh), where the
+ * reference JIT-compiles them and assigns ids by scanning PTX
+ * (src/mw/cuda_exec.cpp:596-675). Phases: register / add nodes -> build ->
+ * make entities, write columns -> step. */
+typedef struct mdr_ecs_config {
+    int32_t num_worlds;
+    int32_t first_world;          /* global index of world 0 (multi-GPU sharding; seeds)   */
+    int32_t gpu_id;
+    int32_t ids_per_world;        /* entity-id capacity per world; 0: sized from the tables */
+    int32_t max_script_handles;   /* handle slots per world for mdr_ecs_script; 0: none      */
+    int32_t app;                  /* set by mdr_app_setup                                     */
+} mdr_ecs_config;
+typedef struct mdr_ecs mdr_ecs;
+enum { MDR_ARCH_FIXED = 1 };      /* registerFixedSizeArchetype: exports alias the table    */
+enum { MDR_COMP_ENTITY = 0 };     /* component id of Entity in queries                       */
+
+int32_t mdr_ecs_create(const mdr_ecs_config *cfg, mdr_ecs **out);
+void mdr_ecs_destroy(mdr_ecs *e);
+/* ECSRegistry::registerComponent<T>: returns the component id (registration
+ * order, Entity = 0). Sizes are multiples of 4 bytes. */
+int32_t mdr_ecs_register_component(mdr_ecs *e, int32_t bytes, int32_t align);
+/* registerArchetype<Archetype<Cs...>> / registerFixedSizeArchetype: returns the
+ * archetype id; max_rows is the per-world row capacity. */
+int32_t mdr_ecs_register_archetype(mdr_ecs *e, const int32_t *comps, int32_t n, int32_t max_rows, int32_t flags);
+/* registerSingleton<T> (include/madrona/state.inl:171-187): component + one-row
+ * archetype + one entity per world from the init id cache. Returns the archetype id. */
+int32_t mdr_ecs_register_singleton(mdr_ecs *e, int32_t bytes, int32_t align);
+/* exportColumn<Archetype, Component>(slot) */
+int32_t mdr_ecs_export_column(mdr_ecs *e, int32_t arch, int32_t comp, int32_t slot);
+/* builder.addToGraph<ParallelForNode<Ctx, fn, Cs...>>(deps); returns the node id */
+int32_t mdr_ecs_add_parallel_for(mdr_ecs *e, int32_t func, const int32_t *comps, int32_t n, const int32_t *deps,
+                                 int32_t ndeps);
+/* ClearTmpNode<Archetype>, ResetTmpAllocNode (include/madrona/taskgraph.inl:83-101) */
+int32_t mdr_ecs_add_clear_tmp(mdr_ecs *e, int32_t arch, const int32_t *deps, int32_t ndeps);
+int32_t mdr_ecs_add_reset_tmp_alloc(mdr_ecs *e, const int32_t *deps, int32_t ndeps);
+/* SortArchetypeNode (src/mw/device/sort_archetype.cpp:1281-1392): stable sort of
+ * every world's rows by a 4-byte unsigned key component; remap_entities patches
+ * the id map for archetypes whose rows carry entity ids. */
+int32_t mdr_ecs_add_sort(mdr_ecs *e, int32_t arch, int32_t key_comp, int32_t remap_entities, const int32_t *deps,
+                         int32_t ndeps);
+/* Builder::build() + state allocation (src/mw/cuda_exec.cpp:1090-1355) */
+int32_t mdr_ecs_build(mdr_ecs *e);
+/* World-constructor loops: `count` x makeEntityNow<arch>() in every world. */
+int32_t mdr_ecs_make_entities(mdr_ecs *e, int32_t arch, int32_t count);
+/* Immediate-mode ops per world (script app): ops of world w are
+ * ops[offsets[w] .. offsets[w+1]). */
+int32_t mdr_ecs_script(mdr_ecs *e, const mdr_script_op *ops, const int32_t *offsets);
+/* Host copy of a column, [num_worlds][rows][bytes] (rows <= row stride). */
+int32_t mdr_ecs_write_column(mdr_ecs *e, int32_t arch, int32_t col, int32_t rows, const void *host);
+int32_t mdr_ecs_read_column(mdr_ecs *e, int32_t arch, int32_t col, int32_t rows, void *host);
+int32_t mdr_ecs_row_counts(mdr_ecs *e, int32_t arch, int32_t *host);
+int32_t mdr_ecs_num_archetypes(mdr_ecs *e);
+int32_t mdr_ecs_num_columns(mdr_ecs *e, int32_t arch);
+int32_t mdr_ecs_column_bytes(mdr_ecs *e, int32_t arch, int32_t col);
+int32_t mdr_ecs_row_stride(mdr_ecs *e, int32_t arch);
+void *mdr_ecs_column_ptr(mdr_ecs *e, int32_t arch, int32_t col);
+int32_t mdr_ecs_id_capacity(mdr_ecs *e);
+/* Entity id map of one world (arrays of mdr_ecs_id_capacity entries); state[10] =
+ * init cache {free head, free count, overflow head, overflow count}, world cache
+ * {same}, global free head, number of ids. Returns the number of ids. */
+int32_t mdr_ecs_read_idmap(mdr_ecs *e, int32_t world, int32_t *a, int32_t *b, uint32_t *gen, int32_t state[10]);
+/* MWCudaExecutor::run(): export copy-in, the task-graph megakernel, export offsets,
+ * export copy-out -- one CUDA graph launch per step. */
+int32_t mdr_ecs_step(mdr_ecs *e, int32_t num_steps);
+int32_t mdr_ecs_step_async(mdr_ecs *e, int32_t num_steps);
+int32_t mdr_ecs_sync(mdr_ecs *e);
+void *mdr_ecs_stream(mdr_ecs *e);
+float mdr_ecs_step_ms(mdr_ecs *e, int32_t *steps);
+int32_t mdr_ecs_launches_per_step(mdr_ecs *e);
+/* getExported(slot): device pointer; staged exports hold mdr_ecs_export_rows rows
+ * (world-major concatenation), fixed ones alias the table. */
+void *mdr_ecs_get_exported(mdr_ecs *e, int32_t slot);
+int64_t mdr_ecs_export_rows(mdr_ecs *e, int32_t slot);
+int32_t mdr_ecs_export_bytes_per_row(mdr_ecs *e, int32_t slot);
+/* Host copy of an exported column; returns the bytes copied. */
+int64_t mdr_ecs_read_exported(mdr_ecs *e, int32_t slot, void *host, int64_t max_bytes);
+/* registerTypes + setupTasks + world constructors of a built-in world
+ * (MDR_APP_* of madrona_b200_apps.h). */
+int32_t mdr_app_setup(mdr_ecs *e, int32_t app, const int32_t *params, int32_t nparams);
 
 const char *mdr_version(void);
 int32_t mdr_device_count(void);

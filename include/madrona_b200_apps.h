@@ -18,9 +18,9 @@
 #include <stdint.h>
 
 #if defined(__CUDACC__)
-#define MDR_HD __host__ __device__ static inline
+#define MDR_APP_FN __host__ __device__ static inline
 #else
-#define MDR_HD static inline
+#define MDR_APP_FN static inline
 #endif
 
 enum { MDR_APP_SCRIPT = 0, MDR_APP_TASKGRAPH = 1, MDR_APP_FANOUT = 2, MDR_APP_FVS = 3, MDR_NUM_APPS = 4 };
@@ -35,12 +35,12 @@ typedef struct { mdr_entity e; int32_t kind; } mdr_cleanup; /* 12 B            *
 
 /* ---- counter-based random numbers (replaces fvs.cpp:19-25's thread_local
  * mt19937, whose stream depends on thread assignment) ----------------------- */
-MDR_HD uint32_t mdr_fmix(uint32_t h)
+MDR_APP_FN uint32_t mdr_fmix(uint32_t h)
 {
     h ^= h >> 16; h *= 0x85ebca6bu; h ^= h >> 13; h *= 0xc2b2ae35u; h ^= h >> 16;
     return h;
 }
-MDR_HD uint32_t mdr_hash4(uint32_t a, uint32_t b, uint32_t c, uint32_t d)
+MDR_APP_FN uint32_t mdr_hash4(uint32_t a, uint32_t b, uint32_t c, uint32_t d)
 {
     uint32_t h = mdr_fmix(a * 0x9e3779b1u + 0x7f4a7c15u);
     h = mdr_fmix(h ^ (b * 0x85ebca77u + 0x165667b1u));
@@ -48,8 +48,8 @@ MDR_HD uint32_t mdr_hash4(uint32_t a, uint32_t b, uint32_t c, uint32_t d)
     h = mdr_fmix(h ^ (d * 0x27d4eb2du + 0x9e3779b9u));
     return h;
 }
-MDR_HD float mdr_u01(uint32_t h) { return (float)(h >> 8) * (1.0f / 16777216.0f); }
-MDR_HD float mdr_clampf(float v, float lo, float hi) { return v < lo ? lo : (hi < v ? hi : v); }
+MDR_APP_FN float mdr_u01(uint32_t h) { return (float)(h >> 8) * (1.0f / 16777216.0f); }
+MDR_APP_FN float mdr_clampf(float v, float lo, float hi) { return v < lo ? lo : (hi < v ? hi : v); }
 
 /* World bounds of all three configs (fvs.cpp:52-55, simple_taskgraph init). */
 #define MDR_BOUNDS_MIN_X (-10.f)
@@ -59,7 +59,7 @@ MDR_HD float mdr_clampf(float v, float lo, float hi) { return v < lo ? lo : (hi 
 #define MDR_BOUNDS_MAX_Y (10.f)
 #define MDR_BOUNDS_MAX_Z (10.f)
 
-MDR_HD mdr_vec3 mdr_random_position(uint32_t h)
+MDR_APP_FN mdr_vec3 mdr_random_position(uint32_t h)
 {
     mdr_vec3 p;
     p.x = MDR_BOUNDS_MIN_X + (MDR_BOUNDS_MAX_X - MDR_BOUNDS_MIN_X) * mdr_u01(mdr_fmix(h ^ 0x1111u));
@@ -70,14 +70,14 @@ MDR_HD mdr_vec3 mdr_random_position(uint32_t h)
 
 /* ================= config 1: simple_taskgraph ============================== */
 /* One node that moves (so that clamping has work to do), one that clamps. */
-MDR_HD void mdr_tg_drift(mdr_vec3 *p)
+MDR_APP_FN void mdr_tg_drift(mdr_vec3 *p)
 {
     float x = p->x, y = p->y;
     p->x = x + 0.05f * y;
     p->y = y - 0.05f * x;
     p->z = p->z + 0.01f;
 }
-MDR_HD void mdr_tg_clamp(mdr_vec3 *p)   /* simple.cpp:22-35 */
+MDR_APP_FN void mdr_tg_clamp(mdr_vec3 *p)   /* simple.cpp:22-35 */
 {
     p->x = mdr_clampf(p->x, MDR_BOUNDS_MIN_X, MDR_BOUNDS_MAX_X);
     p->y = mdr_clampf(p->y, MDR_BOUNDS_MIN_Y, MDR_BOUNDS_MAX_Y);
@@ -85,16 +85,16 @@ MDR_HD void mdr_tg_clamp(mdr_vec3 *p)   /* simple.cpp:22-35 */
 }
 
 /* ================= config 2: fan-out ======================================= */
-MDR_HD void mdr_fan_move(mdr_vec3 *p)
+MDR_APP_FN void mdr_fan_move(mdr_vec3 *p)
 {
     float x = p->x, y = p->y;
     p->x = mdr_clampf(x + 0.02f * y, MDR_BOUNDS_MIN_X, MDR_BOUNDS_MAX_X);
     p->y = mdr_clampf(y - 0.02f * x, MDR_BOUNDS_MIN_Y, MDR_BOUNDS_MAX_Y);
 }
-MDR_HD float mdr_absf(float v) { return v < 0.f ? -v : v; }
+MDR_APP_FN float mdr_absf(float v) { return v < 0.f ? -v : v; }
 /* World box of the +-1 cube under (rotation, translation): simple_jobs
  * simple.cpp:60-94 restated with the rotation-matrix extents. */
-MDR_HD void mdr_fan_box(const mdr_vec3 *p, const mdr_quat *q, mdr_box *out)
+MDR_APP_FN void mdr_fan_box(const mdr_vec3 *p, const mdr_quat *q, mdr_box *out)
 {
     float x2 = q->x * q->x, y2 = q->y * q->y, z2 = q->z * q->z;
     float xy = q->x * q->y, xz = q->x * q->z, yz = q->y * q->z;
@@ -108,12 +108,12 @@ MDR_HD void mdr_fan_box(const mdr_vec3 *p, const mdr_quat *q, mdr_box *out)
     out->mn[0] = p->x - ex; out->mn[1] = p->y - ey; out->mn[2] = p->z - ez;
     out->mx[0] = p->x + ex; out->mx[1] = p->y + ey; out->mx[2] = p->z + ez;
 }
-MDR_HD int mdr_box_overlap(const mdr_box *a, const mdr_box *b)   /* math.hpp:999-1007, strict */
+MDR_APP_FN int mdr_box_overlap(const mdr_box *a, const mdr_box *b)   /* math.hpp:999-1007, strict */
 {
     return a->mn[0] < b->mx[0] && b->mn[0] < a->mx[0] && a->mn[1] < b->mx[1] && b->mn[1] < a->mx[1] &&
            a->mn[2] < b->mx[2] && b->mn[2] < a->mx[2];
 }
-MDR_HD uint32_t mdr_fan_key(int32_t row_a, int32_t row_b) { return ((uint32_t)row_a << 16) | (uint32_t)row_b; }
+MDR_APP_FN uint32_t mdr_fan_key(int32_t row_a, int32_t row_b) { return ((uint32_t)row_a << 16) | (uint32_t)row_b; }
 
 /* ================= config 4: fantasy_vs ==================================== */
 #define MDR_FVS_DT (1.f / 60.f)
@@ -131,7 +131,7 @@ enum { MDR_FVS_DRAGON = 0, MDR_FVS_KNIGHT = 1 };   /* archetype ids, registratio
 enum { MDR_FVS_S_ACTION = 1, MDR_FVS_S_MOVE = 2, MDR_FVS_S_CAST = 3, MDR_FVS_S_SHOOT = 4, MDR_FVS_S_SPAWN = 5 };
 
 /* fvs.cpp:111-152. Returns nothing; updates pos / remaining time in place. */
-MDR_HD void mdr_fvs_action_select(uint32_t world, uint32_t tick, int32_t id, mdr_vec3 *pos, float *remaining)
+MDR_APP_FN void mdr_fvs_action_select(uint32_t world, uint32_t tick, int32_t id, mdr_vec3 *pos, float *remaining)
 {
     if (*remaining > 0.f) { *remaining = *remaining - MDR_FVS_DT; return; }
     if (mdr_u01(mdr_hash4(world, tick, (uint32_t)id, MDR_FVS_S_ACTION)) <= 0.5f) {
@@ -156,7 +156,7 @@ MDR_HD void mdr_fvs_action_select(uint32_t world, uint32_t tick, int32_t id, mdr
 }
 /* fvs.cpp:154-196, first half: mana bookkeeping; returns 1 when the caster
  * fires this tick and writes the blast centre. */
-MDR_HD int mdr_fvs_caster(uint32_t world, uint32_t tick, int32_t id, float *remaining, float *mp, mdr_vec3 *target)
+MDR_APP_FN int mdr_fvs_caster(uint32_t world, uint32_t tick, int32_t id, float *remaining, float *mp, mdr_vec3 *target)
 {
     *mp = *mp + MDR_FVS_MANA_REGEN * MDR_FVS_DT;
     if (*remaining > 0.f) return 0;
@@ -166,13 +166,13 @@ MDR_HD int mdr_fvs_caster(uint32_t world, uint32_t tick, int32_t id, float *rema
     *remaining = MDR_FVS_CAST_TIME;
     return 1;
 }
-MDR_HD int mdr_fvs_in_blast(const mdr_vec3 *target, const mdr_vec3 *pos)
+MDR_APP_FN int mdr_fvs_in_blast(const mdr_vec3 *target, const mdr_vec3 *pos)
 {
     float dx = target->x - pos->x, dy = target->y - pos->y, dz = target->z - pos->z;
     return ((dx * dx + dy * dy) + dz * dz) <= MDR_FVS_BLAST_RADIUS * MDR_FVS_BLAST_RADIUS;
 }
 /* fvs.cpp:198-223: returns the dragon row hit, or -1. */
-MDR_HD int32_t mdr_fvs_archer(uint32_t world, uint32_t tick, int32_t id, float *remaining, int32_t *arrows,
+MDR_APP_FN int32_t mdr_fvs_archer(uint32_t world, uint32_t tick, int32_t id, float *remaining, int32_t *arrows,
                               int32_t num_dragons)
 {
     if (*remaining > 0.f || *arrows == 0 || num_dragons == 0) return -1;
@@ -181,9 +181,9 @@ MDR_HD int32_t mdr_fvs_archer(uint32_t world, uint32_t tick, int32_t id, float *
     *remaining = MDR_FVS_SHOOT_TIME;
     return target;
 }
-MDR_HD uint32_t mdr_fvs_cleanup_key(uint32_t archetype, int32_t row) { return (archetype << 16) | (uint32_t)row; }
+MDR_APP_FN uint32_t mdr_fvs_cleanup_key(uint32_t archetype, int32_t row) { return (archetype << 16) | (uint32_t)row; }
 /* Stats of a respawned unit (replaces Game::Game's distributions, fvs.cpp:86-109). */
-MDR_HD void mdr_fvs_spawn(uint32_t world, uint32_t tick, int32_t old_id, int32_t kind, mdr_vec3 *pos, int32_t *hp,
+MDR_APP_FN void mdr_fvs_spawn(uint32_t world, uint32_t tick, int32_t old_id, int32_t kind, mdr_vec3 *pos, int32_t *hp,
                           float *mp, int32_t *arrows)
 {
     uint32_t h = mdr_hash4(world, tick, (uint32_t)old_id, MDR_FVS_S_SPAWN);
@@ -204,7 +204,7 @@ enum {
     MDR_OP_TMP = 4,         /* b = value tag: Context::makeTemporary<T>               */
     MDR_OP_CLEAR_TMP = 5    /* Context::clearTemporaries<T>                            */
 };
-MDR_HD void mdr_script_payload(int32_t v, float b[3], float c[4])
+MDR_APP_FN void mdr_script_payload(int32_t v, float b[3], float c[4])
 {
     b[0] = (float)v; b[1] = (float)v + 0.5f; b[2] = -(float)v;
     c[0] = (float)v * 2.f; c[1] = 1.f; c[2] = (float)v * 0.25f; c[3] = -1.f;
