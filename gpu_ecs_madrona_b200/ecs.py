@@ -248,7 +248,7 @@ class EcsExecutor(EcsRegistry):
             for (arch, col), data in ecs_apps.initial_columns(app, num_worlds, self.params, first_world).items():
                 self.write_column_all(arch, col, data)
 
-    # the oracle's per-world accessors, so tests can snapshot both sides with one routine
+    # whole-state accessor used by the parity tests
     def read_world_columns(self):
         """{(arch, col): [W, stride, bytes]} of every column, one device copy each."""
         return {(a, c): self.read_column_all(a, c) for a in range(self.num_archetypes)
