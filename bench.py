@@ -149,9 +149,9 @@ def run_ours(args):
 
     from gpu_ecs_madrona_b200 import phys, scenes
     W = args.worlds_per_gpu
-    sc = scenes.collisions64(W, world_offset=rank * W)
+    sc = scenes.collisions64(W, world_offset=rank * W, max_contacts=args.max_contacts)
     ex = phys.PhysExecutor(sc, gpu_id=local, block_threads=args.threads,
-                           worlds_per_block=args.worlds_per_block)
+                           worlds_per_block=args.worlds_per_block, smem_contacts=args.smem_contacts)
     info = ex.launch_info()
 
     def barrier():
@@ -264,6 +264,8 @@ def main():
     ap.add_argument("--worlds-per-gpu", type=int, default=16384)
     ap.add_argument("--threads", type=int, default=0, help="threads per world (0: library default)")
     ap.add_argument("--worlds-per-block", type=int, default=0)
+    ap.add_argument("--smem-contacts", type=int, default=0, help="contact slots in shared memory (0: default)")
+    ap.add_argument("--max-contacts", type=int, default=640, help="candidate-pair capacity per world (SURVEY 8d: 640)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     args = ap.parse_args()
     if args.impl == "reference":
