@@ -81,7 +81,7 @@ def run(name, worlds, steps, warmup, no_cpu):
                          "frac": Abytes * W / (ms * 1e-3) / 1e9 / peak, "algorithmic_bytes_per_world_step": Abytes,
                          "kernel": "ecsStepKernel (+export kernels)"}}
     if not no_cpu:
-        line["cpu_baseline"] = cpu_baseline(app, min(steps, 40), min(warmup, 5), 64)
+        line["cpu_baseline"] = cpu_baseline(app, min(steps, 40), min(warmup, 5), 8)
     ex.close()
     print(json.dumps(line))
 

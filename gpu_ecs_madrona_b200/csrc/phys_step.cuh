@@ -8,11 +8,92 @@
 
 namespace mdr {
 
+// ------------------------------------------------- dense solver lanes -------
+// Contacts of one dependency level commute exactly, whichever thread solves
+// them. Per substep the block gathers the contacts of ALL its world slots into
+// one list bucketed by level, and every level is then solved by as few warps as
+// it has contacts (instead of every world slot walking its own pair list with
+// mostly idle lanes, level after level). Levels nobody has cost nothing, not
+// even a barrier. Falls back to the per-slot walk when a level is deeper than
+// kDenseLevels or the block holds more than kDenseItems contacts.
+constexpr int kDenseLevels = 30;
+constexpr int kDenseItems = 1024;
+constexpr int kDenseSlots = 16;
+struct BlockSolve {
+    int32_t cnt[32];                  // per level (index 31: deeper than kDenseLevels)
+    int32_t off[33];
+    int32_t dense;
+    uint16_t items[kDenseItems];      // world slot << 10 | pair slot
+    WorldView views[kDenseSlots];
+};
+
+#if defined(__CUDA_ARCH__)
+// All threads of the block; the contacts of this substep are final and a block
+// barrier has passed since they were written. Returns the block-uniform verdict.
+__device__ __forceinline__ bool buildLevelLists(const BlockCtx &c, const WorldView &v, BlockSolve *bs, int slot,
+                                                int max_level)
+{
+    const int t = threadIdx.x;
+    if (t < 32) bs->cnt[t] = 0;
+    __syncthreads();
+    const int np = v.misc[0];
+    for (int i = c.tid(); i < np; i += c.nthreads()) {
+        if (contactSlot(v, i)->hdr == 0) continue;
+        const int lv = (int)(v.pairs[i] >> 20);
+        atomicAdd(&bs->cnt[lv <= kDenseLevels ? lv : 31], 1);
+    }
+    __syncthreads();
+    if (t < 32) {
+        const int x = bs->cnt[t];
+        int incl = x;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const int y = __shfl_up_sync(0xffffffffu, incl, d);
+            if (t >= d) incl += y;
+        }
+        bs->off[t] = incl - x;
+        bs->cnt[t] = 0;
+        if (t == 31) {
+            bs->off[32] = incl;
+            bs->dense = x == 0 && incl <= kDenseItems && max_level <= kDenseLevels;
+        }
+    }
+    __syncthreads();
+    if (!bs->dense) return false;
+    for (int i = c.tid(); i < np; i += c.nthreads()) {
+        if (contactSlot(v, i)->hdr == 0) continue;
+        const int lv = (int)(v.pairs[i] >> 20);
+        const int at = bs->off[lv] + atomicAdd(&bs->cnt[lv], 1);
+        bs->items[at] = (uint16_t)((slot << 10) | i);
+    }
+    __syncthreads();
+    return true;
+}
+
+template <bool kVelocity>
+__device__ __forceinline__ void solveDense(BlockSolve *bs, const StepParams &p, int max_level)
+{
+    for (int lv = 1; lv <= max_level; lv++) {
+        const int begin = bs->off[lv], end = bs->off[lv + 1];
+        if (begin == end) continue;                    // block-uniform
+        for (int k = begin + (int)threadIdx.x; k < end; k += (int)blockDim.x) {
+            const uint32_t code = bs->items[k];
+            WorldView &vv = bs->views[code >> 10];
+            SolverContact *ct = contactSlot(vv, (int)(code & 1023u));
+            if (kVelocity) solveContactVelocities(vv, p, ct);
+            else solveContactPositions(vv, p, ct);
+        }
+        __syncthreads();
+    }
+}
+#endif
+
 // Steps world `w` in world slot `v`. `group_level` is one int shared by the
 // whole block: the level loops must run the same number of barriers in every
 // world slot, so they run to the block-wide maximum. A slot without a world
 // this round (`!v.active`) walks the same barriers with zero rows.
-MDR_HD void stepWorld(const BlockCtx &c, WorldView &v, const StepParams &p, int w, int *group_level)
+MDR_HD void stepWorld(const BlockCtx &c, WorldView &v, const StepParams &p, int w, int *group_level,
+                      BlockSolve *bs = nullptr, int slot = 0)
 {
     v.n = v.active ? p.t.row_count[w] : 0;
     if (v.n > v.np) v.n = v.np;
@@ -44,6 +125,15 @@ MDR_HD void stepWorld(const BlockCtx &c, WorldView &v, const StepParams &p, int 
 #if defined(__CUDA_ARCH__)
         satQueueWarp(c, v, p, probing, sub);
         c.sync();
+#endif
+#if defined(__CUDA_ARCH__)
+        if (bs && buildLevelLists(c, v, bs, slot, max_level)) {
+            solveDense<false>(bs, p, max_level);
+            setVelocities(c, v, p);
+            c.sync();
+            solveDense<true>(bs, p, max_level);
+            continue;
+        }
 #endif
         solveLevels<false>(c, v, p, max_level);
         setVelocities(c, v, p);

@@ -34,6 +34,7 @@ physStepKernel(const __grid_constant__ StepParams p, int threads_per_world, int 
                int overflow_per_slot, int lockstep)
 {
     __shared__ int group_level;
+    __shared__ BlockSolve block_solve;
     const int slots = blockDim.x / threads_per_world;
     const int slot = threadIdx.x / threads_per_world;
     BlockCtx ctx;
@@ -43,12 +44,16 @@ physStepKernel(const __grid_constant__ StepParams p, int threads_per_world, int 
     WorldView v;
     carveWorld(v, mdr_smem + (size_t)slot * slot_bytes, p.t.stride, p.max_pairs, p.smem_contacts);
     v.overflow = p.overflow + ((size_t)blockIdx.x * slots + slot) * overflow_per_slot;
+    // dense solver lanes need block-wide barriers, pair slots in 10 bits and a view per slot
+    BlockSolve *bs = lockstep && slots <= kDenseSlots && p.max_pairs <= 1024 ? &block_solve : nullptr;
+    if (bs && ctx.tid_ == 0) { v.n = 0; v.active = false; bs->views[slot] = v; }
+    __syncthreads();
     // Every slot of the block walks the same barriers: the trip count depends on
     // the block index only; a slot past the last world idles through them.
     for (int base = blockIdx.x * slots; base < p.t.num_worlds; base += gridDim.x * slots) {
         const int w = base + slot;
         v.active = w < p.t.num_worlds;
-        stepWorld(ctx, v, p, v.active ? w : 0, &group_level);
+        stepWorld(ctx, v, p, v.active ? w : 0, &group_level, bs, slot);
     }
 }
 

@@ -2,7 +2,7 @@
 # Usage: profiles/analyze.sh <tag> <kernel mangled substring>   (run in the build container)
 TAG=$1; K=$2
 mkdir -p /tmp/cub && cd /tmp/cub && rm -f *.cubin && cuobjdump -xelf all /root/repo/gpu_ecs_madrona_b200/libmadrona_b200.so > /dev/null
-nvdisasm -gi -c *.cubin > dis.txt 2>/dev/null
+for f in *.cubin; do nvdisasm -gi -c $f; done > dis.txt 2>/dev/null
 cd /root/repo
 ncu -i gpurun_out/${TAG}_prof.ncu-rep --page source --csv --print-source sass > gpurun_out/${TAG}_sass.csv 2>/dev/null
 python - <<PY
