@@ -36,7 +36,8 @@ namespace {
 constexpr int kWarpsPerBlock = 8;
 
 // ------------------------------------------------------------------ kernels --
-__global__ void __launch_bounds__(32 * kWarpsPerBlock)
+template <int kMinBlocks>
+__global__ void __launch_bounds__(32 * kWarpsPerBlock, kMinBlocks)
 ecsStepKernel(const EcsDev *__restrict__ E)
 {
     __shared__ WarpShared shared[kWarpsPerBlock];
@@ -237,6 +238,7 @@ struct mdr_ecs {
     cudaGraphExec_t graph = nullptr;
     bool exports_dirty = true;
     int blocks = 0;
+    void (*step_kernel)(const EcsDev *) = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     double timed_ms = 0;
     int timed_steps = 0, pending_steps = 0;
@@ -565,8 +567,27 @@ int32_t mdr_ecs_build(mdr_ecs *e)
     e->dev = e->dalloc<EcsDev>(1, false);
     REQ_CUDA(cudaMemcpy(e->dev, &H, sizeof(H), cudaMemcpyHostToDevice));
 
+    // Register budget of the megakernel: more resident warps hide the latency of the
+    // dependent table accesses (the step is latency-bound, profiles/r01e_summary.md).
+    // Measured (profiles/r01e_summary.md): 4 blocks per SM (62 registers, no spills) is the
+    // fastest per warp; 6 or 8 (40 / 32 registers, spills) only pay when they let every world
+    // be resident at once instead of leaving a partial second round.
+    cudaDeviceProp prop0;
+    REQ_CUDA(cudaGetDeviceProperties(&prop0, e->cfg.gpu_id));
+    const char *mb = getenv("MDR_ECS_MIN_BLOCKS");
+    int want = mb && *mb ? atoi(mb) : 0;
+    if (want == 0) {
+        auto rounds = [&](int v) {
+            const long long cap = (long long)prop0.multiProcessorCount * v * kWarpsPerBlock;
+            return (W + cap - 1) / cap;
+        };
+        want = 4;
+        if (rounds(6) < rounds(want)) want = 6;
+        if (rounds(8) < rounds(want)) want = 8;
+    }
+    e->step_kernel = want == 6 ? ecsStepKernel<6> : want == 8 ? ecsStepKernel<8> : ecsStepKernel<4>;
     int per_sm = 0;
-    REQ_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, ecsStepKernel, 32 * kWarpsPerBlock, 0));
+    REQ_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, e->step_kernel, 32 * kWarpsPerBlock, 0));
     cudaDeviceProp prop;
     REQ_CUDA(cudaGetDeviceProperties(&prop, e->cfg.gpu_id));
     long long grid = (long long)(per_sm > 0 ? per_sm : 1) * prop.multiProcessorCount;
@@ -719,7 +740,7 @@ int32_t mdr_ecs_step_async(mdr_ecs *e, int32_t num_steps)
         cudaGraph_t g = nullptr;
         REQ_CUDA(cudaStreamBeginCapture(e->stream, cudaStreamCaptureModeThreadLocal));
         if (staged) ecsExportCopy<<<(e->host.num_worlds + 7) / 8, 256, 0, e->stream>>>(e->dev, 0);
-        ecsStepKernel<<<e->blocks, 32 * kWarpsPerBlock, 0, e->stream>>>(e->dev);
+        e->step_kernel<<<e->blocks, 32 * kWarpsPerBlock, 0, e->stream>>>(e->dev);
         if (staged) {
             ecsExportOffsets<<<e->host.num_exports, 1024, 0, e->stream>>>(e->dev);
             ecsExportCopy<<<(e->host.num_worlds + 7) / 8, 256, 0, e->stream>>>(e->dev, 1);

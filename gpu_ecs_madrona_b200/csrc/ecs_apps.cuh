@@ -85,10 +85,18 @@ __device__ __forceinline__ void fvsCaster(Context &ctx, Entity &e, Action &a, Ma
 {
     mdr_vec3 target;
     if (!mdr_fvs_caster(ctx.world_id, fvsTickNow(ctx), e.id, &a.remainingTime, &m.mp, &target)) return;
+    // fvs.cpp:180: ctx.parallelFor(healthQuery, blast) from inside the system
+    ctx.submitNested(__float_as_uint(target.x), __float_as_uint(target.y), __float_as_uint(target.z), 0u);
+}
+// The nested job: every (Position, Health) row, Dragon table then Knight table, all lanes.
+__device__ __forceinline__ void fvsBlast(Context &ctx, uint32_t tx, uint32_t ty, uint32_t tz, uint32_t)
+{
+    mdr_vec3 target;
+    target.x = __uint_as_float(tx); target.y = __uint_as_float(ty); target.z = __uint_as_float(tz);
     for (int arch = 0; arch < 2; arch++) {
         const Position *pos = ctx.column<Position>(arch, 1);
         Health *hp = ctx.column<Health>(arch, 2);
-        for (int32_t i = 0, n = ctx.numRows(arch); i < n; i++) {
+        for (int32_t i = laneId(), n = ctx.numRows(arch); i < n; i += 32) {
             const mdr_vec3 p = pos[i];
             if (mdr_fvs_in_blast(&target, &p)) atomicSub(&hp[i].hp, MDR_FVS_BLAST_DAMAGE);
         }
@@ -138,7 +146,7 @@ __device__ __forceinline__ void dispatchParallelFor(Context &ctx, const NodeDev 
     case kFanOverlap: parallelFor<fanOverlap, Entity, Box>(ctx, nd); break;
     case kFanConsume: parallelFor<fanConsume, Candidate>(ctx, nd); break;
     case kFvsAction: parallelFor<fvsAction, Entity, Position, Action>(ctx, nd); break;
-    case kFvsCaster: parallelFor<fvsCaster, Entity, Action, Mana>(ctx, nd); break;
+    case kFvsCaster: parallelForNested<fvsCaster, fvsBlast, Entity, Action, Mana>(ctx, nd); break;
     case kFvsArcher: parallelFor<fvsArcher, Entity, Action, Quiver>(ctx, nd); break;
     case kFvsMark: parallelFor<fvsMark, Entity, Health>(ctx, nd); break;
     case kFvsDestroy: parallelFor<fvsDestroy, CleanupEntity>(ctx, nd); break;

@@ -215,7 +215,8 @@ struct Context {
     WarpShared *ws;
     int32_t world;          // index on this GPU
     uint32_t world_id;      // global index (seeds)
-    uint32_t pend;          // bit 0: destroy pending, bit 1: create pending
+    uint32_t pend;          // bit 0: destroy pending, bit 1: create pending, bit 2: nested job pending
+    uint32_t nested[4];     // arguments of the pending nested parallel-for
     Entity pend_e;
     int32_t create_arch;
     Entity created;         // result of the applied create (script kernel)
@@ -262,6 +263,14 @@ struct Context {
     // Context::destroyEntityNow / makeEntityNow<Archetype>(components...): at most one
     // of each per invocation, applied in row order after the slice (destroy first).
     __device__ __forceinline__ void destroyEntityNow(Entity e) { pend |= 1u; pend_e = e; }
+    // Context::parallelFor issued from inside a system (examples/fantasy_vs/fvs.cpp:180-190):
+    // the nested loop is handed to the whole warp after the slice (see parallelForNested);
+    // at most one per invocation, four words of arguments.
+    __device__ __forceinline__ void submitNested(uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3)
+    {
+        pend |= 4u;
+        nested[0] = a0; nested[1] = a1; nested[2] = a2; nested[3] = a3;
+    }
     template <typename ArchT, typename... Cs> __device__ __forceinline__ void makeEntityNow(const Cs &...cs)
     {
         makeEntityNowIn(ArchT::kId, cs...);
@@ -413,8 +422,8 @@ __device__ inline void createBatch(Context &ctx, unsigned run)
 // one kind.
 __device__ inline void applyPending(Context &ctx)
 {
-    unsigned rd = __ballot_sync(kFull, ctx.pend & 1u);
-    unsigned rc = __ballot_sync(kFull, ctx.pend & 2u);
+    unsigned rd = __ballot_sync(kFull, (ctx.pend & 1u) != 0u);
+    unsigned rc = __ballot_sync(kFull, (ctx.pend & 2u) != 0u);
     ctx.created = Entity { 0u, -1 };
     ctx.created_row = -1;
     while (rd | rc) {
@@ -433,7 +442,7 @@ __device__ inline void applyPending(Context &ctx)
             rc &= ~run;
         }
     }
-    ctx.pend = 0u;
+    ctx.pend &= 4u;
 }
 
 // ------------------------------------------------------------------- clear --
@@ -602,6 +611,42 @@ template <auto Fn, typename... Cs>
 __device__ __forceinline__ void parallelFor(Context &ctx, const NodeDev &nd)
 {
     parallelForImpl<Fn, Cs...>(ctx, nd, std::make_integer_sequence<int, (int)sizeof...(Cs)>());
+}
+
+// A system that may submit one nested parallel-for per invocation (Context::
+// submitNested). The nested jobs of a slice run right after it, one at a time in row
+// order, each executed by ALL 32 lanes: Nested(ctx, args) is called converged and
+// strides its own loop by lane. Valid when the nested job's effects are not read by
+// later rows of the same node (the reference runs it inline).
+template <auto Fn, auto Nested, typename... Cs, int... Is>
+__device__ __forceinline__ void parallelForNestedImpl(Context &ctx, const NodeDev &nd, std::integer_sequence<int, Is...>)
+{
+    const int lane = laneId();
+    for (int m = 0; m < nd.num_match; m++) {
+        const MatchDev &mt = nd.match[m];
+        const int32_t n = ctx.numRows(mt.arch);
+        for (int32_t base = 0; base < n; base += 32) {
+            const int32_t row = base + lane;
+            if (row < n) Fn(ctx, ctx.column<Cs>(mt.arch, mt.col[Is])[row]...);
+            __syncwarp();
+            unsigned jobs = __ballot_sync(kFull, (ctx.pend & 4u) != 0u);
+            while (jobs) {
+                const int src = __ffs(jobs) - 1;
+                jobs &= jobs - 1;
+                Nested(ctx, __shfl_sync(kFull, ctx.nested[0], src), __shfl_sync(kFull, ctx.nested[1], src),
+                       __shfl_sync(kFull, ctx.nested[2], src), __shfl_sync(kFull, ctx.nested[3], src));
+            }
+            ctx.pend &= ~4u;
+            __syncwarp();
+            if (__any_sync(kFull, ctx.pend != 0u)) applyPending(ctx);
+        }
+        __syncwarp();
+    }
+}
+template <auto Fn, auto Nested, typename... Cs>
+__device__ __forceinline__ void parallelForNested(Context &ctx, const NodeDev &nd)
+{
+    parallelForNestedImpl<Fn, Nested, Cs...>(ctx, nd, std::make_integer_sequence<int, (int)sizeof...(Cs)>());
 }
 
 }  // namespace ecs
