@@ -109,7 +109,10 @@ def cpu_baseline(steps, warmup, worlds_per_thread=256, kind=None):
     if kind == "port" and not orc.available("port"):
         orc.build("port")
     cores = len(os.sched_getaffinity(0))
-    worlds = worlds_per_thread * cores
+    # The reference reserves 48 GB of virtual address space per StateManager
+    # (src/common/virtual.cpp:79), one per world: stay well under the 128 TB user space.
+    worlds = min(worlds_per_thread * cores, 1024)
+    worlds = max(cores, worlds // cores * cores)
     sc = scenes.collisions64(worlds)
     o = orc.Oracle(sc, kind)
     o.step(warmup, cores)
@@ -118,8 +121,27 @@ def cpu_baseline(steps, warmup, worlds_per_thread=256, kind=None):
     dt = time.perf_counter() - t0
     o.close()
     return {"value": worlds * steps / dt, "unit": UNIT, "cores": cores, "kind": kind,
-            "sample": f"{worlds} worlds x {steps} steps after {warmup} warm-up steps, "
-                      f"collisions-64, {cores} threads ({dt:.1f} s wall)"}, dt
+            "sample": f"{worlds} worlds x {steps} steps after {warmup} warm-up steps (the same step range), "
+                      f"collisions-64, {cores} threads ({dt:.1f} s wall); worlds capped at 1024 by the "
+                      "reference's 48 GB address-space reservation per world"}, dt
+
+
+def mean_pairs_contacts(args, gpu):
+    """Mean candidate pairs / contacts per world-step over the TIMED step range, from an untimed
+    replay of the first 256 worlds of the batch (same scene, same steps), sampled every step:
+    the inputs of the algorithmic-byte figure of SURVEY 8(d)."""
+    from gpu_ecs_madrona_b200 import phys, scenes
+    sc = scenes.collisions64(256, max_contacts=args.max_contacts)
+    ex = phys.PhysExecutor(sc, gpu_id=gpu)
+    ex.run(args.warmup)
+    ps, cs = [], []
+    for _ in range(args.steps):
+        ex.run(1)
+        p, c = ex.stats()
+        ps.append(p.mean())
+        cs.append(c.mean())
+    ex.close()
+    return float(np.mean(ps)), float(np.mean(cs))
 
 
 def run_reference(args):
@@ -173,8 +195,7 @@ def run_ours(args):
     clocks = sampler.stop()
     assert launches == args.steps
     dev_ms = kms * launches
-    pairs, contacts = ex.stats()
-    P, C = float(pairs.mean()), float(contacts.mean())
+    P, C = mean_pairs_contacts(args, local)
     if dist is not None:
         t = torch.tensor([dev_ms], dtype=torch.float64, device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -225,7 +246,7 @@ def run_ours(args):
                 traffic = json.load(open(tpath)).get("dram_bytes_per_launch")
             except Exception:
                 traffic = None
-        base, _ = cpu_baseline(min(args.steps, 40), min(args.warmup, 10)) if not args.no_cpu else ({}, 0)
+        base, _ = cpu_baseline(args.steps, args.warmup) if not args.no_cpu else ({}, 0)
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": dev_ms / args.steps, "higher_is_better": True,
