@@ -95,6 +95,7 @@ class EcsRegistry:
     def __init__(self, num_worlds, gpu_id=0, first_world=0, ids_per_world=0, max_script_handles=0):
         self.lib = _lib()
         self.num_worlds = num_worlds
+        self.gpu_id = gpu_id
         cfg = MdrEcsConfig(num_worlds, first_world, gpu_id, ids_per_world, max_script_handles, 0)
         h = C.c_void_p()
         _check(self.lib.mdr_ecs_create(C.byref(cfg), C.byref(h)), "mdr_ecs_create")
@@ -223,6 +224,21 @@ class EcsRegistry:
         """(device pointer, rows, bytes per row) of an exported column: getExported(slot)."""
         return (self.lib.mdr_ecs_get_exported(self.h, slot), self.lib.mdr_ecs_export_rows(self.h, slot),
                 self.lib.mdr_ecs_export_bytes_per_row(self.h, slot))
+
+    def export_tensor(self, slot, dtype=np.float32):
+        """Zero-copy torch view of an exported column, [rows, bytes_per_row / itemsize]: what a trainer
+        holds (Tensor.to_torch() of the reference). Staged exports change length with the row counts:
+        take a new view after a step that created or destroyed rows."""
+        from .tensor import as_torch
+        ptr, rows, nb = self.get_exported(slot)
+        return as_torch(ptr, (rows, nb // np.dtype(dtype).itemsize), dtype, self.gpu_id, owner=self)
+
+    def column_tensor(self, arch, col, dtype=np.float32):
+        """Zero-copy torch view of a whole table column, [num_worlds, row_stride, bytes / itemsize]."""
+        from .tensor import as_torch
+        nb = self.col_bytes[arch][col]
+        return as_torch(self.column_ptr(arch, col), (self.num_worlds, self.stride[arch], nb // np.dtype(dtype).itemsize),
+                        dtype, self.gpu_id, owner=self)
 
     def export(self, slot):
         """Host copy of an exported column (u8)."""

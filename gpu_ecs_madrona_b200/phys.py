@@ -135,6 +135,7 @@ class PhysExecutor:
     """Batched rigid-body worlds on one GPU. ``scene`` is a ``scenes.Scene``."""
 
     def __init__(self, scene, gpu_id=0, block_threads=0, smem_contacts=0, worlds_per_block=0, lib=None):
+        self.gpu_id = gpu_id
         self.lib = lib if lib is not None else load_library()
         self.scene = scene
         self.W, self.N = scene.num_worlds, scene.bodies_per_world
@@ -258,6 +259,13 @@ class PhysExecutor:
     # ---- CUDA-only entry points -------------------------------------------
     def column_ptr(self, col):
         return self.lib.mdr_phys_column_ptr(self.h, col)
+
+    def column_tensor(self, col, dtype=np.float32):
+        """Zero-copy torch view [num_worlds, row_stride, bytes / itemsize] of an exported column
+        (getExported + Tensor.to_torch of the reference, include/madrona/python.hpp:21-73)."""
+        from .tensor import as_torch
+        shape = (self.W, self.row_stride(), COL_BYTES[col] // np.dtype(dtype).itemsize)
+        return as_torch(self.column_ptr(col), shape, dtype, self.gpu_id, owner=self)
 
     def row_stride(self):
         return int(self.lib.mdr_phys_row_stride(self.h))

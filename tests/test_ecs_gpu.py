@@ -177,3 +177,24 @@ def test_full_size_fvs_properties():
     assert churn > 0
     tick = ex.read_column_all(3, 1).view(np.uint32).reshape(8192, -1)[:, 0]
     assert (tick == 150).all()
+
+
+def test_zero_copy_tensor_views():
+    """getExported -> torch (the reference's py::Tensor role): views alias the tables, no copy."""
+    import torch
+    from gpu_ecs_madrona_b200.ecs import EcsExecutor
+    from gpu_ecs_madrona_b200 import phys, scenes
+    ex = EcsExecutor(A.APP_TASKGRAPH, 5)
+    t = ex.export_tensor(0)                       # Agent Position, staged export: [5 rows, 3]
+    assert t.shape == (5, 3) and t.is_cuda
+    assert np.array_equal(t.cpu().numpy().view(np.uint8).ravel(), ex.export(0))
+    col = ex.column_tensor(0, 1)                  # Sphere Position column, in place
+    before = col[:, :100].clone()
+    ex.run(3)
+    torch.cuda.synchronize()
+    assert not torch.equal(before, col[:, :100])  # the view sees the step's writes
+    assert np.array_equal(col.cpu().numpy().view(np.uint8).reshape(5, -1, 12), ex.read_column_all(0, 1))
+    pe = phys.PhysExecutor(scenes.collisions64(3))
+    pos = pe.column_tensor(phys.COL_POSITION)
+    pe.run(2)
+    assert np.array_equal(pos.cpu().numpy()[:, :65], pe.state()[0])
