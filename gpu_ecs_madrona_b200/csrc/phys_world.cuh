@@ -89,6 +89,9 @@ struct WorldView {
     uint32_t *mask;        // [np][mask_words] hit bits in rank order
     uint16_t *order;       // [np] leaf at traversal rank r
     uint16_t *last_level;  // [np]
+    uint16_t *rank_of;     // [np] traversal rank of leaf i (inverse of order)
+    float *rbox;           // [np][8] per traversal RANK, two 16-byte loads: slot lo.xyz, entity id bits,
+                           //         slot hi.xyz, (leaf | static << 15) bits
     int mask_words;
     // --- substep phase ---
     SolverContact *contacts;   // [smem_contacts]
@@ -130,6 +133,8 @@ MDR_HD size_t carveWorld(WorldView &v, char *base, int np, int max_pairs, int sm
     MDR_CARVE(mask, uint32_t, np * v.mask_words)
     MDR_CARVE(order, uint16_t, np)
     MDR_CARVE(last_level, uint16_t, np)
+    MDR_CARVE(rank_of, uint16_t, np)
+    MDR_CARVE(rbox, float, 8 * np)
 #undef MDR_CARVE
     if (end_contacts > off) off = end_contacts;
     return alignUp(off, 16);
@@ -199,12 +204,17 @@ MDR_HD void loadWorld(const BlockCtx &c, WorldView &v, const StepParams &p, int 
     copyWords(c, v.slot, t.slot_box + 6 * r0, 6 * n);
     for (int i = c.tid(); i < n; i += c.nthreads()) {
         v.ent_id[i] = t.entity[2 * (r0 + i) + 1];
-        v.order[i] = t.order[r0 + i];
         const uint32_t obj = (uint32_t)t.obj[r0 + i];
         uint32_t m = obj & 0xffffu;
         if (t.resp[r0 + i] == 2u) m |= META_STATIC;
         if (MDR_LDG(&p.a.objs[obj].type) == 2) m |= META_HULL;
         v.meta[i] = m;
+        // thread i also owns traversal rank i: the leaf met i-th by the reference's walk
+        const uint32_t b = t.order[r0 + i];
+        v.order[i] = (uint16_t)b;
+        v.rank_of[b] = (uint16_t)i;
+        reinterpret_cast<int32_t *>(v.rbox)[8 * i + 3] = t.entity[2 * (r0 + b) + 1];
+        reinterpret_cast<uint32_t *>(v.rbox)[8 * i + 7] = b | (t.resp[r0 + b] == 2u ? 1u << 15 : 0u);
     }
 }
 
@@ -256,7 +266,11 @@ MDR_HD void updateLeavesAndRefit(const BlockCtx &c, WorldView &v, const StepPara
     for (int i = c.tid(); i < v.n; i += c.nthreads()) {
         Box leaf = leafBox(v, p, i);
         stBox(v.box, i, leaf);
-        stBox(v.slot, i, growBox(ldBox(v.slot, i), leaf));
+        const Box grown = growBox(ldBox(v.slot, i), leaf);
+        stBox(v.slot, i, grown);
+        float *rb = v.rbox + 8 * v.rank_of[i];
+        rb[0] = grown.lo.x; rb[1] = grown.lo.y; rb[2] = grown.lo.z;
+        rb[4] = grown.hi.x; rb[5] = grown.hi.y; rb[6] = grown.hi.z;
     }
 }
 
@@ -310,6 +324,15 @@ MDR_HD void raiseError(const StepParams &p, int bit)
 #endif
 }
 
+// One rank-ordered broadphase entry against row a's current box.
+struct alignas(16) RankEntry { float lx, ly, lz; int32_t ent; float hx, hy, hz; uint32_t info; };
+MDR_HD bool pairTest(const float *rbox, int r, const Box &q, int a_id, bool a_static)
+{
+    const RankEntry e = *reinterpret_cast<const RankEntry *>(rbox + 8 * r);
+    return a_id < e.ent && !(a_static && (e.info >> 15)) &&
+           q.lo.x < e.hx && e.lx < q.hi.x && q.lo.y < e.hy && e.ly < q.hi.y && q.lo.z < e.hz && e.lz < q.hi.z;
+}
+
 // findOverlappingEntry + BVH::findOverlaps (broadphase.cpp:897-932,
 // include/madrona/physics.inl:61-100): pairs (a, b) with a's entity id below
 // b's, not both static, a's CURRENT leaf box strictly overlapping b's slot box,
@@ -319,16 +342,22 @@ MDR_HD void findPairs(const BlockCtx &c, WorldView &v, const StepParams &p, int 
 {
     const int n = v.n;
     const size_t r0 = (size_t)w * p.t.stride;
-    for (int a = c.tid(); a < n; a += c.nthreads()) {
+    // Rows are taken one per thread; the rows left over after the last full pass
+    // (row 64 of 65 with 64 threads) are swept by the whole group instead, one rank
+    // per thread, so that no thread walks all ranks alone while the others wait.
+#if defined(__CUDA_ARCH__)
+    const int full = n / c.nthreads() * c.nthreads();
+#else
+    const int full = n;
+#endif
+    for (int a = c.tid(); a < full; a += c.nthreads()) {
         const Box q = ldBox(v.box, a);
         const int a_id = v.ent_id[a];
         const bool a_static = (v.meta[a] & META_STATIC) != 0;
         int count = 0;
         uint32_t word = 0;
         for (int r = 0; r < n; r++) {
-            const int b = v.order[r];
-            bool hit = a_id < v.ent_id[b] && !(a_static && (v.meta[b] & META_STATIC)) &&
-                       overlaps(q, ldBox(v.slot, b));
+            const bool hit = pairTest(v.rbox, r, q, a_id, a_static);
             if (hit) { word |= 1u << (r & 31); count++; }
             if ((r & 31) == 31 || r == n - 1) { v.mask[a * v.mask_words + (r >> 5)] = word; word = 0; }
         }
@@ -336,6 +365,30 @@ MDR_HD void findPairs(const BlockCtx &c, WorldView &v, const StepParams &p, int 
         v.last_level[a] = 0;
         if (!(a_static && staticStable(ld3(v.pos, a), ld4(v.rot, a)))) v.meta[a] |= META_DEP;
     }
+#if defined(__CUDA_ARCH__)
+    for (int a = full + c.tid(); a < n; a += c.nthreads()) {
+        v.cnt[a] = 0;
+        v.last_level[a] = 0;
+        if (!((v.meta[a] & META_STATIC) && staticStable(ld3(v.pos, a), ld4(v.rot, a)))) v.meta[a] |= META_DEP;
+    }
+    c.sync();       // every world slot of the block takes this barrier, tail rows or not
+    if (full < n) {
+        const int padded = (n + 31) & ~31;
+        for (int a = full; a < n; a++) {
+            const Box q = ldBox(v.box, a);
+            const int a_id = v.ent_id[a];
+            const bool a_static = (v.meta[a] & META_STATIC) != 0;
+            for (int r = c.tid(); r < padded; r += c.nthreads()) {      // whole warps iterate together
+                const bool hit = r < n && pairTest(v.rbox, r, q, a_id, a_static);
+                const uint32_t word = __ballot_sync(0xffffffffu, hit);
+                if ((c.tid() & 31) == 0) {
+                    v.mask[a * v.mask_words + (r >> 5)] = word;
+                    if (word) atomicAdd(&v.cnt[a], __popc(word));
+                }
+            }
+        }
+    }
+#endif
     if (v.active) copyWords(c, p.t.slot_box + 6 * r0, v.slot, 6 * n);
     c.sync();
     groupExclusiveScan(c, v.cnt, n);
