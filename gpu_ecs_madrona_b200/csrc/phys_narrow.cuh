@@ -565,9 +565,12 @@ MDR_HD void narrowphasePair(WorldView &v, const StepParams &p, int pi, bool prob
 
 // Per body, per substep: world AABB of the object box, the narrowphase's cheap
 // reject (narrowphase.cpp:1583-1596).
-MDR_HD void worldBoxes(const BlockCtx &c, WorldView &v, const StepParams &p)
+MDR_HD void worldBoxes(const BlockCtx &c, WorldView &v, const StepParams &p, int sub)
 {
-    for (int i = c.tid(); i < v.n; i += c.nthreads()) {
+    // same row -> thread mapping as substepBodies: no barrier between the two
+    const int rows = sub > 0 ? v.misc[3] : v.n;
+    for (int k = c.tid(); k < rows; k += c.nthreads()) {
+        const int i = v.row_perm[k];
         const ObjDev *o = p.a.objs + (v.meta[i] & 0xffffu);
         stBox(v.box, i, applyTRS(objAABB(o), ld3(v.pos, i), ld4(v.rot, i), ld3(v.scale, i)));
     }

@@ -38,12 +38,14 @@ MDR_HD BodyMass bodyMass(const WorldView &v, const StepParams &p, int row)
 // read straight from HBM (read-only, once per substep); PreSolvePositional is
 // only an output of the step (the solver keeps local arms instead) and goes
 // straight to HBM.
-MDR_HD void substepBodies(const BlockCtx &c, WorldView &v, const StepParams &p, int w)
+MDR_HD void substepBodies(const BlockCtx &c, WorldView &v, const StepParams &p, int w, int sub)
 {
     const float h = p.h;
     const V3 g = mk3(p.g[0], p.g[1], p.g[2]);
     const size_t r0 = (size_t)w * p.t.stride;
-    for (int i = c.tid(); i < v.n; i += c.nthreads()) {
+    const int rows = sub > 0 ? v.misc[3] : v.n;
+    for (int k = c.tid(); k < rows; k += c.nthreads()) {
+        const int i = v.row_perm[k];
         V3 x = ld3(v.pos, i);
         Q4 q = ld4(v.rot, i);
         V3 vl = ldVelLin(v.vel, i), omega = ldVelAng(v.vel, i);
@@ -176,10 +178,12 @@ MDR_HD void solveContactPositions(WorldView &v, const StepParams &p, SolverConta
 }
 
 // solver::setVelocities, physics.cpp:673-714
-MDR_HD void setVelocities(const BlockCtx &c, WorldView &v, const StepParams &p)
+MDR_HD void setVelocities(const BlockCtx &c, WorldView &v, const StepParams &p, int sub)
 {
     const float h = p.h;
-    for (int i = c.tid(); i < v.n; i += c.nthreads()) {
+    const int rows = sub > 0 ? v.misc[3] : v.n;
+    for (int k = c.tid(); k < rows; k += c.nthreads()) {
+        const int i = v.row_perm[k];
         Q4 q = ld4(v.rot, i), qp = ldPoseQ(v.prev, i);
         Q4 dq;
         if (q.w != qp.w || q.x != qp.x || q.y != qp.y || q.z != qp.z) dq = q * qinv(qp);

@@ -115,9 +115,8 @@ MDR_HD void stepWorld(const BlockCtx &c, WorldView &v, const StepParams &p, int 
     const int max_level = c.lockstep() ? *group_level : v.misc[1];
     const bool probing = v.active && p.probe.world == w;
     for (int sub = 0; sub < p.substeps; sub++) {
-        substepBodies(c, v, p, w);
-        c.sync();
-        worldBoxes(c, v, p);
+        substepBodies(c, v, p, w, sub);
+        worldBoxes(c, v, p, sub);
         c.sync();
         const int np = v.misc[0];
         for (int i = c.tid(); i < np; i += c.nthreads()) narrowphasePair(v, p, i, probing, sub);
@@ -129,14 +128,14 @@ MDR_HD void stepWorld(const BlockCtx &c, WorldView &v, const StepParams &p, int 
 #if defined(__CUDA_ARCH__)
         if (bs && buildLevelLists(c, v, bs, slot, max_level)) {
             solveDense<false>(bs, p, max_level);
-            setVelocities(c, v, p);
+            setVelocities(c, v, p, sub);
             c.sync();
             solveDense<true>(bs, p, max_level);
             continue;
         }
 #endif
         solveLevels<false>(c, v, p, max_level);
-        setVelocities(c, v, p);
+        setVelocities(c, v, p, sub);
         c.sync();
         solveLevels<true>(c, v, p, max_level);
     }

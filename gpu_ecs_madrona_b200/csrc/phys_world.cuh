@@ -89,6 +89,7 @@ struct WorldView {
     uint32_t *mask;        // [np][mask_words] hit bits in rank order
     uint16_t *order;       // [np] leaf at traversal rank r
     uint16_t *last_level;  // [np]
+    uint16_t *row_perm;    // [np] rows in the order the per-row substep loops take them: stable statics last
     uint16_t *rank_of;     // [np] traversal rank of leaf i (inverse of order)
     float *rbox;           // [np][8] per traversal RANK, two 16-byte loads: slot lo.xyz, entity id bits,
                            //         slot hi.xyz, (leaf | static << 15) bits
@@ -122,6 +123,7 @@ MDR_HD size_t carveWorld(WorldView &v, char *base, int np, int max_pairs, int sm
     MDR_CARVE(pairs, uint32_t, max_pairs)
     MDR_CARVE(misc, int32_t, 4)
     MDR_CARVE(sat_queue, uint16_t, MDR_SAT_QUEUE)
+    MDR_CARVE(row_perm, uint16_t, np)
     off = alignUp(off, 16);
     const size_t region = off;
     MDR_CARVE(contacts, SolverContact, smem_contacts)
@@ -412,6 +414,16 @@ MDR_HD void findPairs(const BlockCtx &c, WorldView &v, const StepParams &p, int 
         }
     }
     c.sync();
+    // A stable static body (see staticStable) comes out of every substep exactly as it
+    // went in, so the per-row substep loops only visit it in the first substep: such
+    // rows go to the end of the row order (misc[3] = rows before them). Built by the
+    // second warp's first lane while thread 0 assigns the levels.
+    if (c.tid() == (c.nthreads() > 32 ? 32 : 0)) {
+        int k = 0;
+        for (int i = 0; i < n; i++) if (v.meta[i] & META_DEP) v.row_perm[k++] = (uint16_t)i;
+        v.misc[3] = k;
+        for (int i = 0; i < n; i++) if (!(v.meta[i] & META_DEP)) v.row_perm[k++] = (uint16_t)i;
+    }
     if (c.tid() == 0) {
         int np = total;
         if (np > p.max_pairs) { np = p.max_pairs; raiseError(p, MDR_ERR_PAIR_OVERFLOW); }
