@@ -181,6 +181,27 @@ MDR_HD void copyWords(const BlockCtx &c, T *dst, const T *src, int words)
     for (int i = c.tid(); i < words; i += c.nthreads()) dst[i] = src[i];
 }
 
+// HBM -> SMEM without a register round trip: every copy of the tile is in flight
+// before the first one is waited for (world tiles are only 4-byte aligned, so
+// the copies are word-sized). Completed by fetchWait() + a barrier.
+MDR_HD void fetchWords(const BlockCtx &c, float *dst, const float *src, int words)
+{
+#if defined(__CUDA_ARCH__)
+    for (int i = c.tid(); i < words; i += c.nthreads()) {
+        asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((uint32_t)__cvta_generic_to_shared(dst + i)),
+                     "l"(src + i) : "memory");
+    }
+#else
+    copyWords(c, dst, src, words);
+#endif
+}
+MDR_HD void fetchWait()
+{
+#if defined(__CUDA_ARCH__)
+    asm volatile("cp.async.wait_all;" ::: "memory");
+#endif
+}
+
 // A static body whose pose the positional solver's write-back leaves bit-identical
 // (physics.cpp:185-211 with zero inverse mass and inertia): no component is -0
 // and q is a fixed point of Quat::normalize. Such a body does not order contacts.
@@ -199,25 +220,27 @@ MDR_HD void loadWorld(const BlockCtx &c, WorldView &v, const StepParams &p, int 
     const PhysTables &t = p.t;
     const size_t r0 = (size_t)w * t.stride;
     const int n = v.n;
-    copyWords(c, v.pos, t.pos + 3 * r0, 3 * n);
-    copyWords(c, v.rot, t.rot + 4 * r0, 4 * n);
-    copyWords(c, v.vel, t.vel + 6 * r0, 6 * n);
-    copyWords(c, v.scale, t.scale + 3 * r0, 3 * n);
-    copyWords(c, v.slot, t.slot_box + 6 * r0, 6 * n);
+    fetchWords(c, v.pos, t.pos + 3 * r0, 3 * n);
+    fetchWords(c, v.rot, t.rot + 4 * r0, 4 * n);
+    fetchWords(c, v.vel, t.vel + 6 * r0, 6 * n);
+    fetchWords(c, v.scale, t.scale + 3 * r0, 3 * n);
+    fetchWords(c, v.slot, t.slot_box + 6 * r0, 6 * n);
     for (int i = c.tid(); i < n; i += c.nthreads()) {
-        v.ent_id[i] = t.entity[2 * (r0 + i) + 1];
+        // four independent loads, then the object table (cached)
+        const int32_t ent = t.entity[2 * (r0 + i) + 1];
         const uint32_t obj = (uint32_t)t.obj[r0 + i];
+        const uint32_t resp = t.resp[r0 + i];
+        const uint32_t b = t.order[r0 + i];
+        v.ent_id[i] = ent;
         uint32_t m = obj & 0xffffu;
-        if (t.resp[r0 + i] == 2u) m |= META_STATIC;
+        if (resp == 2u) m |= META_STATIC;
         if (MDR_LDG(&p.a.objs[obj].type) == 2) m |= META_HULL;
         v.meta[i] = m;
         // thread i also owns traversal rank i: the leaf met i-th by the reference's walk
-        const uint32_t b = t.order[r0 + i];
         v.order[i] = (uint16_t)b;
         v.rank_of[b] = (uint16_t)i;
-        reinterpret_cast<int32_t *>(v.rbox)[8 * i + 3] = t.entity[2 * (r0 + b) + 1];
-        reinterpret_cast<uint32_t *>(v.rbox)[8 * i + 7] = b | (t.resp[r0 + b] == 2u ? 1u << 15 : 0u);
     }
+    fetchWait();
 }
 
 MDR_HD void storeWorld(const BlockCtx &c, const WorldView &v, const PhysTables &t, int w)
@@ -272,7 +295,9 @@ MDR_HD void updateLeavesAndRefit(const BlockCtx &c, WorldView &v, const StepPara
         stBox(v.slot, i, grown);
         float *rb = v.rbox + 8 * v.rank_of[i];
         rb[0] = grown.lo.x; rb[1] = grown.lo.y; rb[2] = grown.lo.z;
+        reinterpret_cast<int32_t *>(rb)[3] = v.ent_id[i];
         rb[4] = grown.hi.x; rb[5] = grown.hi.y; rb[6] = grown.hi.z;
+        reinterpret_cast<uint32_t *>(rb)[7] = (uint32_t)i | ((v.meta[i] & META_STATIC) ? 1u << 15 : 0u);
     }
 }
 
