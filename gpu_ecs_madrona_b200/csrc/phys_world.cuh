@@ -421,21 +421,29 @@ MDR_HD void findPairs(const BlockCtx &c, WorldView &v, const StepParams &p, int 
     groupExclusiveScan(c, v.cnt, n);
     c.sync();
     const int total = v.cnt[n];
-    for (int a = c.tid(); a < n; a += c.nthreads()) {
+    // one (row, mask word) per thread: a row with many pairs is shared by several threads
+    const int words = (n + 31) / 32;
+    for (int task = c.tid(); task < n * words; task += c.nthreads()) {
+        const int a = task / words, wd = task - a * words;
+        uint32_t m = v.mask[a * v.mask_words + wd];
+        if (!m) continue;
         int off = v.cnt[a];
-        const int words = (n + 31) / 32;
-        for (int wd = 0; wd < words; wd++) {
-            uint32_t m = v.mask[a * v.mask_words + wd];
-            while (m) {
+        for (int e = 0; e < wd; e++) {
 #if defined(__CUDA_ARCH__)
-                int bit = __ffs(m) - 1;
+            off += __popc(v.mask[a * v.mask_words + e]);
 #else
-                int bit = __builtin_ctz(m);
+            off += __builtin_popcount(v.mask[a * v.mask_words + e]);
 #endif
-                m &= m - 1;
-                if (off < p.max_pairs) v.pairs[off] = (uint32_t)a | ((uint32_t)v.order[wd * 32 + bit] << 10);
-                off++;
-            }
+        }
+        while (m) {
+#if defined(__CUDA_ARCH__)
+            int bit = __ffs(m) - 1;
+#else
+            int bit = __builtin_ctz(m);
+#endif
+            m &= m - 1;
+            if (off < p.max_pairs) v.pairs[off] = (uint32_t)a | ((uint32_t)v.order[wd * 32 + bit] << 10);
+            off++;
         }
     }
     c.sync();
@@ -449,10 +457,66 @@ MDR_HD void findPairs(const BlockCtx &c, WorldView &v, const StepParams &p, int 
         v.misc[3] = k;
         for (int i = 0; i < n; i++) if (!(v.meta[i] & META_DEP)) v.row_perm[k++] = (uint16_t)i;
     }
+    // Level of a pair = 1 + the latest earlier pair sharing an ordering body: a walk over
+    // the pairs in order. The pairs of one row are contiguous and their second bodies
+    // all differ, so when the row itself does not order contacts (a stable static: the
+    // ground plane and its 64 pairs) the whole run is independent and the first warp
+    // takes it at once; the other pairs are walked by its first lane.
+#if defined(__CUDA_ARCH__)
+    if (c.tid() < 32) {
+        const int lane = c.tid();
+        int np = total;
+        if (np > p.max_pairs) { np = p.max_pairs; if (lane == 0) raiseError(p, MDR_ERR_PAIR_OVERFLOW); }
+        int max_level = 0;
+        bool too_deep = false;
+        int i = 0;
+        while (i < np) {
+            const uint32_t pr = v.pairs[i];
+            const int a = pr & 1023;
+            if (!(v.meta[a] & META_DEP)) {
+                int end = v.cnt[a + 1];
+                if (end > np) end = np;
+                for (int k = i + lane; k < end; k += 32) {
+                    const uint32_t q = v.pairs[k];
+                    const int b = (q >> 10) & 1023;
+                    int lv = 1;
+                    if (v.meta[b] & META_DEP) {
+                        lv = v.last_level[b] + 1;
+                        if (lv > MDR_MAX_LEVEL) { lv = MDR_MAX_LEVEL; too_deep = true; }
+                        v.last_level[b] = (uint16_t)lv;
+                    }
+                    v.pairs[k] = q | ((uint32_t)lv << 20);
+                    if (lv > max_level) max_level = lv;
+                }
+                i = end;
+            } else {
+                if (lane == 0) {
+                    const int b = (pr >> 10) & 1023;
+                    const bool db = (v.meta[b] & META_DEP) != 0;
+                    const int la = v.last_level[a];
+                    const int lb = db ? v.last_level[b] : 0;
+                    int lv = (la > lb ? la : lb) + 1;
+                    if (lv > MDR_MAX_LEVEL) { lv = MDR_MAX_LEVEL; too_deep = true; }
+                    v.last_level[a] = (uint16_t)lv;
+                    if (db) v.last_level[b] = (uint16_t)lv;
+                    v.pairs[i] = pr | ((uint32_t)lv << 20);
+                    if (lv > max_level) max_level = lv;
+                }
+                i++;
+            }
+            __syncwarp();
+        }
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) {
+            const int o = __shfl_xor_sync(0xffffffffu, max_level, d);
+            if (o > max_level) max_level = o;
+        }
+        if (__any_sync(0xffffffffu, too_deep) && lane == 0) raiseError(p, MDR_ERR_PAIR_OVERFLOW);
+    if (lane == 0) {
+#else
     if (c.tid() == 0) {
         int np = total;
         if (np > p.max_pairs) { np = p.max_pairs; raiseError(p, MDR_ERR_PAIR_OVERFLOW); }
-        // Level of a pair = 1 + the latest earlier pair sharing an ordering body.
         int max_level = 0;
         for (int i = 0; i < np; i++) {
             const uint32_t pr = v.pairs[i];
@@ -467,6 +531,8 @@ MDR_HD void findPairs(const BlockCtx &c, WorldView &v, const StepParams &p, int 
             v.pairs[i] = pr | ((uint32_t)lv << 20);
             if (lv > max_level) max_level = lv;
         }
+    {
+#endif
         v.misc[0] = np;
         v.misc[1] = max_level;
         if (v.active) {
@@ -479,6 +545,7 @@ MDR_HD void findPairs(const BlockCtx &c, WorldView &v, const StepParams &p, int 
                 }
             }
         }
+    }
     }
     c.sync();
 }
