@@ -139,11 +139,20 @@ MDR_HD void stepWorld(const BlockCtx &c, WorldView &v, const StepParams &p, int 
         c.sync();
         solveLevels<true>(c, v, p, max_level);
     }
+#if defined(__CUDA_ARCH__)
+    if (c.tid() < 32 && v.active) {
+        int nc = 0;
+        for (int i = c.tid(); i < v.misc[0]; i += 32) nc += contactSlot(v, i)->hdr != 0;
+        nc = __reduce_add_sync(0xffffffffu, nc);
+        if (c.tid() == 0) p.world_contacts[w] = nc;
+    }
+#else
     if (c.tid() == 0 && v.active) {
         int nc = 0;
         for (int i = 0; i < v.misc[0]; i++) nc += contactSlot(v, i)->hdr != 0;
         p.world_contacts[w] = nc;
     }
+#endif
     updateLeavesAndRefitGlobal(c, v, p, w);
     c.sync();
     storeWorld(c, v, p.t, w);
