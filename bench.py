@@ -213,11 +213,14 @@ def run_ours(args):
     d2h = sum(a.nbytes for _, a in outs)
 
     def e2e_step():
-        for c, a in ins:
-            ex.write_raw_async(c, a)
-        ex.run_async(1)
-        for c, a in outs:
-            ex.read_raw_async(c, a)
+        if args.io_chunks > 1:
+            ex.step_io_async(ins, outs, args.io_chunks)     # copies overlap the step, range by range
+        else:
+            for c, a in ins:
+                ex.write_raw_async(c, a)
+            ex.run_async(1)
+            for c, a in outs:
+                ex.read_raw_async(c, a)
         ex.sync()
 
     for _ in range(3):
@@ -287,6 +290,8 @@ def main():
     ap.add_argument("--worlds-per-block", type=int, default=0)
     ap.add_argument("--smem-contacts", type=int, default=0, help="contact slots in shared memory (0: default)")
     ap.add_argument("--max-contacts", type=int, default=640, help="candidate-pair capacity per world (SURVEY 8d: 640)")
+    ap.add_argument("--io-chunks", type=int, default=4,
+                    help="world ranges the end-to-end step is pipelined over (1: copy, step, copy in sequence)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     args = ap.parse_args()
     if args.impl == "reference":

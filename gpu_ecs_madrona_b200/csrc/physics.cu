@@ -31,7 +31,7 @@ extern __shared__ __align__(16) char mdr_smem[];
 template <int kMaxThreads, int kMinBlocks>
 __global__ void __launch_bounds__(kMaxThreads, kMinBlocks)
 physStepKernel(const __grid_constant__ StepParams p, int threads_per_world, int slot_bytes,
-               int overflow_per_slot, int lockstep)
+               int overflow_per_slot, int lockstep, int first_world, int end_world)
 {
     __shared__ int group_level;
     __shared__ BlockSolve block_solve;
@@ -50,10 +50,10 @@ physStepKernel(const __grid_constant__ StepParams p, int threads_per_world, int 
     __syncthreads();
     // Every slot of the block walks the same barriers: the trip count depends on
     // the block index only; a slot past the last world idles through them.
-    for (int base = blockIdx.x * slots; base < p.t.num_worlds; base += gridDim.x * slots) {
+    for (int base = first_world + blockIdx.x * slots; base < end_world; base += gridDim.x * slots) {
         const int w = base + slot;
-        v.active = w < p.t.num_worlds;
-        stepWorld(ctx, v, p, v.active ? w : 0, &group_level, bs, slot);
+        v.active = w < end_world;
+        stepWorld(ctx, v, p, v.active ? w : first_world, &group_level, bs, slot);
     }
 }
 
@@ -77,7 +77,7 @@ __global__ void bvhRebuildKernel(const __grid_constant__ StepParams p)
 }
 
 // -------------------------------------------------------------- host state --
-typedef void (*StepKernel)(const StepParams, int, int, int, int);
+typedef void (*StepKernel)(const StepParams, int, int, int, int, int, int);
 // Compiled register budgets: {max block threads, min resident blocks}.
 struct KernelVariant { int threads, min_blocks; StepKernel fn; };
 static const KernelVariant kVariants[] = {
@@ -100,6 +100,9 @@ struct mdr_phys {
     std::vector<void *> allocs;
     cudaStream_t stream = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    // mdr_phys_step_io: copy-in / copy-out streams and per-chunk events
+    cudaStream_t io_in = nullptr, io_out = nullptr;
+    std::vector<cudaEvent_t> io_events;
     bool timing_open = false;
     int pending_launches = 0;
     double timed_ms = 0.0;
@@ -304,6 +307,9 @@ void mdr_phys_destroy(mdr_phys *p)
     if (!p) return;
     cudaSetDevice(p->cfg.gpu_id);
     if (p->stream) { cudaStreamSynchronize(p->stream); cudaStreamDestroy(p->stream); }
+    if (p->io_in) { cudaStreamSynchronize(p->io_in); cudaStreamDestroy(p->io_in); }
+    if (p->io_out) { cudaStreamSynchronize(p->io_out); cudaStreamDestroy(p->io_out); }
+    for (cudaEvent_t e : p->io_events) cudaEventDestroy(e);
     if (p->ev0) cudaEventDestroy(p->ev0);
     if (p->ev1) cudaEventDestroy(p->ev1);
     for (void *a : p->allocs) cudaFree(a);
@@ -426,12 +432,86 @@ int32_t mdr_phys_step_async(mdr_phys *p, int32_t num_steps)
     REQ_CUDA(cudaEventRecord(p->ev0, p->stream));
     for (int s = 0; s < num_steps; s++) {
         p->kernel<<<p->blocks, p->threads, p->smem_bytes, p->stream>>>(
-            p->params, p->threads_per_world, (int)p->slot_bytes, p->overflow_per_slot, p->lockstep);
+            p->params, p->threads_per_world, (int)p->slot_bytes, p->overflow_per_slot, p->lockstep,
+            0, p->cfg.num_worlds);
     }
     REQ_CUDA(cudaGetLastError());
     REQ_CUDA(cudaEventRecord(p->ev1, p->stream));
     p->timing_open = true;
     p->pending_launches = num_steps;
+    return MDR_OK;
+}
+
+// One step with host-side inputs and outputs, pipelined over world ranges: the
+// copy-in of range k+1 and the copy-out of range k-1 run beside the step of
+// range k (three streams). A range is a whole number of resident waves.
+int32_t mdr_phys_step_io_async(mdr_phys *p, int32_t num_in, const int32_t *in_cols, const void *const *in_host,
+                               int32_t num_out, const int32_t *out_cols, void *const *out_host, int32_t chunks)
+{
+    if (!p || num_in < 0 || num_out < 0 || (num_in && (!in_cols || !in_host)) || (num_out && (!out_cols || !out_host)))
+        return MDR_EINVAL;
+    for (int i = 0; i < num_in; i++) if (!colSlot(p->params.t, in_cols[i]) || !in_host[i]) return MDR_EINVAL;
+    for (int i = 0; i < num_out; i++) if (!colSlot(p->params.t, out_cols[i]) || !out_host[i]) return MDR_EINVAL;
+    REQ_CUDA(cudaSetDevice(p->cfg.gpu_id));
+    closeTiming(p);
+    const int W = p->cfg.num_worlds;
+    const int wave = p->blocks * p->worlds_per_block;
+    const int waves = (W + wave - 1) / wave;
+    if (chunks < 1) chunks = 1;
+    if (chunks > waves) chunks = waves;
+    const int per = (waves + chunks - 1) / chunks * wave;       // worlds per range
+    const int ranges = (W + per - 1) / per;
+    if (!p->io_in) {
+        REQ_CUDA(cudaStreamCreateWithFlags(&p->io_in, cudaStreamNonBlocking));
+        REQ_CUDA(cudaStreamCreateWithFlags(&p->io_out, cudaStreamNonBlocking));
+    }
+    while ((int)p->io_events.size() < 2 * ranges + 2) {
+        cudaEvent_t e;
+        REQ_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+        p->io_events.push_back(e);
+    }
+    if (p->maybe_rebuild) {
+        bvhRebuildKernel<<<(W + 63) / 64, 64, 0, p->stream>>>(p->params);
+        REQ_CUDA(cudaGetLastError());
+        p->maybe_rebuild = false;
+    }
+    // the side streams start after everything already queued on the executor's stream
+    cudaEvent_t start = p->io_events[2 * ranges], done = p->io_events[2 * ranges + 1];
+    REQ_CUDA(cudaEventRecord(start, p->stream));
+    REQ_CUDA(cudaStreamWaitEvent(p->io_in, start, 0));
+    REQ_CUDA(cudaStreamWaitEvent(p->io_out, start, 0));
+    REQ_CUDA(cudaEventRecord(p->ev0, p->stream));
+    const size_t stride = p->params.t.stride;
+    for (int r = 0; r < ranges; r++) {
+        const int first = r * per, end = first + per < W ? first + per : W;
+        for (int i = 0; i < num_in; i++) {
+            const size_t row = (size_t)kColBytes[in_cols[i]] * stride;
+            REQ_CUDA(cudaMemcpyAsync((char *)*colSlot(p->params.t, in_cols[i]) + row * first,
+                                     (const char *)in_host[i] + row * first, row * (end - first),
+                                     cudaMemcpyHostToDevice, p->io_in));
+        }
+        REQ_CUDA(cudaEventRecord(p->io_events[2 * r], p->io_in));
+        REQ_CUDA(cudaStreamWaitEvent(p->stream, p->io_events[2 * r], 0));
+        long long grid = ((long long)(end - first) + p->worlds_per_block - 1) / p->worlds_per_block;
+        if (grid > p->blocks) grid = p->blocks;
+        p->kernel<<<(int)grid, p->threads, p->smem_bytes, p->stream>>>(
+            p->params, p->threads_per_world, (int)p->slot_bytes, p->overflow_per_slot, p->lockstep, first, end);
+        REQ_CUDA(cudaGetLastError());
+        REQ_CUDA(cudaEventRecord(p->io_events[2 * r + 1], p->stream));
+        REQ_CUDA(cudaStreamWaitEvent(p->io_out, p->io_events[2 * r + 1], 0));
+        for (int i = 0; i < num_out; i++) {
+            const size_t row = (size_t)kColBytes[out_cols[i]] * stride;
+            REQ_CUDA(cudaMemcpyAsync((char *)out_host[i] + row * first,
+                                     (const char *)*colSlot(p->params.t, out_cols[i]) + row * first,
+                                     row * (end - first), cudaMemcpyDeviceToHost, p->io_out));
+        }
+    }
+    // mdr_phys_sync (the executor's stream) also covers the last copy-out
+    REQ_CUDA(cudaEventRecord(done, p->io_out));
+    REQ_CUDA(cudaStreamWaitEvent(p->stream, done, 0));
+    REQ_CUDA(cudaEventRecord(p->ev1, p->stream));
+    p->timing_open = true;
+    p->pending_launches = ranges;
     return MDR_OK;
 }
 

@@ -87,6 +87,8 @@ def bind(lib):
         lib.mdr_phys_row_stride.argtypes = [vp]
         lib.mdr_phys_write_column_raw_async.argtypes = [vp, i32, vp]
         lib.mdr_phys_read_column_raw_async.argtypes = [vp, i32, vp]
+        if hasattr(lib, "mdr_phys_step_io_async"):
+            lib.mdr_phys_step_io_async.argtypes = [vp, i32, vp, vp, i32, vp, vp, i32]
         lib.mdr_host_alloc.argtypes = [C.c_uint64]
         lib.mdr_host_alloc.restype = vp
         lib.mdr_host_free.argtypes = [vp]
@@ -286,6 +288,18 @@ class PhysExecutor:
 
     def read_raw_async(self, col, arr):
         self._check(self.lib.mdr_phys_read_column_raw_async(self.h, col, arr.ctypes.data), "read_raw")
+
+    def step_io_async(self, ins, outs, chunks=4):
+        """One step with host-side inputs / outputs [(column, raw host array)], pipelined
+        over `chunks` world ranges (copies overlap the step). sync() waits for it."""
+        def pack(pairs):
+            cols = (C.c_int32 * len(pairs))(*[c for c, _ in pairs])
+            ptrs = (C.c_void_p * len(pairs))(*[a.ctypes.data for _, a in pairs])
+            return cols, ptrs
+        ic, ip = pack(ins)
+        oc, op = pack(outs)
+        self._check(self.lib.mdr_phys_step_io_async(self.h, len(ins), ic, ip, len(outs), oc, op, chunks),
+                    "step_io")
 
     def launch_info(self):
         info = np.zeros(6, np.int32)

@@ -137,6 +137,15 @@ int32_t mdr_phys_flag_rebuild(mdr_phys *p);
 int32_t mdr_phys_step(mdr_phys *p, int32_t num_steps);
 int32_t mdr_phys_step_async(mdr_phys *p, int32_t num_steps);
 int32_t mdr_phys_sync(mdr_phys *p);
+/* One run() with host-side actions and observations, the trainer's loop around
+ * MWCudaExecutor::run() (copy actions into the exported columns, run, copy the
+ * observation columns out; src/mw/cuda_exec.cpp:1562-1579,1777-1794) as ONE
+ * call: the worlds are cut into `chunks` ranges and the copy-in of range k+1 and
+ * the copy-out of range k-1 overlap the step of range k. Host buffers are whole
+ * columns in the raw layout (num_worlds x row_stride elements), page-locked
+ * (mdr_host_alloc) for the copies to overlap. Enqueues only; mdr_phys_sync waits. */
+int32_t mdr_phys_step_io_async(mdr_phys *p, int32_t num_in, const int32_t *in_cols, const void *const *in_host,
+                               int32_t num_out, const int32_t *out_cols, void *const *out_host, int32_t chunks);
 void *mdr_phys_stream(mdr_phys *p);           /* cudaStream_t */
 
 /* One blocking step that also records the intermediates of `world`: the

@@ -176,3 +176,29 @@ def test_exported_column_pointer_is_in_place(cuda_lib):
     pos = host.reshape(sc.num_worlds, stride, 3)[:, :sc.bodies_per_world]
     assert np.array_equal(bits(pos), bits(e.state()[0]))
     del buf
+
+
+@pytest.mark.parametrize("chunks", [1, 2, 5])
+def test_step_io_pipeline_matches_plain_step(cuda_lib, chunks):
+    """mdr_phys_step_io_async (copy-in, step and copy-out pipelined over world ranges)
+    gives the bits of write -> step -> read, forces included."""
+    sc = scenes.collisions64(3000, num_cubes=7)      # several resident waves of worlds
+    a, b = phys.PhysExecutor(sc), phys.PhysExecutor(sc)
+    rng = np.random.default_rng(5)
+    in_cols = (phys.COL_EXT_FORCE, phys.COL_EXT_TORQUE)
+    out_cols = (phys.COL_POSITION, phys.COL_ROTATION, phys.COL_VELOCITY)
+    ins = [(c, b.pinned(c)) for c in in_cols]
+    outs = [(c, b.pinned(c)) for c in out_cols]
+    for st in range(6):
+        for c, arr in ins:
+            f = rng.uniform(-3, 3, (sc.num_worlds, b.row_stride(), 3)).astype(np.float32)
+            arr[:] = f.view(np.uint8).reshape(arr.shape)
+            a.write_raw_async(c, arr)
+        a.run(1)
+        b.step_io_async(ins, outs, chunks)
+        b.sync()
+        for c, arr in outs:
+            want = a.read(c)
+            got = arr.view(np.float32).reshape(sc.num_worlds, b.row_stride(), -1)[:, :sc.bodies_per_world]
+            assert np.array_equal(bits(got), bits(want)), (st, c)
+    assert_state_equal(b.state(), a.state(), None, "after pipelined steps")
