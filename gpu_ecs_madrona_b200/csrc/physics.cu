@@ -10,6 +10,7 @@
 #include <vector>
 
 #include "phys_step.cuh"
+#include "phys_lidar.cuh"
 #include "phys_assets.hpp"
 #include "phys_cols.hpp"
 
@@ -103,6 +104,9 @@ struct mdr_phys {
     // mdr_phys_step_io: copy-in / copy-out streams and per-chunk events
     cudaStream_t io_in = nullptr, io_out = nullptr;
     std::vector<cudaEvent_t> io_events;
+    // mdr_phys_trace_rays: device staging of the host-side ray buffers
+    char *ray_buf = nullptr;
+    size_t ray_buf_bytes = 0;
     bool timing_open = false;
     int pending_launches = 0;
     double timed_ms = 0.0;
@@ -307,6 +311,7 @@ void mdr_phys_destroy(mdr_phys *p)
     if (!p) return;
     cudaSetDevice(p->cfg.gpu_id);
     if (p->stream) { cudaStreamSynchronize(p->stream); cudaStreamDestroy(p->stream); }
+    if (p->ray_buf) cudaFree(p->ray_buf);
     if (p->io_in) { cudaStreamSynchronize(p->io_in); cudaStreamDestroy(p->io_in); }
     if (p->io_out) { cudaStreamSynchronize(p->io_out); cudaStreamDestroy(p->io_out); }
     for (cudaEvent_t e : p->io_events) cudaEventDestroy(e);
@@ -538,6 +543,59 @@ int32_t mdr_phys_step(mdr_phys *p, int32_t num_steps)
 }
 
 void *mdr_phys_stream(mdr_phys *p) { return p ? (void *)p->stream : nullptr; }
+
+int32_t mdr_phys_trace_rays_device(mdr_phys *p, int32_t rays_per_world, const float *origins, const float *dirs,
+                                   const float *t_max, float *out_t, float *out_normal, int32_t *out_entity,
+                                   int32_t *out_row)
+{
+    if (!p || rays_per_world < 0 || (rays_per_world && (!origins || !dirs || !out_t || !out_normal)))
+        return MDR_EINVAL;
+    if (rays_per_world == 0) return MDR_OK;
+    REQ_CUDA(cudaSetDevice(p->cfg.gpu_id));
+    RayJob job;
+    job.origins = origins; job.dirs = dirs; job.t_max = t_max;
+    job.out_t = out_t; job.out_normal = out_normal; job.out_entity = out_entity; job.out_row = out_row;
+    job.rays_per_world = rays_per_world;
+    const size_t smem = sizeof(RayLeaf) * (size_t)p->params.t.stride;
+    if (smem > 48 * 1024)
+        REQ_CUDA(cudaFuncSetAttribute(physTraceRaysKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const int threads = rays_per_world >= 128 ? 128 : (rays_per_world + 31) / 32 * 32;
+    physTraceRaysKernel<<<p->cfg.num_worlds, threads < 32 ? 32 : threads, smem, p->stream>>>(p->params.t, p->params.a, job);
+    REQ_CUDA(cudaGetLastError());
+    return MDR_OK;
+}
+
+int32_t mdr_phys_trace_rays(mdr_phys *p, int32_t rays_per_world, const float *origins, const float *dirs,
+                            const float *t_max, float *out_t, float *out_normal, int32_t *out_entity,
+                            int32_t *out_row)
+{
+    if (!p || rays_per_world < 0 || (rays_per_world && (!origins || !dirs || !out_t || !out_normal)))
+        return MDR_EINVAL;
+    if (rays_per_world == 0) return MDR_OK;
+    REQ_CUDA(cudaSetDevice(p->cfg.gpu_id));
+    const size_t n = (size_t)p->cfg.num_worlds * rays_per_world;
+    // origins 3, dirs 3, t_max 1, t 1, normal 3, entity 2, row 1 words per ray
+    const size_t need = n * 14 * 4;
+    if (need > p->ray_buf_bytes) {
+        REQ_CUDA(cudaStreamSynchronize(p->stream));
+        if (p->ray_buf) REQ_CUDA(cudaFree(p->ray_buf));
+        REQ_CUDA(cudaMalloc(&p->ray_buf, need));
+        p->ray_buf_bytes = need;
+    }
+    float *d_o = (float *)p->ray_buf, *d_d = d_o + 3 * n, *d_tm = d_d + 3 * n, *d_t = d_tm + n, *d_n = d_t + n;
+    int32_t *d_e = (int32_t *)(d_n + 3 * n), *d_r = d_e + 2 * n;
+    REQ_CUDA(cudaMemcpyAsync(d_o, origins, 12 * n, cudaMemcpyHostToDevice, p->stream));
+    REQ_CUDA(cudaMemcpyAsync(d_d, dirs, 12 * n, cudaMemcpyHostToDevice, p->stream));
+    if (t_max) REQ_CUDA(cudaMemcpyAsync(d_tm, t_max, 4 * n, cudaMemcpyHostToDevice, p->stream));
+    int32_t rc = mdr_phys_trace_rays_device(p, rays_per_world, d_o, d_d, t_max ? d_tm : nullptr, d_t, d_n, d_e, d_r);
+    if (rc != MDR_OK) return rc;
+    REQ_CUDA(cudaMemcpyAsync(out_t, d_t, 4 * n, cudaMemcpyDeviceToHost, p->stream));
+    REQ_CUDA(cudaMemcpyAsync(out_normal, d_n, 12 * n, cudaMemcpyDeviceToHost, p->stream));
+    if (out_entity) REQ_CUDA(cudaMemcpyAsync(out_entity, d_e, 8 * n, cudaMemcpyDeviceToHost, p->stream));
+    if (out_row) REQ_CUDA(cudaMemcpyAsync(out_row, d_r, 4 * n, cudaMemcpyDeviceToHost, p->stream));
+    REQ_CUDA(cudaStreamSynchronize(p->stream));
+    return MDR_OK;
+}
 
 int32_t mdr_phys_probe_step(mdr_phys *p, int32_t world, int32_t max_pairs, int32_t *num_pairs,
                             int32_t *pairs, int32_t *num_contacts, mdr_contact *contacts)

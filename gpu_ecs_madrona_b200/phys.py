@@ -75,6 +75,9 @@ def bind(lib):
     lib.mdr_phys_read_bvh.argtypes = [vp, vp, vp, vp]
     lib.mdr_phys_get_hull.argtypes = [vp, i32, vp, vp, vp, vp, vp]
     lib.mdr_version.restype = C.c_char_p
+    if hasattr(lib, "mdr_phys_trace_rays"):
+        lib.mdr_phys_trace_rays.argtypes = [vp, i32] + [vp] * 7
+        lib.mdr_phys_trace_rays_device.argtypes = [vp, i32] + [vp] * 7
     for name in ("mdr_phys_column_ptr", "mdr_phys_stream"):
         if hasattr(lib, name):
             getattr(lib, name).restype = vp
@@ -300,6 +303,22 @@ class PhysExecutor:
         oc, op = pack(outs)
         self._check(self.lib.mdr_phys_step_io_async(self.h, len(ins), ic, ip, len(outs), oc, op, chunks),
                     "step_io")
+
+    def trace_rays(self, origins, dirs, t_max=None):
+        """BVH::traceRay for [W, R, 3] host rays: (t[W,R], normal[W,R,3], entity[W,R,2], row[W,R])."""
+        o = np.ascontiguousarray(origins, np.float32)
+        d = np.ascontiguousarray(dirs, np.float32)
+        assert o.shape == d.shape and o.shape[0] == self.W and o.shape[2] == 3
+        R = o.shape[1]
+        tm = None if t_max is None else np.ascontiguousarray(np.broadcast_to(np.asarray(t_max, np.float32), (self.W, R)))
+        t = np.zeros((self.W, R), np.float32)
+        nrm = np.zeros((self.W, R, 3), np.float32)
+        ent = np.zeros((self.W, R, 2), np.int32)
+        row = np.zeros((self.W, R), np.int32)
+        self._check(self.lib.mdr_phys_trace_rays(self.h, R, o.ctypes.data, d.ctypes.data,
+                                                 None if tm is None else tm.ctypes.data, t.ctypes.data,
+                                                 nrm.ctypes.data, ent.ctypes.data, row.ctypes.data), "trace_rays")
+        return t, nrm, ent, row
 
     def launch_info(self):
         info = np.zeros(6, np.int32)

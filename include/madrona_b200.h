@@ -148,6 +148,24 @@ int32_t mdr_phys_step_io_async(mdr_phys *p, int32_t num_in, const int32_t *in_co
                                int32_t num_out, const int32_t *out_cols, void *const *out_host, int32_t chunks);
 void *mdr_phys_stream(mdr_phys *p);           /* cudaStream_t */
 
+/* broadphase::BVH::traceRay (src/physics/broadphase.cpp:653-856; declared
+ * include/madrona/physics.hpp:316-320), batched: `rays_per_world` rays in every
+ * world against the broadphase state the last step left (call after >= 1 step;
+ * the query behind CameraMode::Lidar, include/madrona/mw_render.hpp:9-13).
+ * All arrays are world-major: origins / dirs [W][R][3], t_max [W][R] or NULL
+ * (infinity); out_t [W][R] (t_max when nothing is hit), out_normal [W][R][3]
+ * (zeros when nothing is hit), out_entity [W][R][2] = (gen, id), Entity::none()
+ * = all ones when nothing is hit, out_row [W][R] = row of the hit body or -1
+ * (out_entity / out_row may be NULL). The _device form takes device pointers
+ * and only enqueues on the executor's stream; the other takes host pointers
+ * and blocks. */
+int32_t mdr_phys_trace_rays(mdr_phys *p, int32_t rays_per_world, const float *origins, const float *dirs,
+                            const float *t_max, float *out_t, float *out_normal, int32_t *out_entity,
+                            int32_t *out_row);
+int32_t mdr_phys_trace_rays_device(mdr_phys *p, int32_t rays_per_world, const float *origins, const float *dirs,
+                                   const float *t_max, float *out_t, float *out_normal, int32_t *out_entity,
+                                   int32_t *out_row);
+
 /* One blocking step that also records the intermediates of `world`: the
  * candidate pair list (reference order) and every substep's contact list.
  * pairs[2*max_pairs], num_contacts[substeps], contacts[substeps*max_contacts].*/

@@ -117,6 +117,14 @@ int32_t orc_get_hull(void *h, int32_t obj,
  * with a non-zero count are excluded from bit-exact comparison. The compiled
  * reference cannot know and reports -1. */
 void orc_indeterminate(void *h, int64_t *out /*[W]*/);
+/* BVH::traceRay (src/physics/broadphase.cpp:653-856) for n rays in world `world`,
+ * against the broadphase state the last step left (leaf transforms and slot
+ * boxes are refreshed at the end of every step; call after >= 1 step).
+ * origins / dirs [n][3], t_max [n]; out_t [n] (t_max when nothing is hit),
+ * out_normal [n][3] (zeros when nothing is hit: the reference leaves it
+ * unset), out_row [n] = row of the hit entity or -1. */
+void orc_trace_rays(void *h, int32_t world, int32_t n, const float *origins, const float *dirs,
+                    const float *t_max, float *out_t, float *out_normal, int32_t *out_row);
 const char *orc_kind(void);
 
 #ifdef __cplusplus

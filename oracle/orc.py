@@ -101,6 +101,7 @@ class Oracle:
         L.orc_flag_rebuild.argtypes = [C.c_void_p]
         L.orc_get_hull.argtypes = [C.c_void_p, C.c_int32] + [C.c_void_p] * 5
         L.orc_indeterminate.argtypes = [C.c_void_p, C.c_void_p]
+        L.orc_trace_rays.argtypes = [C.c_void_p, C.c_int32, C.c_int32] + [C.c_void_p] * 6
         L.orc_kind.restype = C.c_char_p
         self.kind = L.orc_kind().decode()
         self.scene = scene
@@ -162,6 +163,19 @@ class Oracle:
         return dict(pairs=pairs[:p.num_pairs].copy(), num_contacts=ncon,
                     contacts=[contacts[s, :ncon[s]].copy() for s in range(S)],
                     slot_boxes=slot, leaf_aabbs=leaf, ref_rank=rank)
+
+    def trace_rays(self, world, origins, dirs, t_max):
+        """BVH::traceRay for rays [n,3] in one world: (t[n], normal[n,3], row[n])."""
+        o = np.ascontiguousarray(origins, np.float32)
+        d = np.ascontiguousarray(dirs, np.float32)
+        n = o.shape[0]
+        tm = np.ascontiguousarray(np.broadcast_to(np.asarray(t_max, np.float32), (n,)))
+        t = np.zeros(n, np.float32)
+        nrm = np.zeros((n, 3), np.float32)
+        row = np.zeros(n, np.int32)
+        self.lib.orc_trace_rays(self.h, world, n, o.ctypes.data, d.ctypes.data, tm.ctypes.data,
+                                t.ctypes.data, nrm.ctypes.data, row.ctypes.data)
+        return t, nrm, row
 
     def indeterminate(self):
         out = np.zeros(self.scene.num_worlds, np.int64)

@@ -1306,6 +1306,111 @@ int32_t orc_probe_step(void *hp, int32_t world, orc_probe *out)
     return out->num_pairs > out->max_pairs ? -1 : 0;
 }
 
+// ------------------------------------------------------------- traceRay ---
+// AABB::rayIntersects, include/madrona/math.hpp:1043-1069
+static bool rayHitsBox(const Box &b, V3 o, V3 inv_d, float t_min, float t_max)
+{
+    V3 tl = { inv_d.x * (b.lo.x - o.x), inv_d.y * (b.lo.y - o.y), inv_d.z * (b.lo.z - o.z) };
+    V3 tu = { inv_d.x * (b.hi.x - o.x), inv_d.y * (b.hi.y - o.y), inv_d.z * (b.hi.z - o.z) };
+    float mn[4] = { fminf(tl.x, tu.x), fminf(tl.y, tu.y), fminf(tl.z, tu.z), t_min };
+    float mx[4] = { fmaxf(tl.x, tu.x), fmaxf(tl.y, tu.y), fmaxf(tl.z, tu.z), t_max };
+    float box_min = fmaxf(mn[0], fmaxf(mn[1], fmaxf(mn[2], mn[3])));
+    float box_max = fminf(mx[0], fminf(mx[1], fminf(mx[2], mx[3])));
+    return box_min <= box_max;
+}
+
+// BVH::traceRayIntoLeaf + traceRayIntoPlane + traceRayIntoConvexPolyhedron,
+// src/physics/broadphase.cpp:720-856. The leaf transform is the pose the last
+// updateLeafPosition saw (= the current one after a step).
+static bool rayIntoLeaf(const Sim &s, const World &w, int leaf, V3 wo, V3 wd, float t_min, float t_max,
+                        float *hit_t, V3 *hit_normal)
+{
+    const Object &obj = s.objs[w.obj[leaf]];
+    const Q4 to_local = qinv(w.rot[leaf]);
+    const V3 sc = w.scale[leaf];
+    V3 o = rotate(to_local, wo - w.pos[leaf]);
+    o = { o.x / sc.x, o.y / sc.y, o.z / sc.z };
+    V3 d = rotate(qinv(w.rot[leaf]), wd);
+    d = { d.x / sc.x, d.y / sc.y, d.z / sc.z };
+    V3 n = { 0.f, 0.f, 0.f };
+    bool hit;
+    if (obj.type == 2) {
+        float tfirst = t_min, tlast = t_max;
+        hit = true;
+        for (size_t f = 0; f < obj.hull.planes.size() && hit; f++) {
+            const Plane &pl = obj.hull.planes[f];
+            float denom = dot(pl.n, d);
+            float neg_dist = pl.d - dot(pl.n, o);
+            if (denom == 0.0f) {
+                if (neg_dist < 0.0f) hit = false;
+            } else {
+                float t = neg_dist / denom;
+                if (denom < 0.0f) {
+                    if (t >= tfirst) { tfirst = t; n = pl.n; }
+                } else {
+                    if (t <= tlast) tlast = t;
+                }
+                if (tfirst > tlast) hit = false;
+            }
+        }
+        if (hit && n.x == 0 && n.y == 0 && n.z == 0) hit = false;
+        if (hit) *hit_t = tfirst;
+    } else {
+        float denom = d.z;
+        hit = denom != 0;
+        if (hit) {
+            float t = -o.z / denom;
+            hit = !(t < t_min || t > t_max);
+            if (hit) { *hit_t = t; n = { 0.f, 0.f, 1.f }; }
+        }
+    }
+    // the reference rotates whatever normal the primitive test left, hit or not
+    *hit_normal = rotate(w.rot[leaf], n);
+    return hit;
+}
+
+// BVH::traceRay, src/physics/broadphase.cpp:653-718
+void orc_trace_rays(void *hp, int32_t world, int32_t n, const float *origins, const float *dirs,
+                    const float *t_maxs, float *out_t, float *out_normal, int32_t *out_row)
+{
+    Sim *s = (Sim *)hp;
+    const World &w = s->worlds[world];
+    for (int r = 0; r < n; r++) {
+        const V3 o = { origins[3*r], origins[3*r+1], origins[3*r+2] };
+        const V3 d = { dirs[3*r], dirs[3*r+1], dirs[3*r+2] };
+        const V3 inv_d = { 1.f / d.x, 1.f / d.y, 1.f / d.z };
+        float t_max = t_maxs[r];
+        int32_t closest = -1;
+        V3 closest_n = { 0.f, 0.f, 0.f };
+        int32_t stack[128];
+        stack[0] = 0;
+        int sz = 1;
+        while (sz > 0) {
+            const BVHNode &nd = w.nodes[stack[--sz]];
+            for (int i = 0; i < 4; i++) {
+                if (nd.children[i] == kSentinel) continue;
+                Box cb { { nd.minX[i], nd.minY[i], nd.minZ[i] }, { nd.maxX[i], nd.maxY[i], nd.maxZ[i] } };
+                if (!rayHitsBox(cb, o, inv_d, 0.f, t_max)) continue;
+                if (nd.children[i] & 0x80000000) {
+                    const int32_t leaf = nd.children[i] & ~0x80000000;
+                    float hit_t;
+                    V3 hn;
+                    if (rayIntoLeaf(*s, w, leaf, o, d, 0.f, t_max, &hit_t, &hn)) {
+                        t_max = hit_t;
+                        closest = leaf;
+                        closest_n = hn;
+                    }
+                } else {
+                    stack[sz++] = nd.children[i];
+                }
+            }
+        }
+        out_t[r] = t_max;
+        out_row[r] = closest;
+        out_normal[3*r] = closest_n.x; out_normal[3*r+1] = closest_n.y; out_normal[3*r+2] = closest_n.z;
+    }
+}
+
 void orc_indeterminate(void *hp, int64_t *out)
 {
     Sim *s = (Sim *)hp;

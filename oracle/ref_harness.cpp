@@ -357,6 +357,28 @@ int32_t orc_probe_step(void *hp, int32_t world, orc_probe *out)
     return rc;
 }
 
+void orc_trace_rays(void *hp, int32_t world, int32_t n, const float *origins, const float *dirs,
+                    const float *t_max, float *out_t, float *out_normal, int32_t *out_row)
+{
+    Handle *h = (Handle *)hp;
+    World &w = h->worlds[world];
+    auto &bvh = w.ctx->getSingleton<broadphase::BVH>();
+    for (int i = 0; i < n; i++) {
+        float t = 0.f;
+        Vector3 nrm { 0.f, 0.f, 0.f };
+        Entity e = bvh.traceRay(Vector3 { origins[3*i], origins[3*i+1], origins[3*i+2] },
+                                Vector3 { dirs[3*i], dirs[3*i+1], dirs[3*i+2] }, &t, &nrm, t_max[i]);
+        out_t[i] = t;
+        if (e == Entity::none()) {
+            out_row[i] = -1;
+            out_normal[3*i] = out_normal[3*i+1] = out_normal[3*i+2] = 0.f;
+        } else {
+            out_row[i] = w.ctx->getLoc(e).row;
+            out_normal[3*i] = nrm.x; out_normal[3*i+1] = nrm.y; out_normal[3*i+2] = nrm.z;
+        }
+    }
+}
+
 void orc_indeterminate(void *hp, int64_t *out)
 {
     Handle *h = (Handle *)hp;

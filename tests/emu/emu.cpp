@@ -13,6 +13,7 @@
 #include <vector>
 
 #include "../../gpu_ecs_madrona_b200/csrc/phys_step.cuh"
+#include "../../gpu_ecs_madrona_b200/csrc/phys_lidar.cuh"
 #include "../../gpu_ecs_madrona_b200/csrc/phys_assets.hpp"
 #include "../../gpu_ecs_madrona_b200/csrc/phys_cols.hpp"
 
@@ -240,6 +241,52 @@ int32_t mdr_phys_get_hull(mdr_phys *p, int32_t obj, uint32_t *half_edges, uint32
     memcpy(polys, p->assets.polys.data() + o.face_off, 4 * (size_t)o.num_faces);
     memcpy(planes, p->assets.planes.data() + 4 * (size_t)o.face_off, 16 * (size_t)o.num_faces);
     return MDR_OK;
+}
+
+// physTraceRaysKernel's body, one world after the other.
+int32_t mdr_phys_trace_rays(mdr_phys *p, int32_t R, const float *origins, const float *dirs, const float *t_max,
+                            float *out_t, float *out_normal, int32_t *out_entity, int32_t *out_row)
+{
+    PhysTables &t = p->params.t;
+    std::vector<RayLeaf> leaves(t.stride);
+    for (int w = 0; w < p->cfg.num_worlds; w++) {
+        const size_t r0 = (size_t)w * t.stride;
+        const int n = t.row_count[w];
+        for (int r = 0; r < n; r++) {
+            const int leaf = t.order[r0 + r];
+            const size_t i = r0 + leaf;
+            RayLeaf lf;
+            for (int k = 0; k < 3; k++) {
+                lf.lo[k] = t.slot_box[6 * i + k]; lf.hi[k] = t.slot_box[6 * i + 3 + k];
+                lf.pos[k] = t.pos[3 * i + k]; lf.scale[k] = t.scale[3 * i + k];
+            }
+            for (int k = 0; k < 4; k++) lf.rot[k] = t.rot[4 * i + k];
+            lf.obj = (t.obj[i] & 0xffff) | (leaf << 16);
+            leaves[r] = lf;
+        }
+        for (int k = 0; k < R; k++) {
+            const size_t ri = (size_t)w * R + k;
+            float hit_t;
+            V3 hn;
+            int row;
+            traceRay(p->params.a, leaves.data(), n, mk3(origins[3 * ri], origins[3 * ri + 1], origins[3 * ri + 2]),
+                     mk3(dirs[3 * ri], dirs[3 * ri + 1], dirs[3 * ri + 2]), t_max ? t_max[ri] : INFINITY,
+                     &hit_t, &hn, &row);
+            out_t[ri] = hit_t;
+            out_normal[3 * ri] = hn.x; out_normal[3 * ri + 1] = hn.y; out_normal[3 * ri + 2] = hn.z;
+            if (out_row) out_row[ri] = row;
+            if (out_entity) {
+                out_entity[2 * ri] = row >= 0 ? t.entity[2 * (r0 + row)] : -1;
+                out_entity[2 * ri + 1] = row >= 0 ? t.entity[2 * (r0 + row) + 1] : -1;
+            }
+        }
+    }
+    return MDR_OK;
+}
+int32_t mdr_phys_trace_rays_device(mdr_phys *p, int32_t R, const float *o, const float *d, const float *tm,
+                                   float *ot, float *on, int32_t *oe, int32_t *orow)
+{
+    return mdr_phys_trace_rays(p, R, o, d, tm, ot, on, oe, orow);
 }
 
 }
