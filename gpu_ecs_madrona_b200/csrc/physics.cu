@@ -11,6 +11,7 @@
 
 #include "phys_step.cuh"
 #include "phys_lidar.cuh"
+#include "phys_feeder.cuh"
 #include "phys_assets.hpp"
 #include "phys_cols.hpp"
 
@@ -543,6 +544,46 @@ int32_t mdr_phys_step(mdr_phys *p, int32_t num_steps)
 }
 
 void *mdr_phys_stream(mdr_phys *p) { return p ? (void *)p->stream : nullptr; }
+
+int32_t mdr_phys_pack_instances(mdr_phys *p, const float *world_offset, float *out_transforms,
+                                int32_t *out_object_ids)
+{
+    if (!p || !out_transforms || !out_object_ids) return MDR_EINVAL;
+    REQ_CUDA(cudaSetDevice(p->cfg.gpu_id));
+    FeederJob job;
+    memset(&job, 0, sizeof(job));
+    for (int k = 0; k < 3; k++) job.world_offset[k] = world_offset ? world_offset[k] : 0.f;
+    job.transforms = out_transforms;
+    job.object_ids = out_object_ids;
+    const size_t total = (size_t)p->cfg.num_worlds * p->params.t.stride;
+    const int blocks = (int)((total + 255) / 256 < 148 * 8 ? (total + 255) / 256 : 148 * 8);
+    physFeedInstancesKernel<<<blocks, 256, 0, p->stream>>>(p->params.t, job);
+    REQ_CUDA(cudaGetLastError());
+    return MDR_OK;
+}
+
+int32_t mdr_phys_pack_views(mdr_phys *p, int32_t views_per_world, const int32_t *view_rows,
+                            const float *camera_offset, const float *y_scale, const float *world_offset,
+                            float *out_views)
+{
+    if (!p || views_per_world < 0 || (views_per_world && (!view_rows || !camera_offset || !y_scale || !out_views)))
+        return MDR_EINVAL;
+    if (views_per_world == 0) return MDR_OK;
+    REQ_CUDA(cudaSetDevice(p->cfg.gpu_id));
+    FeederJob job;
+    memset(&job, 0, sizeof(job));
+    for (int k = 0; k < 3; k++) job.world_offset[k] = world_offset ? world_offset[k] : 0.f;
+    job.views_per_world = views_per_world;
+    job.view_rows = view_rows;
+    job.camera_offset = camera_offset;
+    job.y_scale = y_scale;
+    job.views = out_views;
+    const size_t total = (size_t)p->cfg.num_worlds * views_per_world;
+    const int blocks = (int)((total + 255) / 256 < 148 * 8 ? (total + 255) / 256 : 148 * 8);
+    physFeedViewsKernel<<<blocks, 256, 0, p->stream>>>(p->params.t, job);
+    REQ_CUDA(cudaGetLastError());
+    return MDR_OK;
+}
 
 int32_t mdr_phys_trace_rays_device(mdr_phys *p, int32_t rays_per_world, const float *origins, const float *dirs,
                                    const float *t_max, float *out_t, float *out_normal, int32_t *out_entity,

@@ -75,6 +75,9 @@ def bind(lib):
     lib.mdr_phys_read_bvh.argtypes = [vp, vp, vp, vp]
     lib.mdr_phys_get_hull.argtypes = [vp, i32, vp, vp, vp, vp, vp]
     lib.mdr_version.restype = C.c_char_p
+    if hasattr(lib, "mdr_phys_pack_instances"):
+        lib.mdr_phys_pack_instances.argtypes = [vp, vp, vp, vp]
+        lib.mdr_phys_pack_views.argtypes = [vp, i32, vp, vp, vp, vp, vp]
     if hasattr(lib, "mdr_phys_trace_rays"):
         lib.mdr_phys_trace_rays.argtypes = [vp, i32] + [vp] * 7
         lib.mdr_phys_trace_rays_device.argtypes = [vp, i32] + [vp] * 7
@@ -303,6 +306,20 @@ class PhysExecutor:
         oc, op = pack(outs)
         self._check(self.lib.mdr_phys_step_io_async(self.h, len(ins), ic, ip, len(outs), oc, op, chunks),
                     "step_io")
+
+    def pack_instances(self, out_transforms, out_object_ids, world_offset=None):
+        """instanceTransformSetup into buffers [W, row_stride, 12] f32 / [W, row_stride] i32
+        given as raw addresses (device pointers on the CUDA library). Enqueues only."""
+        off = None if world_offset is None else np.ascontiguousarray(world_offset, np.float32)
+        self._check(self.lib.mdr_phys_pack_instances(self.h, None if off is None else off.ctypes.data,
+                                                     out_transforms, out_object_ids), "pack_instances")
+
+    def pack_views(self, view_rows, camera_offset, y_scale, out_views, views_per_world, world_offset=None):
+        """updateViewData into [W, V, 8] f32; all arrays raw addresses (device pointers on CUDA)."""
+        off = None if world_offset is None else np.ascontiguousarray(world_offset, np.float32)
+        self._check(self.lib.mdr_phys_pack_views(self.h, views_per_world, view_rows, camera_offset, y_scale,
+                                                 None if off is None else off.ctypes.data, out_views),
+                    "pack_views")
 
     def trace_rays(self, origins, dirs, t_max=None):
         """BVH::traceRay for [W, R, 3] host rays: (t[W,R], normal[W,R,3], entity[W,R,2], row[W,R])."""

@@ -159,6 +159,24 @@ void *mdr_phys_stream(mdr_phys *p);           /* cudaStream_t */
  * (out_entity / out_row may be NULL). The _device form takes device pointers
  * and only enqueues on the executor's stream; the other takes host pointers
  * and blocks. */
+/* The observation feeder: RenderingSystem's two nodes (src/mw/render/interop.cpp:
+ * 10-96, setupTasks :112-139) writing to plain DEVICE buffers instead of a Vulkan /
+ * Metal renderer's (graphics APIs: unavailable on this box). Enqueued on the
+ * executor's stream. `world_offset` is a host float[3] or NULL (zero).
+ *  pack_instances = instanceTransformSetup: out_transforms [W][row_stride][12] is the
+ *   row-major 3x4 object-to-world matrix Mat3x4::fromTRS(pos + world_offset, rot,
+ *   scale) of every body (translation in column 3, interop.cpp:27-41),
+ *   out_object_ids [W][row_stride] its ObjectID (-1 and a zero matrix past a world's
+ *   rows). World-major row order (the reference appends by an atomic counter).
+ *  pack_views = updateViewData: out_views [W][V][8] = PackedViewData {rotation
+ *   w,x,y,z; pos + camera_offset + world_offset; y_scale} of the body in row
+ *   view_rows[w][v] (ViewSettings, include/madrona/mw_render.hpp:19-25). */
+int32_t mdr_phys_pack_instances(mdr_phys *p, const float *world_offset, float *out_transforms,
+                                int32_t *out_object_ids);
+int32_t mdr_phys_pack_views(mdr_phys *p, int32_t views_per_world, const int32_t *view_rows,
+                            const float *camera_offset, const float *y_scale, const float *world_offset,
+                            float *out_views);
+
 int32_t mdr_phys_trace_rays(mdr_phys *p, int32_t rays_per_world, const float *origins, const float *dirs,
                             const float *t_max, float *out_t, float *out_normal, int32_t *out_entity,
                             int32_t *out_row);

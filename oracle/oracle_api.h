@@ -125,6 +125,13 @@ void orc_indeterminate(void *h, int64_t *out /*[W]*/);
  * unset), out_row [n] = row of the hit entity or -1. */
 void orc_trace_rays(void *h, int32_t world, int32_t n, const float *origins, const float *dirs,
                     const float *t_max, float *out_t, float *out_normal, int32_t *out_row);
+/* The renderer feeder's arithmetic (src/mw/render/interop.cpp:10-96) on the
+ * checker's own columns: out_transforms [W][N][12] = row-major 3x4
+ * Mat3x4::fromTRS(pos + world_offset, rot, scale) as interop.cpp:27-41 lays it
+ * out; out_views [W][V][8] = {rot w,x,y,z; pos + camera_offset + world_offset;
+ * y_scale} of the body in view_rows[w][v] (interop.cpp:69-79). */
+void orc_feeder(void *h, const float *world_offset, float *out_transforms, int32_t views_per_world,
+                const int32_t *view_rows, const float *camera_offset, const float *y_scale, float *out_views);
 const char *orc_kind(void);
 
 #ifdef __cplusplus

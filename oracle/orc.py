@@ -102,6 +102,7 @@ class Oracle:
         L.orc_get_hull.argtypes = [C.c_void_p, C.c_int32] + [C.c_void_p] * 5
         L.orc_indeterminate.argtypes = [C.c_void_p, C.c_void_p]
         L.orc_trace_rays.argtypes = [C.c_void_p, C.c_int32, C.c_int32] + [C.c_void_p] * 6
+        L.orc_feeder.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32] + [C.c_void_p] * 4
         L.orc_kind.restype = C.c_char_p
         self.kind = L.orc_kind().decode()
         self.scene = scene
@@ -176,6 +177,20 @@ class Oracle:
         self.lib.orc_trace_rays(self.h, world, n, o.ctypes.data, d.ctypes.data, tm.ctypes.data,
                                 t.ctypes.data, nrm.ctypes.data, row.ctypes.data)
         return t, nrm, row
+
+    def feeder(self, world_offset, view_rows, camera_offset, y_scale):
+        """(transforms[W,N,12], views[W,V,8]) of the renderer feeder's arithmetic."""
+        W, N = self.scene.num_worlds, self.scene.bodies_per_world
+        off = np.ascontiguousarray(world_offset, np.float32)
+        rows = np.ascontiguousarray(view_rows, np.int32)
+        cam = np.ascontiguousarray(camera_offset, np.float32)
+        ys = np.ascontiguousarray(y_scale, np.float32)
+        V = rows.shape[1]
+        tr = np.zeros((W, N, 12), np.float32)
+        views = np.zeros((W, V, 8), np.float32)
+        self.lib.orc_feeder(self.h, off.ctypes.data, tr.ctypes.data, V, rows.ctypes.data, cam.ctypes.data,
+                            ys.ctypes.data, views.ctypes.data)
+        return tr, views
 
     def indeterminate(self):
         out = np.zeros(self.scene.num_worlds, np.int64)

@@ -1411,6 +1411,41 @@ void orc_trace_rays(void *hp, int32_t world, int32_t n, const float *origins, co
     }
 }
 
+// instanceTransformSetup / updateViewData, src/mw/render/interop.cpp:10-96;
+// Mat3x4::fromTRS, include/madrona/math.hpp:929-962
+void orc_feeder(void *hp, const float *world_offset, float *out_transforms, int32_t V,
+                const int32_t *view_rows, const float *camera_offset, const float *y_scale, float *out_views)
+{
+    Sim *s = (Sim *)hp;
+    const V3 off = { world_offset[0], world_offset[1], world_offset[2] };
+    for (size_t wi = 0; wi < s->worlds.size(); wi++) {
+        const World &w = s->worlds[wi];
+        for (int i = 0; i < w.N; i++) {
+            const V3 t = w.pos[i] + off, sc = w.scale[i];
+            const Q4 r = w.rot[i];
+            float x2 = r.x * r.x, y2 = r.y * r.y, z2 = r.z * r.z;
+            float xz = r.x * r.z, xy = r.x * r.y, yz = r.y * r.z;
+            float wx = r.w * r.x, wy = r.w * r.y, wz = r.w * r.z;
+            V3 ds = { 2.f * sc.x, 2.f * sc.y, 2.f * sc.z };
+            V3 c0 = { sc.x - ds.x * (y2 + z2), ds.x * (xy + wz), ds.x * (xz - wy) };
+            V3 c1 = { ds.y * (xy - wz), sc.y - ds.y * (x2 + z2), ds.y * (yz + wx) };
+            V3 c2 = { ds.z * (xz + wy), ds.z * (yz - wx), sc.z - ds.z * (x2 + y2) };
+            float *m = out_transforms + 12 * (wi * w.N + i);
+            m[0] = c0.x; m[1] = c1.x; m[2] = c2.x; m[3] = t.x;
+            m[4] = c0.y; m[5] = c1.y; m[6] = c2.y; m[7] = t.y;
+            m[8] = c0.z; m[9] = c1.z; m[10] = c2.z; m[11] = t.z;
+        }
+        for (int k = 0; k < V; k++) {
+            const size_t vi = wi * V + k;
+            const int row = view_rows[vi];
+            const V3 cam = w.pos[row] + V3 { camera_offset[3*vi], camera_offset[3*vi+1], camera_offset[3*vi+2] } + off;
+            float *o = out_views + 8 * vi;
+            o[0] = w.rot[row].w; o[1] = w.rot[row].x; o[2] = w.rot[row].y; o[3] = w.rot[row].z;
+            o[4] = cam.x; o[5] = cam.y; o[6] = cam.z; o[7] = y_scale[vi];
+        }
+    }
+}
+
 void orc_indeterminate(void *hp, int64_t *out)
 {
     Sim *s = (Sim *)hp;

@@ -379,6 +379,41 @@ void orc_trace_rays(void *hp, int32_t world, int32_t n, const float *origins, co
     }
 }
 
+void orc_feeder(void *hp, const float *world_offset, float *out_transforms, int32_t V,
+                const int32_t *view_rows, const float *camera_offset, const float *y_scale, float *out_views)
+{
+    Handle *h = (Handle *)hp;
+    const int N = h->cfg.bodies_per_world;
+    const Vector3 off { world_offset[0], world_offset[1], world_offset[2] };
+    for (size_t wi = 0; wi < h->worlds.size(); wi++) {
+        World &w = h->worlds[wi];
+        for (int i = 0; i < N; i++) {
+            const Position &pos = *(const Position *)colPtr(w, ORC_COL_POSITION, i);
+            const Rotation &rot = *(const Rotation *)colPtr(w, ORC_COL_ROTATION, i);
+            const Scale &scale = *(const Scale *)colPtr(w, ORC_COL_SCALE, i);
+            // the statements of instanceTransformSetup, interop.cpp:25-41
+            Mat3x4 o2w = Mat3x4::fromTRS(pos + off, rot, scale);
+            float (*m)[4] = (float (*)[4])(out_transforms + 12 * (wi * N + i));
+            m[0][0] = o2w.cols[0].x; m[0][1] = o2w.cols[1].x; m[0][2] = o2w.cols[2].x; m[0][3] = o2w.cols[3].x;
+            m[1][0] = o2w.cols[0].y; m[1][1] = o2w.cols[1].y; m[1][2] = o2w.cols[2].y; m[1][3] = o2w.cols[3].y;
+            m[2][0] = o2w.cols[0].z; m[2][1] = o2w.cols[1].z; m[2][2] = o2w.cols[2].z; m[2][3] = o2w.cols[3].z;
+        }
+        for (int k = 0; k < V; k++) {
+            const size_t vi = wi * V + k;
+            const int row = view_rows[vi];
+            const Position &pos = *(const Position *)colPtr(w, ORC_COL_POSITION, row);
+            const Rotation &rot = *(const Rotation *)colPtr(w, ORC_COL_ROTATION, row);
+            const Vector3 cam_off { camera_offset[3*vi], camera_offset[3*vi+1], camera_offset[3*vi+2] };
+            // updateViewData, interop.cpp:69-79
+            auto camera_pos = pos + cam_off + off;
+            float *o = out_views + 8 * vi;
+            Quat q = rot;
+            o[0] = q.w; o[1] = q.x; o[2] = q.y; o[3] = q.z;
+            o[4] = camera_pos.x; o[5] = camera_pos.y; o[6] = camera_pos.z; o[7] = y_scale[vi];
+        }
+    }
+}
+
 void orc_indeterminate(void *hp, int64_t *out)
 {
     Handle *h = (Handle *)hp;

@@ -14,6 +14,7 @@
 
 #include "../../gpu_ecs_madrona_b200/csrc/phys_step.cuh"
 #include "../../gpu_ecs_madrona_b200/csrc/phys_lidar.cuh"
+#include "../../gpu_ecs_madrona_b200/csrc/phys_feeder.cuh"
 #include "../../gpu_ecs_madrona_b200/csrc/phys_assets.hpp"
 #include "../../gpu_ecs_madrona_b200/csrc/phys_cols.hpp"
 
@@ -288,5 +289,31 @@ int32_t mdr_phys_trace_rays_device(mdr_phys *p, int32_t R, const float *o, const
 {
     return mdr_phys_trace_rays(p, R, o, d, tm, ot, on, oe, orow);
 }
+
+// the feeder kernels' bodies over host buffers
+int32_t mdr_phys_pack_instances(mdr_phys *p, const float *world_offset, float *out_transforms, int32_t *out_object_ids)
+{
+    FeederJob job;
+    memset(&job, 0, sizeof(job));
+    for (int k = 0; k < 3; k++) job.world_offset[k] = world_offset ? world_offset[k] : 0.f;
+    job.transforms = out_transforms;
+    job.object_ids = out_object_ids;
+    for (int w = 0; w < p->cfg.num_worlds; w++)
+        for (int i = 0; i < p->params.t.stride; i++) feedInstance(p->params.t, job, w, i);
+    return MDR_OK;
+}
+int32_t mdr_phys_pack_views(mdr_phys *p, int32_t V, const int32_t *view_rows, const float *camera_offset,
+                            const float *y_scale, const float *world_offset, float *out_views)
+{
+    FeederJob job;
+    memset(&job, 0, sizeof(job));
+    for (int k = 0; k < 3; k++) job.world_offset[k] = world_offset ? world_offset[k] : 0.f;
+    job.views_per_world = V; job.view_rows = view_rows; job.camera_offset = camera_offset;
+    job.y_scale = y_scale; job.views = out_views;
+    for (int w = 0; w < p->cfg.num_worlds; w++)
+        for (int k = 0; k < V; k++) feedView(p->params.t, job, w, k);
+    return MDR_OK;
+}
+int32_t mdr_phys_row_stride(mdr_phys *p) { return p->params.t.stride; }
 
 }
