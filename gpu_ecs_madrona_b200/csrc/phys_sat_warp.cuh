@@ -22,6 +22,47 @@ __device__ __forceinline__ V3 shfl3(V3 v, int src)
                __shfl_sync(MDR_FULL, v.z, src));
 }
 
+// Vertex k of a hull whose world vertices sit one per lane. Every lane of the
+// warp must call at() together (contact generation below runs on all lanes
+// with identical inputs, so its control flow is uniform).
+struct LaneVerts {
+    V3 mine;
+    __device__ __forceinline__ V3 at(int k) const { return shfl3(mine, k); }
+};
+
+// emitContact with one contact point per lane (lanes 0..3); every lane holds
+// the same manifold.
+__device__ __forceinline__ void emitContactLanes(WorldView &v, const StepParams &p, SolverContact *sc,
+                                                 const Manifold &m, int ref, int alt, int lane)
+{
+    const bool s1 = !(v.meta[ref] & META_DEP), s2 = !(v.meta[alt] & META_DEP);
+    if (lane == 0) {
+        sc->hdr = (uint32_t)ref | ((uint32_t)alt << 10) | ((uint32_t)m.n << 20) |
+                  ((uint32_t)s1 << 24) | ((uint32_t)s2 << 25);
+        sc->normal[0] = m.normal.x; sc->normal[1] = m.normal.y; sc->normal[2] = m.normal.z;
+    }
+    if (lane >= 4) return;
+    const int i = lane;
+    sc->lambda[i] = 0.f;
+    if (i >= m.n) return;
+    const V3 c1 = i == 0 ? m.pts[0] : i == 1 ? m.pts[1] : i == 2 ? m.pts[2] : m.pts[3];
+    const float depth = i == 0 ? m.depths[0] : i == 1 ? m.depths[1] : i == 2 ? m.depths[2] : m.depths[3];
+    const V3 x1 = ld3(v.pos, ref), x2 = ld3(v.pos, alt);
+    const Q4 q1 = ld4(v.rot, ref), q2 = ld4(v.rot, alt);
+    const V3 zero = mk3(0.f, 0.f, 0.f);
+    const V3 c2 = c1 - m.normal * depth;
+    const V3 r1 = rotate(qinv(q1), c1 - x1);
+    const V3 r2 = rotate(qinv(q2), c2 - x2);
+    const V3 r1w = rotate(q1, r1), r2w = rotate(q2, r2);
+    const V3 va = s1 ? zero : ldVelLin(v.prev_vel, ref) + cross(ldVelAng(v.prev_vel, ref), r1w);
+    const V3 vb = s2 ? zero : ldVelLin(v.prev_vel, alt) + cross(ldVelAng(v.prev_vel, alt), r2w);
+    sc->vn_bar[i] = dot(m.normal, va - vb);
+    const V3 o1 = s1 ? r1w + x1 : r1;
+    const V3 o2 = s2 ? r2w + x2 : r2;
+    sc->r1[i][0] = o1.x; sc->r1[i][1] = o1.y; sc->r1[i][2] = o1.z;
+    sc->r2[i][0] = o2.x; sc->r2[i][1] = o2.y; sc->r2[i][2] = o2.z;
+}
+
 // Arg-max over the warp: largest value, lowest index on ties. All lanes get it.
 __device__ __forceinline__ void warpArgMax(float &val, int &idx)
 {
@@ -148,8 +189,8 @@ __device__ __forceinline__ void hullHullWarp(WorldView &v, const StepParams &p, 
         const EdgeWin eq = edgeQueryWarp(lane, va, pa, ta.he, edges_a, nea, xa.t, vb, pb, tb.he, edges_b, neb);
         if (eq.sep > 0.0f) break;
         const bool face_a = fa_sep > eq.sep, face_b = fb_sep > eq.sep;
-        XfVerts xva, xvb;
-        xva.x = xa; xva.src = src_va; xvb.x = xb; xvb.src = src_vb;
+        LaneVerts xva, xvb;
+        xva.mine = va; xvb.mine = vb;
         if (face_a || face_b) {
             const bool a_ref = fa_sep >= fb_sep;
             const int rf = a_ref ? fa_face : fb_face;
@@ -163,24 +204,20 @@ __device__ __forceinline__ void hullHullWarp(WorldView &v, const StepParams &p, 
             float neg = lane < nfo ? -dot(po.n, rp.n) : -FLT_MAX;
             int inc = lane;
             warpArgMax(neg, inc);
-            if (lane == 0) {
-                if (a_ref) faceContact(m, rp, rf, inc, ta, xva, tb, xvb);
-                else faceContact(m, rp, rf, inc, tb, xvb, ta, xva);
-            }
+            // all lanes, same inputs: vertices come by shuffle instead of being recomputed
+            if (a_ref) faceContact(m, rp, rf, inc, ta, xva, tb, xvb);
+            else faceContact(m, rp, rf, inc, tb, xvb, ta, xva);
             ref = a_ref ? a : b;
             alt = a_ref ? b : a;
         } else {
-            if (lane == 0) edgeContact(m, eq.normal, eq.sep, eq.ea, eq.eb, ta, xva, tb, xvb);
+            edgeContact(m, eq.normal, eq.sep, eq.ea, eq.eb, ta, xva, tb, xvb);
             ref = a; alt = b;
         }
         hit = true;
     } while (false);
-    if (lane == 0) {
-        SolverContact *sc = contactSlot(v, pi);
-        const bool emit = hit && m.n > 0;
-        if (emit) emitContact(v, p, sc, m, ref, alt);
-        if (probing) probeContact(p, sub, pi, emit ? &m : nullptr, ref, alt);
-    }
+    const bool emit = hit && m.n > 0;
+    if (emit) emitContactLanes(v, p, contactSlot(v, pi), m, ref, alt, lane);
+    if (lane == 0 && probing) probeContact(p, sub, pi, emit ? &m : nullptr, ref, alt);
 }
 
 // The queue: all warps of the world's thread group take queued pairs in turn.
