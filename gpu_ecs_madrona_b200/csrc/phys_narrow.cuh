@@ -528,7 +528,8 @@ MDR_HD void narrowphasePair(WorldView &v, const StepParams &p, int pi, bool prob
 {
     SolverContact *sc = contactSlot(v, pi);
     sc->hdr = 0;
-    const uint32_t pr = v.pairs[pi];
+    uint32_t pr = v.pairs[pi];
+    if (pr & PAIR_SAT) { pr &= ~PAIR_SAT; v.pairs[pi] = pr; }     // last substep's mark
     int a = pr & 1023, b = (pr >> 10) & 1023;
     // order by primitive type bits: hull (2) before plane (4)
     if (!(v.meta[a] & META_HULL) && (v.meta[b] & META_HULL)) { int t = a; a = b; b = t; }
@@ -538,17 +539,14 @@ MDR_HD void narrowphasePair(WorldView &v, const StepParams &p, int pi, bool prob
     if (overlaps(ldBox(v.box, a), ldBox(v.box, b))) {
         if (a_hull && b_hull) {
 #if defined(__CUDA_ARCH__)
-            // hand the pair to a whole warp (phys_sat_warp.cuh); the serial
-            // path below only takes what does not fit the queue
-            const int k = atomicAdd(&v.misc[2], 1);
-            if (k < MDR_SAT_QUEUE) {
-                v.sat_queue[k] = (uint16_t)pi;
-                return;
-            }
-#endif
+            // a whole warp takes the pair after this pass (phys_sat_warp.cuh)
+            v.pairs[pi] = pr | PAIR_SAT;
+            return;
+#else
             int r = hullHullContact(m, bodyXf(v, p, a), bodyXf(v, p, b), p);
             if (r == 1) { ref = a; alt = b; }
             else if (r == 2) { ref = b; alt = a; }
+#endif
         } else if (a_hull) {
             Plane plane;
             plane.n = rotate(ld4(v.rot, b), mk3(0.f, 0.f, 1.f));
@@ -574,7 +572,6 @@ MDR_HD void worldBoxes(const BlockCtx &c, WorldView &v, const StepParams &p, int
         const ObjDev *o = p.a.objs + (v.meta[i] & 0xffffu);
         stBox(v.box, i, applyTRS(objAABB(o), ld3(v.pos, i), ld4(v.rot, i), ld3(v.scale, i)));
     }
-    if (c.tid() == 0) v.misc[2] = 0;
 }
 
 }  // namespace mdr

@@ -1,6 +1,6 @@
 // Warp-cooperative hull-hull SAT (device only). The thread-per-pair narrowphase
-// queues the hull-hull pairs that pass the AABB reject; here one warp takes one
-// queued pair: lane k holds world vertex k and world face plane k of both hulls
+// marks the hull-hull pairs that pass the AABB reject; here one warp takes one
+// marked pair: lane k holds world vertex k and world face plane k of both hulls
 // (MDR_MAX_HULL_VERTS / FACES = 32), face queries run one face per lane, the
 // edge-edge query one edge pair per lane, and warp arg-max reductions pick the
 // same winner as the reference's sequential scans (first strict maximum =
@@ -220,14 +220,25 @@ __device__ __forceinline__ void hullHullWarp(WorldView &v, const StepParams &p, 
     if (lane == 0 && probing) probeContact(p, sub, pi, emit ? &m : nullptr, ref, alt);
 }
 
-// The queue: all warps of the world's thread group take queued pairs in turn.
+// The marked pairs of the world, in turn over the warps of its thread group.
+// Every warp walks the same marks (nobody writes the pair words in this phase)
+// and takes every nwarps-th one.
 __device__ __forceinline__ void satQueueWarp(const BlockCtx &c, WorldView &v, const StepParams &p,
                                              bool probing, int sub)
 {
-    int count = v.misc[2];
-    if (count > MDR_SAT_QUEUE) count = MDR_SAT_QUEUE;
+    const int np = v.misc[0];
     const int warp = c.tid() >> 5, nwarps = c.nthreads() >> 5, lane = c.tid() & 31;
-    for (int k = warp; k < count; k += nwarps) hullHullWarp(v, p, v.sat_queue[k], lane, probing, sub);
+    int turn = 0;
+    for (int base = 0; base < np; base += 32) {
+        const int i = base + lane;
+        uint32_t marks = __ballot_sync(MDR_FULL, i < np && (v.pairs[i] & PAIR_SAT));
+        while (marks) {
+            const int bit = __ffs(marks) - 1;
+            marks &= marks - 1;
+            if (turn == warp) hullHullWarp(v, p, base + bit, lane, probing, sub);
+            if (++turn == nwarps) turn = 0;
+        }
+    }
 }
 
 }  // namespace mdr

@@ -293,7 +293,7 @@ MDR_HD void solveLevels(const BlockCtx &c, WorldView &v, const StepParams &p, in
     const int np = v.misc[0];
     for (int lv = 1; lv <= max_level; lv++) {
         for (int i = c.tid(); i < np; i += c.nthreads()) {
-            if ((int)(v.pairs[i] >> 20) != lv) continue;
+            if (pairLevel(v.pairs[i]) != lv) continue;
             SolverContact *ct = contactSlot(v, i);
             if (ct->hdr == 0) continue;
             if (kVelocity) solveContactVelocities(v, p, ct);

@@ -39,7 +39,7 @@ __device__ __forceinline__ bool buildLevelLists(const BlockCtx &c, const WorldVi
     const int np = v.misc[0];
     for (int i = c.tid(); i < np; i += c.nthreads()) {
         if (contactSlot(v, i)->hdr == 0) continue;
-        const int lv = (int)(v.pairs[i] >> 20);
+        const int lv = pairLevel(v.pairs[i]);
         atomicAdd(&bs->cnt[lv <= kDenseLevels ? lv : 31], 1);
     }
     __syncthreads();
@@ -62,7 +62,7 @@ __device__ __forceinline__ bool buildLevelLists(const BlockCtx &c, const WorldVi
     if (!bs->dense) return false;
     for (int i = c.tid(); i < np; i += c.nthreads()) {
         if (contactSlot(v, i)->hdr == 0) continue;
-        const int lv = (int)(v.pairs[i] >> 20);
+        const int lv = pairLevel(v.pairs[i]);
         const int at = bs->off[lv] + atomicAdd(&bs->cnt[lv], 1);
         bs->items[at] = (uint16_t)((slot << 10) | i);
     }

@@ -122,8 +122,7 @@ enum { MDR_ERR_PAIR_OVERFLOW = 1 };
 #ifndef MDR_MAX_HULL_FACES
 #define MDR_MAX_HULL_FACES 32
 #endif
-#define MDR_SAT_QUEUE 64         // hull-hull pairs per world and substep handed to whole warps
 #define MDR_MAX_BODIES 1024      // rows are packed in 10 bits
-#define MDR_MAX_LEVEL 4095
+#define MDR_MAX_LEVEL 2047        // 11 bits of the pair word
 
 }  // namespace mdr

@@ -79,9 +79,8 @@ struct WorldView {
     float *pos, *rot, *vel, *prev, *prev_vel, *scale;
     uint32_t *meta;        // object id | META_*
     float *box;            // [np][6] leaf AABBs (broadphase) / world AABBs (narrowphase)
-    uint32_t *pairs;       // [max_pairs] row a | row b << 10 | level << 20
+    uint32_t *pairs;       // [max_pairs] row a | row b << 10 | level << 20 (11 bits) | PAIR_SAT
     int32_t *misc;         // [0] num pairs  [1] max level  [2] queued hull-hull pairs
-    uint16_t *sat_queue;   // [MDR_SAT_QUEUE] pair slots awaiting the warp-cooperative SAT
     // --- broadphase scratch, aliased with the contact slots ---
     float *slot;           // [np][6] grow-only slot boxes
     int32_t *ent_id;       // [np]
@@ -99,6 +98,11 @@ struct WorldView {
     SolverContact *overflow;   // this slot's global overflow contacts
     int smem_contacts;
 };
+
+// Pair word: the dependency level, and the per-substep mark "this hull-hull pair
+// passed the box test and waits for a whole warp" (phys_sat_warp.cuh).
+constexpr uint32_t PAIR_SAT = 1u << 31;
+MDR_HD int pairLevel(uint32_t word) { return (int)((word >> 20) & 0x7ffu); }
 
 MDR_HD size_t alignUp(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
@@ -122,7 +126,6 @@ MDR_HD size_t carveWorld(WorldView &v, char *base, int np, int max_pairs, int sm
     MDR_CARVE(box, float, 6 * np)
     MDR_CARVE(pairs, uint32_t, max_pairs)
     MDR_CARVE(misc, int32_t, 4)
-    MDR_CARVE(sat_queue, uint16_t, MDR_SAT_QUEUE)
     MDR_CARVE(row_perm, uint16_t, np)
     off = alignUp(off, 16);
     const size_t region = off;
