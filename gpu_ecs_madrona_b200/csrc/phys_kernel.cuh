@@ -1,0 +1,55 @@
+// The persistent step kernel (one block steps `slots` worlds side by side, worlds strided over
+// the grid) and the table of its compiled register budgets. Instantiated by phys_inst*.cu, a few
+// variants per translation unit so that the units build in parallel; physics.cu picks one.
+#pragma once
+#include <cuda_runtime.h>
+
+#include "phys_step.cuh"
+
+namespace mdr {
+
+extern __shared__ __align__(16) char mdr_smem[];
+
+template <int kMaxThreads, int kMinBlocks, bool kJoints>
+__global__ void __launch_bounds__(kMaxThreads, kMinBlocks)
+physStepKernel(const __grid_constant__ StepParams p, int threads_per_world, int slot_bytes,
+               int overflow_per_slot, int lockstep, int first_world, int end_world)
+{
+    __shared__ int group_level;
+    __shared__ BlockSolve block_solve;
+    const int slots = blockDim.x / threads_per_world;
+    const int slot = threadIdx.x / threads_per_world;
+    BlockCtx ctx;
+    ctx.tid_ = threadIdx.x - slot * threads_per_world;
+    ctx.nth_ = threads_per_world;
+    ctx.bar_ = lockstep ? 0 : slot + 1;
+    WorldView v;
+    carveWorld(v, mdr_smem + (size_t)slot * slot_bytes, p.t.stride, p.max_pairs, p.smem_contacts);
+    v.overflow = p.overflow + ((size_t)blockIdx.x * slots + slot) * overflow_per_slot;
+    // dense solver lanes need block-wide barriers, pair slots in 10 bits and a view per slot
+    BlockSolve *bs = lockstep && slots <= kDenseSlots && p.max_pairs <= 1024 ? &block_solve : nullptr;
+    if (bs && ctx.tid_ == 0) { v.n = 0; v.active = false; bs->views[slot] = v; }
+    __syncthreads();
+    // Every slot of the block walks the same barriers: the trip count depends on
+    // the block index only; a slot past the last world idles through them.
+    for (int base = first_world + blockIdx.x * slots; base < end_world; base += gridDim.x * slots) {
+        const int w = base + slot;
+        v.active = w < end_world;
+        stepWorld<kJoints>(ctx, v, p, v.active ? w : first_world, &group_level, bs, slot);
+    }
+}
+
+
+typedef void (*StepKernel)(const StepParams, int, int, int, int, int, int);
+// {max block threads, min resident blocks}; fn_joints is the same kernel with the joint
+// solve compiled in (mdr_phys_set_joints), so that batches without joints do not carry it.
+struct KernelVariant { int threads, min_blocks; StepKernel fn, fn_joints; };
+#define MDR_STEP_VARIANT(T, B) { T, B, mdr::physStepKernel<T, B, false>, mdr::physStepKernel<T, B, true> }
+
+}  // namespace mdr
+
+const mdr::KernelVariant *mdrStepVariants0(int *n);
+const mdr::KernelVariant *mdrStepVariants1(int *n);
+const mdr::KernelVariant *mdrStepVariants2(int *n);
+const mdr::KernelVariant *mdrStepVariants3(int *n);
+const mdr::KernelVariant *mdrStepVariants4(int *n);

@@ -177,6 +177,93 @@ MDR_HD void solveContactPositions(WorldView &v, const StepParams &p, SolverConta
     else solveContactPositionsT<false, false>(v, p, ct);
 }
 
+// ------------------------------------------------------------- joints -------
+// computeAngularUpdate + applyAngularUpdate (physics.cpp:247-279) behind the
+// part applyJointOrientationConstraint and applyJointAxisConstraint (:478-535)
+// share: normalise the error vector, take it to both body frames, rotate both.
+MDR_HD void jointAngularConstraint(Q4 &q1, Q4 &q2, V3 delta_q, V3 inv_I1, V3 inv_I2)
+{
+    const float theta = len(delta_q);
+    if (theta > 0) {
+        delta_q = delta_q / theta;
+        const V3 n1 = rotate(qinv(q1), delta_q), n2 = rotate(qinv(q2), delta_q);
+        const V3 ra1 = mulDiag(inv_I1, n1), ra2 = mulDiag(inv_I2, n2);
+        const float w1 = dot(n1, ra1), w2 = dot(n2, ra2);
+        const float half = 0.5f * (-theta / (w1 + w2 + 0.f));
+        const Q4 u1 = fromAngular(rotate(q1, half * ra1));
+        const Q4 u2 = fromAngular(rotate(q2, half * ra2));
+        q1 = qnormalize(q1 + u1 * q1);
+        q2 = qnormalize(q2 - u2 * q2);
+    }
+}
+
+// handleJointConstraint, physics.cpp:537-648. Static bodies take part with zero
+// inverse mass / inertia and are written back like the reference does (a stable
+// static's pose comes back bit for bit: +-0 added, a fixed point renormalised).
+#if defined(__CUDA_ARCH__)
+__device__ __noinline__
+#else
+inline
+#endif
+void solveJoint(WorldView &v, const StepParams &p, const JointDev *j)
+{
+    const int a = MDR_LDG(&j->row1), b = MDR_LDG(&j->row2);
+    V3 x1 = ld3(v.pos, a), x2 = ld3(v.pos, b);
+    Q4 q1 = ld4(v.rot, a), q2 = ld4(v.rot, b);
+    const BodyMass m1 = bodyMass(v, p, a), m2 = bodyMass(v, p, b);
+    const V3 r1 = mk3(MDR_LDG(&j->r1[0]), MDR_LDG(&j->r1[1]), MDR_LDG(&j->r1[2]));
+    const V3 r2 = mk3(MDR_LDG(&j->r2[0]), MDR_LDG(&j->r2[1]), MDR_LDG(&j->r2[2]));
+    float d[12];
+#pragma unroll
+    for (int k = 0; k < 12; k++) d[k] = MDR_LDG(&j->data[k]);
+    V3 corr;
+    if (MDR_LDG(&j->type) == 0) {
+        const Q4 at1 = mk4(d[0], d[1], d[2], d[3]), at2 = mk4(d[4], d[5], d[6], d[7]);
+        const Q4 o1 = qnormalize(q1 * at1), o2 = qnormalize(q2 * at2);
+        const Q4 diff = o1 * qinv(o2);
+        jointAngularConstraint(q1, q2, 2.f * mk3(diff.x, diff.y, diff.z), m1.inv_I, m2.inv_I);
+        const V3 delta_r = (rotate(q2, r2) + x2) - (rotate(q1, r1) + x1);
+        const Q4 axes = qnormalize(q1 * at1);
+        const V3 a1 = rotate(axes, mk3(0.f, 1.f, 0.f));      // math::fwd
+        const V3 b1 = rotate(axes, mk3(1.f, 0.f, 0.f));      // math::right
+        const V3 c1 = cross(a1, b1);
+        corr = mk3(0.f, 0.f, 0.f);
+        corr = corr - (dot(delta_r, a1) - d[8]) * a1;
+        corr = corr - dot(delta_r, b1) * b1;
+        corr = corr - dot(delta_r, c1) * c1;
+    } else {
+        const V3 ax1 = rotate(q1, mk3(d[0], d[1], d[2])), ax2 = rotate(q2, mk3(d[3], d[4], d[5]));
+        jointAngularConstraint(q1, q2, cross(ax1, ax2), m1.inv_I, m2.inv_I);
+        corr = (rotate(q2, r2) + x2) - (rotate(q1, r1) + x1);
+    }
+    const float mag = len(corr);
+    if (mag > 0.f) {
+        corr = corr / mag;
+        V3 ra1, ra2;
+        const float w1 = generalizedInvMass(m1, cross(r1, rotate(qinv(q1), corr)), ra1);
+        const float w2 = generalizedInvMass(m2, cross(r2, rotate(qinv(q2), corr)), ra2);
+        const float lambda = -mag / (w1 + w2 + 0.f);
+        applyPositionalSide<1>(x1, q1, ra1, m1.inv_m, corr, lambda);
+        applyPositionalSide<-1>(x2, q2, ra2, m2.inv_m, corr, lambda);
+    }
+    st3(v.pos, a, x1); st3(v.pos, b, x2);
+    st4(v.rot, a, q1); st4(v.rot, b, q2);
+}
+
+// The joints of one world, after the contacts of the substep, one after the other
+// in table order (solvePositions, physics.cpp:663-668). `joint_stride` is uniform
+// over the grid: a batch without joints pays one predictable branch.
+MDR_HD void solveJoints(const BlockCtx &c, WorldView &v, const StepParams &p, int w)
+{
+    if (p.joint_stride == 0) return;
+    if (c.tid() == 0 && v.active) {
+        const int nj = MDR_LDG(p.joint_count + w);
+        const JointDev *js = p.joints + (size_t)w * p.joint_stride;
+        for (int k = 0; k < nj; k++) solveJoint(v, p, js + k);
+    }
+    c.sync();
+}
+
 // solver::setVelocities, physics.cpp:673-714
 MDR_HD void setVelocities(const BlockCtx &c, WorldView &v, const StepParams &p, int sub)
 {

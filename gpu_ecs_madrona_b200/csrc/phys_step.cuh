@@ -92,6 +92,7 @@ __device__ __forceinline__ void solveDense(BlockSolve *bs, const StepParams &p, 
 // whole block: the level loops must run the same number of barriers in every
 // world slot, so they run to the block-wide maximum. A slot without a world
 // this round (`!v.active`) walks the same barriers with zero rows.
+template <bool kJoints = true>
 MDR_HD void stepWorld(const BlockCtx &c, WorldView &v, const StepParams &p, int w, int *group_level,
                       BlockSolve *bs = nullptr, int slot = 0)
 {
@@ -128,6 +129,7 @@ MDR_HD void stepWorld(const BlockCtx &c, WorldView &v, const StepParams &p, int 
 #if defined(__CUDA_ARCH__)
         if (bs && buildLevelLists(c, v, bs, slot, max_level)) {
             solveDense<false>(bs, p, max_level);
+            if (kJoints) solveJoints(c, v, p, w);
             setVelocities(c, v, p, sub);
             c.sync();
             solveDense<true>(bs, p, max_level);
@@ -135,6 +137,7 @@ MDR_HD void stepWorld(const BlockCtx &c, WorldView &v, const StepParams &p, int 
         }
 #endif
         solveLevels<false>(c, v, p, max_level);
+        if (kJoints) solveJoints(c, v, p, w);
         setVelocities(c, v, p, sub);
         c.sync();
         solveLevels<true>(c, v, p, max_level);

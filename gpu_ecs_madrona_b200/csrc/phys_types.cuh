@@ -96,6 +96,15 @@ struct ProbeDev {
                                   // (num_points 0 where the pair made no contact)
 };
 
+// mdr_joint (include/madrona_b200.h), the reference's JointConstraint with the
+// entities reduced to rows.
+struct JointDev {
+    int32_t type;                 // 0 Fixed, 1 Hinge
+    int32_t row1, row2;
+    float r1[3], r2[3];
+    float data[12];
+};
+
 struct StepParams {
     PhysTables t;
     AssetsDev a;
@@ -111,6 +120,9 @@ struct StepParams {
     int32_t *world_contacts;      // [W] contacts of the last substep
     int32_t *error_flags;         // [1] bit 0: pair list overflow
     ProbeDev probe;
+    const JointDev *joints;       // [W][joint_stride]; joint_stride 0: the batch has no joints
+    const int32_t *joint_count;   // [W]
+    int32_t joint_stride;
 };
 
 enum { MDR_ERR_PAIR_OVERFLOW = 1 };

@@ -9,7 +9,7 @@
 #include <cstring>
 #include <vector>
 
-#include "phys_step.cuh"
+#include "phys_kernel.cuh"
 #include "phys_lidar.cuh"
 #include "phys_feeder.cuh"
 #include "phys_assets.hpp"
@@ -28,37 +28,7 @@ using namespace mdr;
     } while (0)
 
 // ------------------------------------------------------------------ kernels --
-extern __shared__ __align__(16) char mdr_smem[];
-
-template <int kMaxThreads, int kMinBlocks>
-__global__ void __launch_bounds__(kMaxThreads, kMinBlocks)
-physStepKernel(const __grid_constant__ StepParams p, int threads_per_world, int slot_bytes,
-               int overflow_per_slot, int lockstep, int first_world, int end_world)
-{
-    __shared__ int group_level;
-    __shared__ BlockSolve block_solve;
-    const int slots = blockDim.x / threads_per_world;
-    const int slot = threadIdx.x / threads_per_world;
-    BlockCtx ctx;
-    ctx.tid_ = threadIdx.x - slot * threads_per_world;
-    ctx.nth_ = threads_per_world;
-    ctx.bar_ = lockstep ? 0 : slot + 1;
-    WorldView v;
-    carveWorld(v, mdr_smem + (size_t)slot * slot_bytes, p.t.stride, p.max_pairs, p.smem_contacts);
-    v.overflow = p.overflow + ((size_t)blockIdx.x * slots + slot) * overflow_per_slot;
-    // dense solver lanes need block-wide barriers, pair slots in 10 bits and a view per slot
-    BlockSolve *bs = lockstep && slots <= kDenseSlots && p.max_pairs <= 1024 ? &block_solve : nullptr;
-    if (bs && ctx.tid_ == 0) { v.n = 0; v.active = false; bs->views[slot] = v; }
-    __syncthreads();
-    // Every slot of the block walks the same barriers: the trip count depends on
-    // the block index only; a slot past the last world idles through them.
-    for (int base = first_world + blockIdx.x * slots; base < end_world; base += gridDim.x * slots) {
-        const int w = base + slot;
-        v.active = w < end_world;
-        stepWorld(ctx, v, p, v.active ? w : first_world, &group_level, bs, slot);
-    }
-}
-
+// physStepKernel lives in phys_kernel.cuh and is instantiated by phys_inst*.cu (parallel builds).
 // One thread per flagged world: current leaf boxes, then the reference's
 // top-down build reduced to traversal order + slot-box reset.
 __global__ void bvhRebuildKernel(const __grid_constant__ StepParams p)
@@ -79,21 +49,20 @@ __global__ void bvhRebuildKernel(const __grid_constant__ StepParams p)
 }
 
 // -------------------------------------------------------------- host state --
-typedef void (*StepKernel)(const StepParams, int, int, int, int, int, int);
-// Compiled register budgets: {max block threads, min resident blocks}.
-struct KernelVariant { int threads, min_blocks; StepKernel fn; };
-static const KernelVariant kVariants[] = {
-    { 64, 8, physStepKernel<64, 8> },        // 128 registers
-    { 128, 4, physStepKernel<128, 4> },      // 128
-    { 128, 6, physStepKernel<128, 6> },      // 80
-    { 256, 2, physStepKernel<256, 2> },      // 128
-    { 256, 3, physStepKernel<256, 3> },      // 80
-    { 384, 1, physStepKernel<384, 1> },      // 168
-    { 384, 2, physStepKernel<384, 2> },      // 80
-    { 512, 1, physStepKernel<512, 1> },      // 128
-    { 640, 1, physStepKernel<640, 1> },      // 96
-    { 1024, 1, physStepKernel<1024, 1> },    // 64
-};
+// Compiled register budgets, gathered from the instantiation units (ascending threads, then blocks).
+static std::vector<KernelVariant> gatherVariants()
+{
+    std::vector<KernelVariant> all;
+    const KernelVariant *(*parts[])(int *) = { mdrStepVariants0, mdrStepVariants1, mdrStepVariants2,
+                                                mdrStepVariants3, mdrStepVariants4 };
+    for (auto part : parts) {
+        int n = 0;
+        const KernelVariant *v = part(&n);
+        all.insert(all.end(), v, v + n);
+    }
+    return all;
+}
+static const std::vector<KernelVariant> kVariants = gatherVariants();
 
 struct mdr_phys {
     mdr_phys_config cfg;
@@ -112,7 +81,8 @@ struct mdr_phys {
     int pending_launches = 0;
     double timed_ms = 0.0;
     int timed_launches = 0;
-    StepKernel kernel = nullptr;
+    StepKernel kernel = nullptr;             // the variant in use: kernel_plain, or kernel_joints once joints are set
+    StepKernel kernel_plain = nullptr, kernel_joints = nullptr;
     int threads = 0, blocks = 0, blocks_per_sm = 0, overflow_per_slot = 0;
     int threads_per_world = 0, worlds_per_block = 0, lockstep = 1;
     size_t smem_bytes = 0, slot_bytes = 0;
@@ -120,6 +90,8 @@ struct mdr_phys {
     int32_t *d_err = nullptr;
     ProbeDev d_probe;   // device buffers of the probe
     int probe_pairs_cap = 0;
+    JointDev *d_joints = nullptr;       // mdr_phys_set_joints
+    int32_t *d_joint_count = nullptr;
 
     template <typename T> T *dalloc(size_t n, bool zero = true)
     {
@@ -285,9 +257,12 @@ int32_t mdr_phys_create(const mdr_phys_config *cfg, const mdr_object *objs, int3
         if (want_min_blocks ? kv.min_blocks == want_min_blocks : kv.min_blocks <= fit) var = &kv;
     }
     if (!var) { mdr_phys_destroy(p); return MDR_EINVAL; }
-    p->kernel = var->fn;
-    REQ_CUDA(cudaFuncSetAttribute(p->kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p->smem_bytes));
-    REQ_CUDA(cudaFuncSetAttribute(p->kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
+    p->kernel = p->kernel_plain = var->fn;
+    p->kernel_joints = var->fn_joints;
+    for (StepKernel k : { p->kernel_plain, p->kernel_joints }) {
+        REQ_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p->smem_bytes));
+        REQ_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
+    }
     int per_sm = 0;
     REQ_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, p->kernel, p->threads, p->smem_bytes));
     if (per_sm < 1) per_sm = 1;
@@ -313,6 +288,8 @@ void mdr_phys_destroy(mdr_phys *p)
     cudaSetDevice(p->cfg.gpu_id);
     if (p->stream) { cudaStreamSynchronize(p->stream); cudaStreamDestroy(p->stream); }
     if (p->ray_buf) cudaFree(p->ray_buf);
+    if (p->d_joints) cudaFree(p->d_joints);
+    if (p->d_joint_count) cudaFree(p->d_joint_count);
     if (p->io_in) { cudaStreamSynchronize(p->io_in); cudaStreamDestroy(p->io_in); }
     if (p->io_out) { cudaStreamSynchronize(p->io_out); cudaStreamDestroy(p->io_out); }
     for (cudaEvent_t e : p->io_events) cudaEventDestroy(e);
@@ -343,6 +320,40 @@ int32_t mdr_phys_set_row_counts(mdr_phys *p, const int32_t *rows)
     REQ_CUDA(cudaMemcpy(t.entity, ent.data(), ent.size() * 4, cudaMemcpyHostToDevice));
     REQ_CUDA(cudaMemcpy(t.leaf_id, leaf.data(), leaf.size() * 4, cudaMemcpyHostToDevice));
     return mdr_phys_flag_rebuild(p);
+}
+
+static_assert(sizeof(JointDev) == sizeof(mdr_joint), "JointDev mirrors mdr_joint");
+
+int32_t mdr_phys_set_joints(mdr_phys *p, int32_t max_joints, const int32_t *counts, const mdr_joint *joints)
+{
+    if (!p || max_joints < 0 || (max_joints > 0 && (!counts || !joints))) return MDR_EINVAL;
+    const int W = p->params.t.num_worlds;
+    for (int w = 0; w < W && max_joints > 0; w++) {
+        if (counts[w] < 0 || counts[w] > max_joints) return MDR_EINVAL;
+        for (int k = 0; k < counts[w]; k++) {
+            const mdr_joint &j = joints[(size_t)w * max_joints + k];
+            if (j.type < 0 || j.type > 1 || j.row1 < 0 || j.row2 < 0 ||
+                j.row1 >= p->cfg.max_bodies_per_world || j.row2 >= p->cfg.max_bodies_per_world)
+                return MDR_EINVAL;
+        }
+    }
+    REQ_CUDA(cudaSetDevice(p->cfg.gpu_id));
+    REQ_CUDA(cudaStreamSynchronize(p->stream));
+    if (p->d_joints) { REQ_CUDA(cudaFree(p->d_joints)); p->d_joints = nullptr; }
+    if (p->d_joint_count) { REQ_CUDA(cudaFree(p->d_joint_count)); p->d_joint_count = nullptr; }
+    if (max_joints > 0) {
+        const size_t nj = (size_t)W * max_joints;
+        REQ_CUDA(cudaMalloc((void **)&p->d_joints, nj * sizeof(JointDev)));
+        REQ_CUDA(cudaMalloc((void **)&p->d_joint_count, (size_t)W * 4));
+        REQ_CUDA(cudaMemcpy(p->d_joints, joints, nj * sizeof(JointDev), cudaMemcpyHostToDevice));
+        REQ_CUDA(cudaMemcpy(p->d_joint_count, counts, (size_t)W * 4, cudaMemcpyHostToDevice));
+    }
+    p->params.joints = p->d_joints;
+    p->params.joint_count = p->d_joint_count;
+    p->params.joint_stride = max_joints;
+    // Same launch bounds, hence the same residency: only the code path differs.
+    p->kernel = max_joints > 0 ? p->kernel_joints : p->kernel_plain;
+    return MDR_OK;
 }
 
 int32_t mdr_phys_write_column(mdr_phys *p, int32_t col, const void *src)

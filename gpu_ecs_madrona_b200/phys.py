@@ -67,6 +67,7 @@ def bind(lib):
     lib.mdr_phys_write_column.argtypes = [vp, i32, vp]
     lib.mdr_phys_read_column.argtypes = [vp, i32, vp]
     lib.mdr_phys_flag_rebuild.argtypes = [vp]
+    lib.mdr_phys_set_joints.argtypes = [vp, i32, vp, vp]
     lib.mdr_phys_step.argtypes = [vp, i32]
     lib.mdr_phys_step_async.argtypes = [vp, i32]
     lib.mdr_phys_sync.argtypes = [vp]
@@ -169,6 +170,24 @@ class PhysExecutor:
                              (COL_EXT_FORCE, scene.ext_force, np.float32),
                              (COL_EXT_TORQUE, scene.ext_torque, np.float32)):
             self.write(col, np.ascontiguousarray(arr, dt))
+        if getattr(scene, "joints", None) is not None:
+            self.set_joints(scene.joints, scene.joint_counts)
+
+    def set_joints(self, joints, counts=None):
+        """Replaces the joint constraints: ``joints`` [W, J] of ``scenes.JOINT_DTYPE`` (the
+        ConstraintData rows of each world, solved in this order after the contacts of every
+        substep), ``counts`` [W] live joints per world (default: all J). ``None`` removes them."""
+        if joints is None:
+            self._check(self.lib.mdr_phys_set_joints(self.h, 0, None, None), "set_joints")
+            return
+        from .scenes import JOINT_DTYPE
+        joints = np.ascontiguousarray(joints, JOINT_DTYPE)
+        assert joints.ndim == 2 and joints.shape[0] == self.W
+        if counts is None:
+            counts = np.full(self.W, joints.shape[1], np.int32)
+        counts = np.ascontiguousarray(counts, np.int32)
+        self._check(self.lib.mdr_phys_set_joints(self.h, joints.shape[1], counts.ctypes.data,
+                                                 joints.ctypes.data), "set_joints")
 
     def _check(self, rc, what):
         if rc != MDR_OK:

@@ -30,6 +30,14 @@ CUBE_POLYS = [
 ]
 
 
+# JointConstraint (include/madrona/physics.hpp:196-238) with the entities as rows:
+# the layout of mdr_joint (include/madrona_b200.h).
+JOINT_FIXED, JOINT_HINGE = 0, 1
+JOINT_DTYPE = np.dtype([("type", "<i4"), ("row1", "<i4"), ("row2", "<i4"),
+                        ("r1", "<f4", (3,)), ("r2", "<f4", (3,)), ("data", "<f4", (12,))])
+assert JOINT_DTYPE.itemsize == 84
+
+
 @dataclass
 class ObjectDef:
     """One shared collision object (reference: ObjectManager row,
@@ -98,6 +106,8 @@ class Scene:
     ext_force: np.ndarray  # [W, N, 3] f32
     ext_torque: np.ndarray # [W, N, 3] f32
     name: str = ""
+    joints: np.ndarray = None        # [W, J] JOINT_DTYPE (ConstraintData rows), optional
+    joint_counts: np.ndarray = None  # [W] i32
 
 
 def _lcg_uniform(seeds, count):
@@ -186,3 +196,109 @@ def tumble(num_worlds, num_bodies=24, seed=1, num_substeps=4, max_contacts=512,
     return Scene(W, N, num_substeps, max_contacts, 1.0 / 60.0, (0.0, 0.0, -9.8),
                  [cube_object(), box_object(0.5, 0.3, 0.2, inv_mass=2.0, mu=0.3), plane_object()],
                  pos, rot, scale, vel, obj_ids, response, f, t, name=f"tumble-{num_bodies}")
+
+
+def jointed(num_worlds, seed=7, num_substeps=4, max_contacts=256, loose=6, hinges=False):
+    """Joint constraints (SURVEY 8f rank 3; JointConstraint::setupFixed / setupHinge,
+    include/madrona/physics.inl:151-191) next to contacts. Per world, over a static plane:
+      * a pendulum: a static anchor cube in the air and three cubes hanging below it,
+        linked by hinges about a common axis (static-dynamic and dynamic-dynamic joints);
+      * a rigid dumbbell: two boxes held apart by a fixed joint with rotated attach
+        frames and a non-zero separation, dropped so that it lands on the plane;
+      * a hinged pair lying on the plane from the start (joints and contacts on the
+        same bodies in the same substep);
+      * `loose` free cubes thrown at the rest.
+    Worlds differ by LCG jitter of poses, velocities and joint frames; every second
+    world leaves its last joint out (ragged joint counts). Parity-test scene only.
+
+    `hinges=False` swaps every hinge for a fixed joint with the same anchors. In this
+    snapshot of the reference the hinge pushes its bodies AWAY from the constraint
+    (handleJointConstraint hands applyPositionalUpdate `r2 - r1`, physics.cpp:617, where the
+    fixed joint hands it the negated error, :594-605; applyJointAxisConstraint has the same
+    sign and a debug printf, :521-535), so hinged bodies leave to infinity within ~10
+    steps: hinge parity is checked bit for bit on the first steps, while the state is finite."""
+    W = num_worlds
+    nb = 4 + 2 + 2 + loose
+    N = 1 + nb
+    seeds = (np.arange(W, dtype=np.uint64) * np.uint64(2891336453) + np.uint64(seed)) & np.uint64(0xFFFFFFFF)
+    u = _lcg_uniform(seeds, 16 * nb + 32).reshape(W, -1)
+    ub, uj = u[:, :16 * nb].reshape(W, nb, 16), u[:, 16 * nb:]
+    pos = np.zeros((W, N, 3))
+    rot = np.zeros((W, N, 4))
+    rot[..., 0] = 1.0
+    scale = np.ones((W, N, 3), np.float32)
+    vel = np.zeros((W, N, 6))
+    obj_ids = np.zeros((W, N), np.int32)
+    response = np.zeros((W, N), np.uint32)
+    obj_ids[:, 0] = 2
+    response[:, 0] = STATIC
+    jit = (ub[..., 0:3] * 2 - 1)
+    # pendulum: rows 1 (static anchor) .. 4
+    for k in range(4):
+        pos[:, 1 + k] = np.array([-3.0, 0.0, 6.0 - 1.2 * k]) + (0.05 * jit[:, k] if k else 0.0)
+        vel[:, 1 + k, 0] = 1.5 * k * (ub[:, k, 3] * 2 - 1)
+        vel[:, 1 + k, 1] = 0.5 * k * (ub[:, k, 4] * 2 - 1)
+    response[:, 1] = STATIC
+    # dumbbell: rows 5, 6 (boxes, object 1)
+    obj_ids[:, 5:7] = 1
+    pos[:, 5] = np.array([0.0, -0.6, 1.2]) + 0.05 * jit[:, 4]
+    pos[:, 6] = np.array([0.0, 0.6, 1.3]) + 0.05 * jit[:, 5]
+    vel[:, 5:7, 3:6] = (ub[:, 4:6, 5:8] * 2 - 1) * 2.0
+    # hinged pair on the ground: rows 7, 8
+    pos[:, 7] = np.array([3.0, -0.55, 0.5]) + 0.02 * jit[:, 6] * np.array([1, 1, 0])
+    pos[:, 8] = np.array([3.0, 0.55, 0.5]) + 0.02 * jit[:, 7] * np.array([1, 1, 0])
+    vel[:, 8, 0] = 1.0
+    # loose cubes
+    for k in range(loose):
+        b = 8 + k
+        pos[:, 1 + b] = np.array([-3.0 + 1.5 * k, -2.0, 2.0 + 0.7 * (k % 3)]) + 0.3 * jit[:, b]
+        q = ub[:, b, 8:12] * 2 - 1
+        rot[:, 1 + b] = q / np.linalg.norm(q, axis=-1, keepdims=True)
+        vel[:, 1 + b, 0:3] = np.array([0.0, 3.0, 0.0]) + (ub[:, b, 12:15] * 2 - 1)
+    J = 6
+    joints = np.zeros((W, J), JOINT_DTYPE)
+    counts = np.full(W, J, np.int32)
+    counts[1::2] = J - 1
+    axis = np.array([0.0, 1.0, 0.0])
+    for k in range(3):                      # anchor-1, 1-2, 2-3
+        j = joints[:, k]
+        j["type"], j["row1"], j["row2"] = JOINT_HINGE, 1 + k, 2 + k
+        j["r1"], j["r2"] = (0.0, 0.0, -0.6), (0.0, 0.0, 0.6)
+        a2 = axis[None] + 0.05 * (uj[:, 3 * k:3 * k + 3] * 2 - 1)
+        a2 /= np.linalg.norm(a2, axis=-1, keepdims=True)
+        j["data"][:, 0:3] = axis
+        j["data"][:, 3:6] = a2
+        j["data"][:, 6:9] = (1.0, 0.0, 0.0)
+        j["data"][:, 9:12] = (1.0, 0.0, 0.0)
+    j = joints[:, 3]                        # dumbbell
+    j["type"], j["row1"], j["row2"] = JOINT_FIXED, 5, 6
+    j["r1"], j["r2"] = (0.0, 0.3, 0.0), (0.0, -0.3, 0.0)
+    q1 = np.array([1.0, 0.0, 0.0, 0.0])[None] + 0.2 * (uj[:, 9:13] * 2 - 1)
+    q1 /= np.linalg.norm(q1, axis=-1, keepdims=True)
+    q2 = np.array([1.0, 0.0, 0.0, 0.0])[None] + 0.2 * (uj[:, 13:17] * 2 - 1)
+    q2 /= np.linalg.norm(q2, axis=-1, keepdims=True)
+    j["data"][:, 0:4], j["data"][:, 4:8] = q1, q2
+    j["data"][:, 8] = 0.5 + 0.2 * uj[:, 17]
+    j = joints[:, 4]                        # ground pair
+    j["type"], j["row1"], j["row2"] = JOINT_HINGE, 7, 8
+    j["r1"], j["r2"] = (0.0, 0.55, 0.0), (0.0, -0.55, 0.0)
+    j["data"][:, 0:3], j["data"][:, 3:6] = (0.0, 0.0, 1.0), (0.0, 0.0, 1.0)
+    j = joints[:, 5]                        # a loose cube tied to the pendulum's tip (odd worlds: absent)
+    j["type"], j["row1"], j["row2"] = JOINT_FIXED, 4, 9
+    j["r1"], j["r2"] = (0.5, 0.0, 0.0), (-0.5, 0.0, 0.0)
+    j["data"][:, 0], j["data"][:, 4] = 1.0, 1.0
+    j["data"][:, 8] = 0.0
+    if not hinges:
+        for k in (0, 1, 2, 4):
+            j = joints[:, k]
+            j["type"] = JOINT_FIXED
+            j["data"] = 0.0
+            j["data"][:, 0], j["data"][:, 4] = 1.0, 1.0
+    for w in np.nonzero(counts < J)[0]:
+        joints[w, counts[w]:] = np.zeros((), JOINT_DTYPE)
+    z = np.zeros((W, N, 3), np.float32)
+    return Scene(W, N, num_substeps, max_contacts, 1.0 / 60.0, (0.0, 0.0, -9.8),
+                 [cube_object(), box_object(0.5, 0.3, 0.2, inv_mass=2.0, mu=0.3), plane_object()],
+                 pos.astype(np.float32), rot.astype(np.float32), scale, vel.astype(np.float32),
+                 obj_ids, response, z, z.copy(), name="jointed-hinges" if hinges else "jointed",
+                 joints=joints, joint_counts=counts)

@@ -130,6 +130,27 @@ int32_t mdr_phys_column_bytes(int32_t col);
  * include/madrona/physics.inl:109-112): rebuild on the next step. */
 int32_t mdr_phys_flag_rebuild(mdr_phys *p);
 
+/* Joint constraints: the ConstraintData archetype (one JointConstraint per
+ * entity, include/madrona/physics.hpp:196-240), collected every substep by
+ * collectConstraintsSystem (src/physics/physics.cpp:34-40,1160-1161) and solved
+ * after the substep's contacts by solvePositions -> handleJointConstraint
+ * (:537-648,663-670), in table row order. The two entities are given as rows of
+ * the joint's world. type 0 = Fixed (JointConstraint::setupFixed,
+ * include/madrona/physics.inl:151-169): data = attachRot1 w,x,y,z, attachRot2
+ * w,x,y,z, separation. type 1 = Hinge (setupHinge, :171-191): data = a1Local,
+ * a2Local, b1Local, b2Local. 84 bytes. */
+typedef struct mdr_joint {
+    int32_t type;
+    int32_t row1, row2;
+    float r1[3], r2[3];
+    float data[12];
+} mdr_joint;
+/* Replaces the joint table: joints_per_world[w] joints for world w taken from
+ * joints[w][0 .. max_joints_per_world). max_joints_per_world 0 removes them all.
+ * MDR_EINVAL for a row outside the world's row capacity or an unknown type. */
+int32_t mdr_phys_set_joints(mdr_phys *p, int32_t max_joints_per_world, const int32_t *joints_per_world,
+                            const mdr_joint *joints);
+
 /* MWCudaExecutor::run() (src/mw/cuda_exec.cpp:1777-1794), `num_steps` times.
  * mdr_phys_step blocks like run(); the _async form only enqueues on the
  * executor's stream (mdr_phys_sync waits). Returns MDR_EOVERFLOW after the

@@ -132,6 +132,26 @@ void orc_trace_rays(void *h, int32_t world, int32_t n, const float *origins, con
  * y_scale} of the body in view_rows[w][v] (interop.cpp:69-79). */
 void orc_feeder(void *h, const float *world_offset, float *out_transforms, int32_t views_per_world,
                 const int32_t *view_rows, const float *camera_offset, const float *y_scale, float *out_views);
+/* One joint constraint of one world (reference: JointConstraint,
+ * include/madrona/physics.hpp:196-238, with the two entities reduced to rows of
+ * the rigid-body table). type 0 = Fixed: data = attachRot1 (w,x,y,z),
+ * attachRot2 (w,x,y,z), separation; type 1 = Hinge: data = a1Local, a2Local,
+ * b1Local, b2Local (3 floats each). */
+typedef struct {
+    int32_t type;
+    int32_t row1, row2;
+    float r1[3], r2[3];
+    float data[12];
+} orc_joint;
+/* Creates joints_per_world[w] ConstraintData entities in world w from
+ * joints[w][0..], in that order (= the order collectConstraintsSystem,
+ * src/physics/physics.cpp:34-40, appends them and solvePositions :663-668
+ * solves them in, after the contacts of the substep). Call once, before stepping.
+ * The compiled reference prints from applyJointAxisConstraint (:529-531, a
+ * debug printf left in the snapshot): the harness points stdout at /dev/null
+ * while it steps worlds that hold hinges. */
+void orc_set_joints(void *h, int32_t max_joints_per_world, const int32_t *joints_per_world,
+                    const orc_joint *joints /*[W][max_joints_per_world]*/);
 const char *orc_kind(void);
 
 #ifdef __cplusplus

@@ -103,6 +103,7 @@ class Oracle:
         L.orc_indeterminate.argtypes = [C.c_void_p, C.c_void_p]
         L.orc_trace_rays.argtypes = [C.c_void_p, C.c_int32, C.c_int32] + [C.c_void_p] * 6
         L.orc_feeder.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32] + [C.c_void_p] * 4
+        L.orc_set_joints.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p]
         L.orc_kind.restype = C.c_char_p
         self.kind = L.orc_kind().decode()
         self.scene = scene
@@ -117,6 +118,11 @@ class Oracle:
         self.h = L.orc_create(C.byref(cfg), objs, len(scene.objects),
                               verts.ctypes.data, words.ctypes.data,
                               *[a.ctypes.data for a in self._keep])
+        if getattr(scene, "joints", None) is not None:
+            j = c(scene.joints)
+            assert j.dtype.itemsize == 84 and j.shape[0] == scene.num_worlds
+            n = c(scene.joint_counts, np.int32)
+            L.orc_set_joints(self.h, j.shape[1], n.ctypes.data, j.ctypes.data)
 
     def close(self):
         if self.h:

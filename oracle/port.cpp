@@ -249,6 +249,7 @@ struct World {
 
     std::vector<std::pair<int32_t, int32_t>> candidates;
     std::vector<Contact> contacts;
+    std::vector<orc_joint> joints;     // ConstraintData rows, creation order
     int64_t indeterminate = 0;
 };
 
@@ -554,6 +555,8 @@ inline void localContacts(V3 pre_x1, Q4 pre_q1, V3 pre_x2, Q4 pre_q2,
     r2 = rotate(qinv(pre_q2), c2 - pre_x2);
 }
 
+void handleJoint(const Sim &s, World &w, const orc_joint &j);
+
 // handleContact + handleContactConstraint, physics.cpp:281-363,387-476
 void solvePositions(const Sim &s, World &w)
 {
@@ -606,6 +609,79 @@ void solvePositions(const Sim &s, World &w)
         w.pos[a] = x1; w.pos[b] = x2;
         w.rot[a] = q1; w.rot[b] = q2;
     }
+    // joints after the contacts, in collection (= table row) order, physics.cpp:663-668
+    for (const orc_joint &j : w.joints) handleJoint(s, w, j);
+}
+
+// computeAngularUpdate + applyAngularUpdate, physics.cpp:247-279 (alpha_tilde = 0)
+inline void angularUpdate(Q4 &q1, Q4 &q2, V3 inv_I1, V3 inv_I2, V3 n1, V3 n2, float theta)
+{
+    V3 ra1 = mulDiag(inv_I1, n1), ra2 = mulDiag(inv_I2, n2);
+    float w1 = dot(n1, ra1), w2 = dot(n2, ra2);
+    float dl = -theta / (w1 + w2 + 0.f);
+    float half = 0.5f * dl;
+    Q4 u1 = fromAngular(rotate(q1, half * ra1));
+    Q4 u2 = fromAngular(rotate(q2, half * ra2));
+    q1 = qnormalize(q1 + u1 * q1);
+    q2 = qnormalize(q2 - u2 * q2);
+}
+
+// applyJointOrientationConstraint / applyJointAxisConstraint (physics.cpp:478-535)
+// share everything after the error vector delta_q.
+inline void angularConstraint(Q4 &q1, Q4 &q2, V3 delta_q, V3 inv_I1, V3 inv_I2)
+{
+    float mag = len(delta_q);
+    if (mag > 0) {
+        delta_q = delta_q / mag;
+        V3 l1 = rotate(qinv(q1), delta_q), l2 = rotate(qinv(q2), delta_q);
+        angularUpdate(q1, q2, inv_I1, inv_I2, l1, l2, mag);
+    }
+}
+
+// handleJointConstraint, physics.cpp:537-648
+void handleJoint(const Sim &s, World &w, const orc_joint &j)
+{
+    int a = j.row1, b = j.row2;
+    V3 x1 = w.pos[a], x2 = w.pos[b];
+    Q4 q1 = w.rot[a], q2 = w.rot[b];
+    const Object &o1 = s.objs[w.obj[a]], &o2 = s.objs[w.obj[b]];
+    float inv_m1 = o1.inv_mass, inv_m2 = o2.inv_mass;
+    V3 inv_I1 = o1.inv_inertia, inv_I2 = o2.inv_inertia;
+    if (w.response[a] == 2) { inv_m1 = 0.f; inv_I1 = { 0, 0, 0 }; }
+    if (w.response[b] == 2) { inv_m2 = 0.f; inv_I2 = { 0, 0, 0 }; }
+    V3 r1 { j.r1[0], j.r1[1], j.r1[2] }, r2 { j.r2[0], j.r2[1], j.r2[2] };
+    const float *d = j.data;
+    V3 corr;
+    if (j.type == 0) {
+        Q4 at1 { d[0], d[1], d[2], d[3] }, at2 { d[4], d[5], d[6], d[7] };
+        float separation = d[8];
+        Q4 o1q = qnormalize(q1 * at1), o2q = qnormalize(q2 * at2);
+        Q4 diff = o1q * qinv(o2q);
+        angularConstraint(q1, q2, 2.f * V3 { diff.x, diff.y, diff.z }, inv_I1, inv_I2);
+        V3 r1w = rotate(q1, r1) + x1, r2w = rotate(q2, r2) + x2;
+        V3 delta_r = r2w - r1w;
+        Q4 axes = qnormalize(q1 * at1);
+        V3 a1 = rotate(axes, V3 { 0, 1, 0 });      // math::fwd
+        V3 b1 = rotate(axes, V3 { 1, 0, 0 });      // math::right
+        V3 c1 = cross(a1, b1);
+        corr = { 0, 0, 0 };
+        corr = corr - (dot(delta_r, a1) - separation) * a1;
+        corr = corr - dot(delta_r, b1) * b1;
+        corr = corr - dot(delta_r, c1) * c1;
+    } else {
+        V3 a1l { d[0], d[1], d[2] }, a2l { d[3], d[4], d[5] };
+        V3 ax1 = rotate(q1, a1l), ax2 = rotate(q2, a2l);
+        angularConstraint(q1, q2, cross(ax1, ax2), inv_I1, inv_I2);
+        V3 r1w = rotate(q1, r1) + x1, r2w = rotate(q2, r2) + x2;
+        corr = r2w - r1w;
+    }
+    float mag = len(corr);
+    if (mag > 0.f) {
+        corr = corr / mag;
+        applyPositionalFull(x1, x2, q1, q2, r1, r2, inv_m1, inv_m2, inv_I1, inv_I2, corr, mag, 0);
+    }
+    w.pos[a] = x1; w.pos[b] = x2;
+    w.rot[a] = q1; w.rot[b] = q2;
 }
 
 // solver::setVelocities, physics.cpp:673-714
@@ -1192,6 +1268,15 @@ void orc_destroy(void *h) { delete (Sim *)h; }
 void orc_flag_rebuild(void *h)
 {
     for (World &w : ((Sim *)h)->worlds) w.force_rebuild = true;
+}
+
+void orc_set_joints(void *h, int32_t max_joints, const int32_t *counts, const orc_joint *joints)
+{
+    Sim *s = (Sim *)h;
+    for (size_t wi = 0; wi < s->worlds.size(); wi++) {
+        const orc_joint *src = joints + wi * (size_t)max_joints;
+        s->worlds[wi].joints.assign(src, src + counts[wi]);
+    }
 }
 
 void orc_step(void *hp, int32_t num_steps, int32_t num_threads)

@@ -26,6 +26,8 @@
 #include <new>
 #include <string>
 #include <mutex>
+#include <fcntl.h>
+#include <unistd.h>
 
 // The harness reads intermediates (task-graph node list, BVH boxes) that the
 // reference keeps private: oracle/Makefile compiles with -fno-access-control.
@@ -78,6 +80,7 @@ struct World {
     Engine *ctx;
     TaskGraph *graph;
     std::vector<Entity> bodies;
+    bool has_hinge = false;
 };
 
 struct Handle {
@@ -167,7 +170,7 @@ void *orc_create(const orc_config *cfg,
         RigidBodyPhysicsSystem::init(*w.ctx, &so.mgr, cfg->delta_t,
             cfg->num_substeps,
             Vector3 { cfg->gravity[0], cfg->gravity[1], cfg->gravity[2] },
-            N, cfg->max_contacts, 16);
+            N, cfg->max_contacts, 64);
 
         w.bodies.resize(N);
         for (int i = 0; i < N; i++) {
@@ -213,10 +216,60 @@ void orc_flag_rebuild(void *hp)
     }
 }
 
+// applyJointAxisConstraint (src/physics/physics.cpp:529-531) prints both axes of
+// every hinge in every substep: stdout goes to /dev/null while such worlds step.
+struct QuietStdout {
+    int saved = -1;
+    explicit QuietStdout(bool on)
+    {
+        if (!on) return;
+        fflush(stdout);
+        saved = dup(1);
+        int nul = open("/dev/null", O_WRONLY);
+        dup2(nul, 1);
+        close(nul);
+    }
+    ~QuietStdout()
+    {
+        if (saved < 0) return;
+        fflush(stdout);
+        dup2(saved, 1);
+        close(saved);
+    }
+};
+
+static bool anyHinge(Handle *h)
+{
+    for (World &w : h->worlds) if (w.has_hinge) return true;
+    return false;
+}
+
+void orc_set_joints(void *hp, int32_t max_joints, const int32_t *counts, const orc_joint *joints)
+{
+    Handle *h = (Handle *)hp;
+    for (size_t wi = 0; wi < h->worlds.size(); wi++) {
+        World &w = h->worlds[wi];
+        for (int k = 0; k < counts[wi]; k++) {
+            const orc_joint &j = joints[wi * (size_t)max_joints + k];
+            const float *d = j.data;
+            Vector3 r1 { j.r1[0], j.r1[1], j.r1[2] }, r2 { j.r2[0], j.r2[1], j.r2[2] };
+            JointConstraint jc = j.type == 0 ?
+                JointConstraint::setupFixed(w.bodies[j.row1], w.bodies[j.row2],
+                    Quat { d[0], d[1], d[2], d[3] }, Quat { d[4], d[5], d[6], d[7] }, r1, r2, d[8]) :
+                JointConstraint::setupHinge(w.bodies[j.row1], w.bodies[j.row2],
+                    Vector3 { d[0], d[1], d[2] }, Vector3 { d[3], d[4], d[5] },
+                    Vector3 { d[6], d[7], d[8] }, Vector3 { d[9], d[10], d[11] }, r1, r2);
+            w.ctx->makeEntityNow<ConstraintData>(jc);
+            if (j.type != 0) w.has_hinge = true;
+        }
+    }
+}
+
 void orc_step(void *hp, int32_t num_steps, int32_t num_threads)
 {
     Handle *h = (Handle *)hp;
     const int W = (int)h->worlds.size();
+    QuietStdout quiet(anyHinge(h));
     if (num_threads <= 1) {
         for (int s = 0; s < num_steps; s++)
             for (int i = 0; i < W; i++)
@@ -292,6 +345,7 @@ int32_t orc_probe_step(void *hp, int32_t world, orc_probe *out)
     const int S = h->cfg.num_substeps;
     TaskGraph &tg = *w.graph;
     int32_t rc = 0;
+    QuietStdout quiet(w.has_hinge);
 
     // Node layout (src/physics/physics.cpp:1142-1205, broadphase.cpp:934-991,
     // narrowphase.cpp:1768-1782): 0 updateLeaf, 1 updateBVH, 2 refit,

@@ -117,6 +117,31 @@ int32_t mdr_phys_set_row_counts(mdr_phys *p, const int32_t *rows)
     return MDR_OK;
 }
 
+int32_t mdr_phys_set_joints(mdr_phys *p, int32_t max_joints, const int32_t *counts, const mdr_joint *joints)
+{
+    if (!p || max_joints < 0 || (max_joints > 0 && (!counts || !joints))) return MDR_EINVAL;
+    const int W = p->cfg.num_worlds;
+    for (int w = 0; w < W && max_joints > 0; w++) {
+        if (counts[w] < 0 || counts[w] > max_joints) return MDR_EINVAL;
+        for (int k = 0; k < counts[w]; k++) {
+            const mdr_joint &j = joints[(size_t)w * max_joints + k];
+            if (j.type < 0 || j.type > 1 || j.row1 < 0 || j.row2 < 0 ||
+                j.row1 >= p->cfg.max_bodies_per_world || j.row2 >= p->cfg.max_bodies_per_world)
+                return MDR_EINVAL;
+        }
+    }
+    JointDev *dj = p->alloc<JointDev>((size_t)W * max_joints);
+    int32_t *dc = p->alloc<int32_t>(W);
+    if (max_joints > 0) {
+        memcpy(dj, joints, (size_t)W * max_joints * sizeof(JointDev));
+        memcpy(dc, counts, (size_t)W * 4);
+    }
+    p->params.joints = dj;
+    p->params.joint_count = dc;
+    p->params.joint_stride = max_joints;
+    return MDR_OK;
+}
+
 int32_t mdr_phys_write_column(mdr_phys *p, int32_t col, const void *src)
 {
     void **s = colSlot(p->params.t, col);

@@ -22,6 +22,9 @@ CASES = {
     "tumble24": (scenes.tumble, dict(num_worlds=6, num_bodies=24), (1, 5, 30), 2),
     "tumble12_noplane": (scenes.tumble, dict(num_worlds=4, num_bodies=12, seed=7, spread=0.8,
                                              with_plane=False), (1, 8), 0),
+    # joint constraints (Fixed) beside contacts; hinges only while the reference keeps them finite
+    "jointed": (scenes.jointed, dict(num_worlds=6), (1, 10, 60), 3),
+    "jointed_hinges": (scenes.jointed, dict(num_worlds=4, hinges=True), (1, 4, 7), 1),
 }
 
 

@@ -15,6 +15,7 @@ SCENES = {
     "tumble24": lambda: scenes.tumble(8),
     "tumble40": lambda: scenes.tumble(4, num_bodies=40, spread=1.0, seed=3),
     "tumble12_noplane": lambda: scenes.tumble(4, num_bodies=12, seed=7, spread=0.8, with_plane=False),
+    "jointed": lambda: scenes.jointed(6),
 }
 
 
@@ -29,6 +30,48 @@ def test_emu_matches_oracle(port_oracle, emu_lib, name):
         assert_state_equal(e.state(), o.state(), None, f"{name} step {st}")
     for col in (phys.COL_SUBSTEP_PREV, phys.COL_PRESOLVE_POS, phys.COL_PRESOLVE_VEL):
         assert np.array_equal(e.read(col), o.read(col)), col
+
+
+def test_emu_hinges_match_oracle(port_oracle, emu_lib):
+    """Hinge joints (physics.cpp:511-535,608-618), while the reference keeps the state finite
+    (see scenes.jointed); then joints replaced / removed through mdr_phys_set_joints."""
+    sc = scenes.jointed(5, hinges=True)
+    o = port_oracle.Oracle(sc, "port")
+    e = phys.PhysExecutor(sc, lib=emu_lib)
+    for st in range(8):
+        o.step()
+        e.run()
+        assert all(np.isfinite(a).all() for a in o.state())
+        assert_state_equal(e.state(), o.state(), None, f"hinges step {st}")
+    plain = scenes.jointed(5)
+    e2 = phys.PhysExecutor(sc, lib=emu_lib)
+    e2.set_joints(plain.joints, plain.joint_counts)     # swap the hinge table for the fixed one
+    o2 = port_oracle.Oracle(plain, "port")
+    e2.run(10)
+    o2.step(10)
+    assert_state_equal(e2.state(), o2.state(), None, "joint table replaced")
+    e3 = phys.PhysExecutor(plain, lib=emu_lib)
+    e3.set_joints(None)
+    plain.joints = plain.joint_counts = None
+    o3 = port_oracle.Oracle(plain, "port")
+    e3.run(10)
+    o3.step(10)
+    assert_state_equal(e3.state(), o3.state(), None, "joints removed")
+
+
+def test_emu_set_joints_rejects_bad_arguments(emu_lib):
+    sc = scenes.jointed(2)
+    e = phys.PhysExecutor(sc, lib=emu_lib)
+    bad = sc.joints.copy()
+    bad["row2"][1, 0] = sc.bodies_per_world
+    with pytest.raises(phys.MadronaError):
+        e.set_joints(bad, sc.joint_counts)
+    bad = sc.joints.copy()
+    bad["type"][0, 2] = 2
+    with pytest.raises(phys.MadronaError):
+        e.set_joints(bad, sc.joint_counts)
+    with pytest.raises(phys.MadronaError):
+        e.set_joints(sc.joints, np.full(2, sc.joints.shape[1] + 1, np.int32))
 
 
 @pytest.mark.parametrize("name", sorted(CASES))

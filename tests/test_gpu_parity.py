@@ -17,6 +17,7 @@ SCENES = {
     "tumble24": lambda: scenes.tumble(48),
     "tumble40": lambda: scenes.tumble(16, num_bodies=40, spread=1.0, seed=3),
     "tumble12_noplane": lambda: scenes.tumble(16, num_bodies=12, seed=7, spread=0.8, with_plane=False),
+    "jointed": lambda: scenes.jointed(37),
 }
 
 
@@ -64,6 +65,39 @@ def test_cuda_matches_reference_golden(cuda_lib, port_oracle, name):
     if o2.indeterminate()[pw] == 0:
         for s, c in enumerate(pr["contacts"]):
             assert contacts_equal(c, g[f"probe_contacts_{s}"]), f"substep {s}"
+
+
+def test_cuda_hinges_and_joint_table_updates(cuda_lib, port_oracle):
+    """Hinge joints while the reference keeps the state finite (scenes.jointed), then the joint
+    table replaced and removed through mdr_phys_set_joints between steps."""
+    sc = scenes.jointed(21, hinges=True)
+    o = port_oracle.Oracle(sc, "port")
+    e = phys.PhysExecutor(sc)
+    for st in range(8):
+        o.step()
+        e.run()
+        assert_state_equal(e.state(), o.state(), None, f"hinges step {st}")
+    plain = scenes.jointed(21)
+    e2 = phys.PhysExecutor(sc)
+    e2.set_joints(plain.joints, plain.joint_counts)
+    o2 = port_oracle.Oracle(plain, "port")
+    e2.run(30)
+    o2.step(30)
+    assert_state_equal(e2.state(), o2.state(), None, "joint table replaced")
+    e2.set_joints(None)
+    bare = scenes.jointed(21)
+    bare.joints = bare.joint_counts = None
+    o3 = port_oracle.Oracle(bare, "port")
+    for c in (phys.COL_POSITION, phys.COL_ROTATION, phys.COL_VELOCITY):
+        o3.write(c, e2.read(c))
+    o3.flag_rebuild(); e2.flag_rebuild()
+    e2.run(5)
+    o3.step(5)
+    assert_state_equal(e2.state(), o3.state(), None, "joints removed")
+    bad = plain.joints.copy()
+    bad["row1"][3, 0] = -1
+    with pytest.raises(phys.MadronaError):
+        e2.set_joints(bad, plain.joint_counts)
 
 
 def test_cuda_drift_100_steps(cuda_lib, port_oracle):

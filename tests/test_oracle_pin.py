@@ -36,9 +36,10 @@ def test_port_matches_golden(port_oracle, name):
             assert contacts_equal(c, g[f"probe_contacts_{s}"]), f"substep {s}"
 
 
-@pytest.mark.parametrize("scene", ["collisions64", "tumble24", "tumble40"])
+@pytest.mark.parametrize("scene", ["collisions64", "tumble24", "tumble40", "jointed"])
 def test_port_matches_compiled_reference(port_oracle, ref_oracle, scene):
     sc = {"collisions64": lambda: scenes.collisions64(6),
+          "jointed": lambda: scenes.jointed(8),
           "tumble24": lambda: scenes.tumble(12),
           "tumble40": lambda: scenes.tumble(6, num_bodies=40, spread=1.0, seed=3)}[scene]()
     r = ref_oracle.Oracle(sc, "reference")
@@ -49,6 +50,18 @@ def test_port_matches_compiled_reference(port_oracle, ref_oracle, scene):
         det = p.indeterminate() == 0
         assert_state_equal(p.state(), r.state(), det, f"{scene} step {st}")
     assert det.any()
+
+
+def test_port_hinges_match_compiled_reference(port_oracle, ref_oracle):
+    """handleJointConstraint's hinge branch, on the steps the reference keeps finite."""
+    sc = scenes.jointed(6, hinges=True)
+    r = ref_oracle.Oracle(sc, "reference")
+    p = port_oracle.Oracle(sc, "port")
+    for st in range(8):
+        r.step()
+        p.step()
+        assert all(np.isfinite(a).all() for a in r.state())
+        assert_state_equal(p.state(), r.state(), None, f"hinges step {st}")
 
 
 def test_hull_tables_match_reference(port_oracle, ref_oracle):
