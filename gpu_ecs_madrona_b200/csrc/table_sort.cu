@@ -1,0 +1,436 @@
+// Global sort / compaction of a shared (not per-world) archetype table by a u32 key
+// column: the reference's SortArchetypeNodeBase graph
+// (src/mw/device/sort_archetype.cpp:960-1392: sortSetup, zeroBins, histogram, binScan,
+// prepareOnesweep + onesweep per 8-bit digit, resizeTable, copyKeys, stageColumn +
+// rearrangeColumn per column, rearrangeEntities) as five hand-written sm_100a kernels
+// behind the mdr_sort_* C ABI.
+//
+// What it computes (the contract the parity tests hold it to): a STABLE sort of the rows
+// by the low 8*passes bits of the key, passes = ceil(bits(num_worlds + 1) / 8) for a
+// WorldID sort (sort_archetype.cpp:1290-1299) else 4; every column permuted the same way;
+// for a WorldID sort the table is cut to the rows whose top digit is below 255
+// (resizeTable, :1216-1221: rows of destroyed entities carry WorldID -1 and sort last);
+// the entity -> row map is rewritten for the surviving rows (rearrangeEntities, :1243-1263).
+//
+// B200 shape: all traffic is streaming and HBM-bound (no tensor cores). One histogram
+// pass builds every digit's bins at once; one single-pass kernel per digit ranks a 4096-key
+// tile with warp match-any (stable), chains tiles with decoupled look-back, reorders the
+// tile in shared memory and writes whole digit runs (coalesced); ONE gather kernel moves
+// every column (the reference stages and copies back each column in two node pairs).
+// Columns are gathered from `columns_in` to `columns_out`: callers that double-buffer
+// their tables pay one read and one write per byte; a column whose in and out pointers
+// are the same goes through a staging buffer like the reference does.
+#include <cuda_runtime.h>
+
+#include <cstdint>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <vector>
+
+#include "../../include/madrona_b200.h"
+
+#define REQ_CUDA(expr)                                                                   \
+    do {                                                                                 \
+        cudaError_t e_ = (expr);                                                         \
+        if (e_ != cudaSuccess) {                                                         \
+            fprintf(stderr, "madrona_b200: CUDA error %s at %s:%d: %s\n",                \
+                    cudaGetErrorName(e_), __FILE__, __LINE__, cudaGetErrorString(e_));   \
+            abort();                                                                     \
+        }                                                                                \
+    } while (0)
+
+namespace {
+
+constexpr int kDigits = 256;          // RADIX_BITS = 8 (sort_archetype.cpp sortConsts)
+constexpr int kThreads = 256;
+constexpr int kWarps = kThreads / 32;
+constexpr int kItems = 16;            // keys per thread in a tile
+constexpr int kTile = kThreads * kItems;
+constexpr int kMaxPasses = 4;
+constexpr uint32_t kFlagAggregate = 1u << 30, kFlagInclusive = 2u << 30, kValueMask = (1u << 30) - 1;
+
+// ---- 1. all digit histograms in one pass over the keys -----------------------
+__global__ void __launch_bounds__(kThreads)
+sortHistogramKernel(const uint32_t *__restrict__ keys, int n, int passes, uint32_t *__restrict__ bins)
+{
+    __shared__ uint32_t s_bins[kMaxPasses][kDigits];
+    for (int p = 0; p < passes; p++) s_bins[p][threadIdx.x] = 0;
+    __syncthreads();
+    const int n4 = n / 4;
+    const uint4 *keys4 = reinterpret_cast<const uint4 *>(keys);
+    for (int i = blockIdx.x * kThreads + threadIdx.x; i < n4; i += gridDim.x * kThreads) {
+        const uint4 k = __ldg(keys4 + i);
+        const uint32_t ks[4] = { k.x, k.y, k.z, k.w };
+#pragma unroll
+        for (int j = 0; j < 4; j++)
+            for (int p = 0; p < passes; p++) atomicAdd(&s_bins[p][(ks[j] >> (8 * p)) & 255u], 1u);
+    }
+    if (blockIdx.x == 0 && threadIdx.x < n - 4 * n4) {
+        const uint32_t k = keys[4 * n4 + threadIdx.x];
+        for (int p = 0; p < passes; p++) atomicAdd(&s_bins[p][(k >> (8 * p)) & 255u], 1u);
+    }
+    __syncthreads();
+    for (int p = 0; p < passes; p++) {
+        const uint32_t c = s_bins[p][threadIdx.x];
+        if (c) atomicAdd(&bins[p * kDigits + threadIdx.x], c);
+    }
+}
+
+// Exclusive scan of 256 values held one per thread of a 256-thread block.
+__device__ __forceinline__ uint32_t blockExclusiveScan(uint32_t x, uint32_t *s_warp /*[kWarps]*/, uint32_t *total)
+{
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    uint32_t incl = x;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const uint32_t y = __shfl_up_sync(0xffffffffu, incl, d);
+        if (lane >= d) incl += y;
+    }
+    if (lane == 31) s_warp[warp] = incl;
+    __syncthreads();
+    uint32_t before = 0, all = 0;
+#pragma unroll
+    for (int w = 0; w < kWarps; w++) {
+        const uint32_t s = s_warp[w];
+        if (w < warp) before += s;
+        all += s;
+    }
+    if (total) *total = all;
+    __syncthreads();
+    return before + incl - x;
+}
+
+// ---- 2. bins -> exclusive offsets, one block per digit position ---------------
+// Also keeps the count of the last digit's value 255 out of the way: the caller reads the
+// new row count as the offset of digit 255 of the last pass (resizeTable).
+__global__ void __launch_bounds__(kThreads) sortScanKernel(uint32_t *bins)
+{
+    __shared__ uint32_t s_warp[kWarps];
+    uint32_t *b = bins + blockIdx.x * kDigits;
+    const uint32_t x = b[threadIdx.x];
+    b[threadIdx.x] = blockExclusiveScan(x, s_warp, nullptr);
+}
+
+// ---- 3. one digit: rank, look back, reorder, scatter --------------------------
+struct OnesweepSmem {
+    uint32_t warp_cnt[kWarps][kDigits];
+    uint32_t tile_off[kDigits];
+    uint32_t gbase[kDigits];
+    uint32_t keys[kTile];
+    int32_t vals[kTile];
+    uint32_t s_warp[kWarps];
+    uint32_t tile;
+};
+
+__global__ void __launch_bounds__(kThreads, 4)
+sortOnesweepKernel(const uint32_t *__restrict__ src_keys, const int32_t *__restrict__ src_vals,
+                   uint32_t *__restrict__ dst_keys, int32_t *__restrict__ dst_vals,
+                   const uint32_t *__restrict__ bins, uint32_t *lookback, uint32_t *tile_counter,
+                   int n, int shift)
+{
+    extern __shared__ __align__(16) char smem_raw[];
+    OnesweepSmem &s = *reinterpret_cast<OnesweepSmem *>(smem_raw);
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    // Tiles are handed out in launch order, so a tile only ever waits for tiles whose blocks
+    // are already running (forward progress of the look-back).
+    if (tid == 0) s.tile = atomicAdd(tile_counter, 1u);
+#pragma unroll
+    for (int w = 0; w < kWarps; w++) s.warp_cnt[w][tid] = 0;
+    __syncthreads();
+    const uint32_t tile = s.tile;
+    const int base = (int)tile * kTile;
+    const int tile_n = min(kTile, n - base);
+
+    // (a) stable rank inside the warp's 512 consecutive keys: match-any per round of 32.
+    // All key loads are issued before the first rank (16 independent loads in flight).
+    uint32_t key[kItems];
+    uint16_t rank[kItems];
+    const uint32_t lt = (1u << lane) - 1u;
+    const int first = warp * (kItems * 32) + lane;
+#pragma unroll
+    for (int r = 0; r < kItems; r++) {
+        const int local = first + r * 32;
+        key[r] = local < tile_n ? __ldg(src_keys + base + local) : 0xffffffffu;
+    }
+#pragma unroll
+    for (int r = 0; r < kItems; r++) {
+        const bool valid = first + r * 32 < tile_n;
+        const uint32_t digit = (key[r] >> shift) & 255u;
+        const uint32_t mask = __match_any_sync(0xffffffffu, valid ? digit : (0x100u | lane));
+        uint32_t *cnt = &s.warp_cnt[warp][digit];
+        const uint32_t before = valid ? *cnt : 0u;
+        __syncwarp();
+        const uint32_t mine = __popc(mask & lt);
+        rank[r] = (uint16_t)(before + mine);
+        if (valid && mine == 0) *cnt = before + __popc(mask);
+        __syncwarp();
+    }
+    __syncthreads();
+
+    // (b) thread d owns digit d: warp counts -> warp offsets, tile count
+    uint32_t tile_count = 0;
+#pragma unroll
+    for (int w = 0; w < kWarps; w++) {
+        const uint32_t c = s.warp_cnt[w][tid];
+        s.warp_cnt[w][tid] = tile_count;
+        tile_count += c;
+    }
+    // (c) decoupled look-back over the tiles before this one, per digit
+    volatile uint32_t *lb = lookback;
+    uint32_t excl = 0;
+    if (tile == 0) {
+        lb[tid] = kFlagInclusive | tile_count;
+    } else {
+        lb[(size_t)tile * kDigits + tid] = kFlagAggregate | tile_count;
+        for (int t = (int)tile - 1;; t--) {
+            uint32_t v;
+            do { v = lb[(size_t)t * kDigits + tid]; } while ((v >> 30) == 0u);
+            excl += v & kValueMask;
+            if ((v >> 30) == 2u) break;
+        }
+        lb[(size_t)tile * kDigits + tid] = kFlagInclusive | (excl + tile_count);
+    }
+    // (d) where each digit's run starts inside the tile and in the output
+    const uint32_t off = blockExclusiveScan(tile_count, s.s_warp, nullptr);
+    s.tile_off[tid] = off;
+    s.gbase[tid] = __ldg(bins + tid) + excl - off;
+    __syncthreads();
+
+    // (e) reorder the tile in shared memory, then write digit runs with consecutive threads
+#pragma unroll
+    for (int r = 0; r < kItems; r++) {
+        const int local = first + r * 32;
+        if (local < tile_n) {
+            const uint32_t digit = (key[r] >> shift) & 255u;
+            const uint32_t pos = s.tile_off[digit] + s.warp_cnt[warp][digit] + rank[r];
+            s.keys[pos] = key[r];
+            s.vals[pos] = src_vals ? __ldg(src_vals + base + local) : base + local;   // pass 0: identity
+        }
+    }
+    __syncthreads();
+    for (int k = tid; k < tile_n; k += kThreads) {
+        const uint32_t kk = s.keys[k];
+        const uint32_t dst = s.gbase[(kk >> shift) & 255u] + (uint32_t)k;
+        dst_keys[dst] = kk;
+        dst_vals[dst] = s.vals[k];
+    }
+}
+
+// ---- 4. every column through the permutation, one launch ----------------------
+struct ColumnDesc {
+    const char *src;
+    char *dst;
+    int32_t words;        // 4-byte words per row (column bytes are a multiple of 4)
+    int32_t is_key;       // the key column is written from the sorted keys
+};
+
+// blockIdx.y = column. Thread = one 4-byte word of the output: consecutive threads write
+// consecutive words (coalesced), and read runs of `words` consecutive words per source row.
+__global__ void __launch_bounds__(256)
+tableGatherKernel(const ColumnDesc *__restrict__ cols, const int32_t *__restrict__ perm,
+                  const uint32_t *__restrict__ sorted_keys, int rows)
+{
+    const ColumnDesc c = cols[blockIdx.y];
+    const int64_t total = (int64_t)rows * c.words;
+    uint32_t *dst = reinterpret_cast<uint32_t *>(c.dst);
+    const uint32_t *src = reinterpret_cast<const uint32_t *>(c.src);
+    for (int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; j < total; j += (int64_t)gridDim.x * blockDim.x) {
+        if (c.is_key) { dst[j] = __ldg(sorted_keys + j); continue; }
+        const int row = (int)(j / c.words);
+        const int k = (int)(j - (int64_t)row * c.words);
+        dst[j] = __ldg(src + (int64_t)__ldg(perm + row) * c.words + k);
+    }
+}
+
+// ---- 5. entity -> row map of the rows that survive (rearrangeEntities) --------
+__global__ void entityRemapKernel(const int32_t *__restrict__ entities /*[rows] (gen, id)*/, int rows,
+                                  const uint32_t *__restrict__ cut, int32_t *__restrict__ entity_row, int32_t max_ids)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= rows || (cut && (uint32_t)i >= __ldg(cut))) return;
+    const int32_t id = __ldg(entities + 2 * (int64_t)i + 1);
+    if (id >= 0 && id < max_ids) entity_row[id] = i;
+}
+
+int passesFor(int num_worlds)
+{
+    if (num_worlds <= 0) return 4;                       // generic key: all 32 bits
+    int bits = 0;
+    for (uint32_t v = (uint32_t)num_worlds + 1u; v; v >>= 1) bits++;   // 32 - clz(num_worlds + 1)
+    return (bits + 7) / 8;
+}
+
+}  // namespace
+
+struct mdr_sort {
+    int gpu_id = 0;
+    int max_rows = 0, num_columns = 0, key_col = 0, passes = 0, world_sort = 0;
+    std::vector<int32_t> col_bytes;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    uint32_t *keys_a = nullptr, *keys_b = nullptr;
+    int32_t *vals_a = nullptr, *vals_b = nullptr;
+    uint32_t *bins = nullptr, *lookback = nullptr, *counters = nullptr;
+    ColumnDesc *d_cols = nullptr;
+    char *staging = nullptr;
+    size_t staging_bytes = 0;
+    int sms = 0;
+    float last_ms = 0.f;
+    int last_launches = 0;
+    uint32_t host_cut = 0;
+};
+
+extern "C" {
+
+int32_t mdr_sort_num_passes(int32_t num_worlds) { return passesFor(num_worlds); }
+
+int32_t mdr_sort_create(int32_t gpu_id, int32_t max_rows, int32_t num_columns, const int32_t *column_bytes,
+                        int32_t key_column, int32_t num_worlds, mdr_sort **out)
+{
+    if (!out || max_rows <= 0 || num_columns <= 0 || num_columns > 128 || !column_bytes ||
+        key_column < 0 || key_column >= num_columns || column_bytes[key_column] != 4)
+        return MDR_EINVAL;
+    size_t max_col = 0;
+    for (int c = 0; c < num_columns; c++) {
+        if (column_bytes[c] <= 0 || column_bytes[c] % 4) return MDR_EINVAL;
+        if ((size_t)column_bytes[c] > max_col) max_col = column_bytes[c];
+    }
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || gpu_id < 0 || gpu_id >= ndev) return MDR_ENODEVICE;
+    REQ_CUDA(cudaSetDevice(gpu_id));
+    mdr_sort *s = new mdr_sort;
+    s->gpu_id = gpu_id;
+    s->max_rows = max_rows;
+    s->num_columns = num_columns;
+    s->key_col = key_column;
+    s->passes = passesFor(num_worlds);
+    s->world_sort = num_worlds > 0;
+    s->col_bytes.assign(column_bytes, column_bytes + num_columns);
+    cudaDeviceProp prop;
+    REQ_CUDA(cudaGetDeviceProperties(&prop, gpu_id));
+    s->sms = prop.multiProcessorCount;
+    const size_t tiles = ((size_t)max_rows + kTile - 1) / kTile;
+    REQ_CUDA(cudaMalloc((void **)&s->keys_a, 4 * (size_t)max_rows));
+    REQ_CUDA(cudaMalloc((void **)&s->keys_b, 4 * (size_t)max_rows));
+    REQ_CUDA(cudaMalloc((void **)&s->vals_a, 4 * (size_t)max_rows));
+    REQ_CUDA(cudaMalloc((void **)&s->vals_b, 4 * (size_t)max_rows));
+    REQ_CUDA(cudaMalloc((void **)&s->bins, 4 * (size_t)kMaxPasses * kDigits));
+    REQ_CUDA(cudaMalloc((void **)&s->lookback, 4 * tiles * kDigits * kMaxPasses));
+    REQ_CUDA(cudaMalloc((void **)&s->counters, 4 * kMaxPasses));
+    REQ_CUDA(cudaMalloc((void **)&s->d_cols, sizeof(ColumnDesc) * (size_t)num_columns));
+    s->staging_bytes = max_col * (size_t)max_rows;
+    REQ_CUDA(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
+    REQ_CUDA(cudaEventCreate(&s->ev0));
+    REQ_CUDA(cudaEventCreate(&s->ev1));
+    REQ_CUDA(cudaFuncSetAttribute(sortOnesweepKernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  (int)sizeof(OnesweepSmem)));
+    *out = s;
+    return MDR_OK;
+}
+
+void mdr_sort_destroy(mdr_sort *s)
+{
+    if (!s) return;
+    cudaSetDevice(s->gpu_id);
+    if (s->stream) { cudaStreamSynchronize(s->stream); cudaStreamDestroy(s->stream); }
+    if (s->ev0) cudaEventDestroy(s->ev0);
+    if (s->ev1) cudaEventDestroy(s->ev1);
+    for (void *p : { (void *)s->keys_a, (void *)s->keys_b, (void *)s->vals_a, (void *)s->vals_b, (void *)s->bins,
+                     (void *)s->lookback, (void *)s->counters, (void *)s->d_cols, (void *)s->staging })
+        if (p) cudaFree(p);
+    delete s;
+}
+
+int32_t mdr_sort_run(mdr_sort *s, const void *const *columns_in, void *const *columns_out, int32_t num_rows,
+                     int32_t *entity_row, int32_t max_entity_ids, int32_t *out_num_rows)
+{
+    if (!s || !columns_in || !columns_out || num_rows < 0 || num_rows > s->max_rows) return MDR_EINVAL;
+    for (int c = 0; c < s->num_columns; c++)
+        if (!columns_in[c] || !columns_out[c] || ((uintptr_t)columns_in[c] & 15u) || ((uintptr_t)columns_out[c] & 3u))
+            return MDR_EINVAL;
+    REQ_CUDA(cudaSetDevice(s->gpu_id));
+    cudaStream_t st = s->stream;
+    int new_rows = num_rows;
+    s->last_launches = 0;
+    REQ_CUDA(cudaEventRecord(s->ev0, st));
+    if (num_rows > 0) {
+        const uint32_t *keys_col = (const uint32_t *)columns_in[s->key_col];
+        const int tiles = (num_rows + kTile - 1) / kTile;
+        REQ_CUDA(cudaMemsetAsync(s->bins, 0, 4 * (size_t)s->passes * kDigits, st));
+        REQ_CUDA(cudaMemsetAsync(s->lookback, 0, 4 * (size_t)tiles * kDigits * s->passes, st));
+        REQ_CUDA(cudaMemsetAsync(s->counters, 0, 4 * kMaxPasses, st));
+        int hgrid = (num_rows / 4 + kThreads - 1) / kThreads;
+        if (hgrid > 8 * s->sms) hgrid = 8 * s->sms;
+        if (hgrid < 1) hgrid = 1;
+        sortHistogramKernel<<<hgrid, kThreads, 0, st>>>(keys_col, num_rows, s->passes, s->bins);
+        sortScanKernel<<<s->passes, kThreads, 0, st>>>(s->bins);
+        s->last_launches += 2;
+        const uint32_t *src_k = keys_col;
+        const int32_t *src_v = nullptr;                  // pass 0 reads the identity permutation
+        for (int p = 0; p < s->passes; p++) {
+            uint32_t *dst_k = p % 2 == 0 ? s->keys_a : s->keys_b;
+            int32_t *dst_v = p % 2 == 0 ? s->vals_a : s->vals_b;
+            sortOnesweepKernel<<<tiles, kThreads, sizeof(OnesweepSmem), st>>>(
+                src_k, src_v, dst_k, dst_v, s->bins + p * kDigits, s->lookback + (size_t)p * tiles * kDigits,
+                s->counters + p, num_rows, 8 * p);
+            s->last_launches++;
+            src_k = dst_k;
+            src_v = dst_v;
+        }
+        // Columns: out-of-place ones straight into columns_out in ONE launch; a column whose in and
+        // out pointers are the same goes through the staging buffer (stageColumn + rearrangeColumn).
+        // Rows past the cut keep their sorted (dead) content, as in the reference.
+        std::vector<ColumnDesc> descs;
+        std::vector<int> inplace;
+        for (int c = 0; c < s->num_columns; c++) {
+            const bool is_key = c == s->key_col;
+            if (columns_in[c] == columns_out[c] && !is_key) { inplace.push_back(c); continue; }
+            descs.push_back(ColumnDesc { (const char *)columns_in[c], (char *)columns_out[c], s->col_bytes[c] / 4, is_key });
+        }
+        const int num_direct = (int)descs.size();
+        if (!inplace.empty() && !s->staging) REQ_CUDA(cudaMalloc((void **)&s->staging, s->staging_bytes));
+        for (int c : inplace)
+            descs.push_back(ColumnDesc { (const char *)columns_in[c], s->staging, s->col_bytes[c] / 4, 0 });
+        REQ_CUDA(cudaMemcpyAsync(s->d_cols, descs.data(), sizeof(ColumnDesc) * descs.size(), cudaMemcpyHostToDevice, st));
+        auto launch = [&](int first, int count) {
+            int64_t max_words = 0;
+            for (int k = first; k < first + count; k++)
+                if ((int64_t)descs[k].words * num_rows > max_words) max_words = (int64_t)descs[k].words * num_rows;
+            int64_t gx = (max_words + 255) / 256;
+            if (gx > 16 * (int64_t)s->sms) gx = 16 * (int64_t)s->sms;
+            if (gx < 1) gx = 1;
+            tableGatherKernel<<<dim3((unsigned)gx, (unsigned)count), 256, 0, st>>>(s->d_cols + first, src_v, src_k, num_rows);
+            s->last_launches++;
+        };
+        if (num_direct) launch(0, num_direct);
+        for (size_t k = 0; k < inplace.size(); k++) {
+            launch(num_direct + (int)k, 1);
+            REQ_CUDA(cudaMemcpyAsync((void *)columns_out[inplace[k]], s->staging,
+                                     (size_t)s->col_bytes[inplace[k]] * num_rows, cudaMemcpyDeviceToDevice, st));
+        }
+        // resizeTable: the rows before digit 255 of the last pass survive a WorldID sort
+        const uint32_t *cut = s->world_sort ? s->bins + (s->passes - 1) * kDigits + 255 : nullptr;
+        if (entity_row) {
+            entityRemapKernel<<<(num_rows + 255) / 256, 256, 0, st>>>((const int32_t *)columns_out[0], num_rows, cut,
+                                                                      entity_row, max_entity_ids);
+            s->last_launches++;
+        }
+        if (cut) REQ_CUDA(cudaMemcpyAsync(&s->host_cut, cut, 4, cudaMemcpyDeviceToHost, st));
+    }
+    REQ_CUDA(cudaEventRecord(s->ev1, st));
+    REQ_CUDA(cudaStreamSynchronize(st));
+    REQ_CUDA(cudaEventElapsedTime(&s->last_ms, s->ev0, s->ev1));
+    if (num_rows > 0 && s->world_sort) new_rows = (int)s->host_cut;
+    if (out_num_rows) *out_num_rows = new_rows;
+    return MDR_OK;
+}
+
+float mdr_sort_last_ms(mdr_sort *s, int32_t *launches)
+{
+    if (!s) return 0.f;
+    if (launches) *launches = s->last_launches;
+    return s->last_ms;
+}
+
+}  // extern "C"

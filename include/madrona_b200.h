@@ -320,6 +320,28 @@ int32_t mdr_app_setup(mdr_ecs *e, int32_t app, const int32_t *params, int32_t np
 const char *mdr_version(void);
 int32_t mdr_device_count(void);
 
+/* ---- global sort / compaction of a shared archetype table ---------------------
+ * SortArchetypeNodeBase::addToGraph (src/mw/device/sort_archetype.cpp:1267-1392) and the nodes
+ * it chains (:960-1265) as one operator: rows of a table stored as one global SoA (not per-world
+ * tiles) are stably sorted by the low 8 * passes bits of a u32 key column, passes =
+ * ceil(bits(num_worlds + 1) / 8) when the key is the WorldID column (num_worlds > 0) and 4
+ * otherwise (:1290-1299); every column is permuted alike; after a WorldID sort the table keeps
+ * the rows whose top digit is below 255 (resizeTable :1216-1221: destroyed rows carry WorldID -1
+ * and sort last) and entity_row[entity id] is rewritten for them (rearrangeEntities :1243-1263).
+ * Column 0 is the Entity column {gen, id} (8 bytes); column sizes are multiples of 4 bytes.
+ * columns_in / columns_out are DEVICE pointers (16-byte aligned), one per column; a column may
+ * be sorted in place (same pointer in both: staged and copied back, as the reference does) or
+ * into a second buffer (one read + one write per byte). Blocking, like MWCudaExecutor::run(). */
+typedef struct mdr_sort mdr_sort;
+int32_t mdr_sort_num_passes(int32_t num_worlds);
+int32_t mdr_sort_create(int32_t gpu_id, int32_t max_rows, int32_t num_columns, const int32_t *column_bytes,
+                        int32_t key_column, int32_t num_worlds, mdr_sort **out);
+void mdr_sort_destroy(mdr_sort *s);
+int32_t mdr_sort_run(mdr_sort *s, const void *const *columns_in, void *const *columns_out, int32_t num_rows,
+                     int32_t *entity_row, int32_t max_entity_ids, int32_t *out_num_rows);
+/* Device time of the last mdr_sort_run (CUDA events on its stream) and its kernel launches. */
+float mdr_sort_last_ms(mdr_sort *s, int32_t *launches);
+
 #ifdef __cplusplus
 }
 #endif
