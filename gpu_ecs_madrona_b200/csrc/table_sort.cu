@@ -226,20 +226,55 @@ struct ColumnDesc {
 };
 
 // blockIdx.y = column. Thread = one 4-byte word of the output: consecutive threads write
-// consecutive words (coalesced), and read runs of `words` consecutive words per source row.
+// consecutive words (coalesced) and read runs of `words` consecutive words per source row.
+// The row of a word is a division by the column's word count: a compile-time constant per
+// instantiation (a variable 64-bit division cost more than the memory traffic), four
+// independent words per thread and iteration in flight.
+template <int kWords>
+__device__ __forceinline__ void gatherColumn(const uint32_t *__restrict__ src, uint32_t *__restrict__ dst,
+                                             const int32_t *__restrict__ perm, uint32_t total, int words_rt)
+{
+    const uint32_t words = kWords > 0 ? (uint32_t)kWords : (uint32_t)words_rt;
+    const uint32_t stride = gridDim.x * blockDim.x;
+    uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+    for (; j + 3u * stride < total; j += 4u * stride) {
+        uint32_t v[4];
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            const uint32_t jj = j + (uint32_t)u * stride;
+            const uint32_t row = jj / words;
+            v[u] = __ldg(src + (size_t)__ldg(perm + row) * words + (jj - row * words));
+        }
+#pragma unroll
+        for (int u = 0; u < 4; u++) dst[j + (uint32_t)u * stride] = v[u];
+    }
+    for (; j < total; j += stride) {
+        const uint32_t row = j / words;
+        dst[j] = __ldg(src + (size_t)__ldg(perm + row) * words + (j - row * words));
+    }
+}
+
 __global__ void __launch_bounds__(256)
 tableGatherKernel(const ColumnDesc *__restrict__ cols, const int32_t *__restrict__ perm,
                   const uint32_t *__restrict__ sorted_keys, int rows)
 {
     const ColumnDesc c = cols[blockIdx.y];
-    const int64_t total = (int64_t)rows * c.words;
+    const uint32_t total = (uint32_t)rows * (uint32_t)c.words;
     uint32_t *dst = reinterpret_cast<uint32_t *>(c.dst);
     const uint32_t *src = reinterpret_cast<const uint32_t *>(c.src);
-    for (int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; j < total; j += (int64_t)gridDim.x * blockDim.x) {
-        if (c.is_key) { dst[j] = __ldg(sorted_keys + j); continue; }
-        const int row = (int)(j / c.words);
-        const int k = (int)(j - (int64_t)row * c.words);
-        dst[j] = __ldg(src + (int64_t)__ldg(perm + row) * c.words + k);
+    if (c.is_key) {
+        for (uint32_t j = blockIdx.x * blockDim.x + threadIdx.x; j < total; j += gridDim.x * blockDim.x)
+            dst[j] = __ldg(sorted_keys + j);
+        return;
+    }
+    switch (c.words) {                   // block-uniform
+    case 1: gatherColumn<1>(src, dst, perm, total, 1); break;
+    case 2: gatherColumn<2>(src, dst, perm, total, 2); break;
+    case 3: gatherColumn<3>(src, dst, perm, total, 3); break;
+    case 4: gatherColumn<4>(src, dst, perm, total, 4); break;
+    case 6: gatherColumn<6>(src, dst, perm, total, 6); break;
+    case 7: gatherColumn<7>(src, dst, perm, total, 7); break;
+    default: gatherColumn<0>(src, dst, perm, total, c.words); break;
     }
 }
 
@@ -273,6 +308,7 @@ struct mdr_sort {
     int32_t *vals_a = nullptr, *vals_b = nullptr;
     uint32_t *bins = nullptr, *lookback = nullptr, *counters = nullptr;
     ColumnDesc *d_cols = nullptr;
+    std::vector<ColumnDesc> h_cols;
     char *staging = nullptr;
     size_t staging_bytes = 0;
     int sms = 0;
@@ -315,9 +351,10 @@ int32_t mdr_sort_create(int32_t gpu_id, int32_t max_rows, int32_t num_columns, c
     REQ_CUDA(cudaMalloc((void **)&s->keys_b, 4 * (size_t)max_rows));
     REQ_CUDA(cudaMalloc((void **)&s->vals_a, 4 * (size_t)max_rows));
     REQ_CUDA(cudaMalloc((void **)&s->vals_b, 4 * (size_t)max_rows));
-    REQ_CUDA(cudaMalloc((void **)&s->bins, 4 * (size_t)kMaxPasses * kDigits));
-    REQ_CUDA(cudaMalloc((void **)&s->lookback, 4 * tiles * kDigits * kMaxPasses));
-    REQ_CUDA(cudaMalloc((void **)&s->counters, 4 * kMaxPasses));
+    // bins | tile counters | look-back words in one block: one memset per run
+    REQ_CUDA(cudaMalloc((void **)&s->bins, 4 * ((size_t)kMaxPasses * kDigits + kDigits + tiles * kDigits * kMaxPasses)));
+    s->counters = s->bins + kMaxPasses * kDigits;
+    s->lookback = s->counters + kDigits;
     REQ_CUDA(cudaMalloc((void **)&s->d_cols, sizeof(ColumnDesc) * (size_t)num_columns));
     s->staging_bytes = max_col * (size_t)max_rows;
     REQ_CUDA(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
@@ -337,7 +374,7 @@ void mdr_sort_destroy(mdr_sort *s)
     if (s->ev0) cudaEventDestroy(s->ev0);
     if (s->ev1) cudaEventDestroy(s->ev1);
     for (void *p : { (void *)s->keys_a, (void *)s->keys_b, (void *)s->vals_a, (void *)s->vals_b, (void *)s->bins,
-                     (void *)s->lookback, (void *)s->counters, (void *)s->d_cols, (void *)s->staging })
+                     (void *)s->d_cols, (void *)s->staging })
         if (p) cudaFree(p);
     delete s;
 }
@@ -357,9 +394,7 @@ int32_t mdr_sort_run(mdr_sort *s, const void *const *columns_in, void *const *co
     if (num_rows > 0) {
         const uint32_t *keys_col = (const uint32_t *)columns_in[s->key_col];
         const int tiles = (num_rows + kTile - 1) / kTile;
-        REQ_CUDA(cudaMemsetAsync(s->bins, 0, 4 * (size_t)s->passes * kDigits, st));
-        REQ_CUDA(cudaMemsetAsync(s->lookback, 0, 4 * (size_t)tiles * kDigits * s->passes, st));
-        REQ_CUDA(cudaMemsetAsync(s->counters, 0, 4 * kMaxPasses, st));
+        REQ_CUDA(cudaMemsetAsync(s->bins, 0, 4 * ((size_t)kMaxPasses * kDigits + kDigits + (size_t)tiles * kDigits * s->passes), st));
         int hgrid = (num_rows / 4 + kThreads - 1) / kThreads;
         if (hgrid > 8 * s->sms) hgrid = 8 * s->sms;
         if (hgrid < 1) hgrid = 1;
@@ -386,13 +421,18 @@ int32_t mdr_sort_run(mdr_sort *s, const void *const *columns_in, void *const *co
         for (int c = 0; c < s->num_columns; c++) {
             const bool is_key = c == s->key_col;
             if (columns_in[c] == columns_out[c] && !is_key) { inplace.push_back(c); continue; }
-            descs.push_back(ColumnDesc { (const char *)columns_in[c], (char *)columns_out[c], s->col_bytes[c] / 4, is_key });
+            { ColumnDesc d; memset(&d, 0, sizeof(d)); d.src = (const char *)columns_in[c]; d.dst = (char *)columns_out[c]; d.words = s->col_bytes[c] / 4; d.is_key = is_key; descs.push_back(d); }
         }
         const int num_direct = (int)descs.size();
+        for (const ColumnDesc &d : descs)
+            if ((int64_t)d.words * num_rows >= (int64_t)1 << 32) return MDR_ECAPACITY;   // word index is 32-bit
         if (!inplace.empty() && !s->staging) REQ_CUDA(cudaMalloc((void **)&s->staging, s->staging_bytes));
         for (int c : inplace)
-            descs.push_back(ColumnDesc { (const char *)columns_in[c], s->staging, s->col_bytes[c] / 4, 0 });
-        REQ_CUDA(cudaMemcpyAsync(s->d_cols, descs.data(), sizeof(ColumnDesc) * descs.size(), cudaMemcpyHostToDevice, st));
+            { ColumnDesc d; memset(&d, 0, sizeof(d)); d.src = (const char *)columns_in[c]; d.dst = s->staging; d.words = s->col_bytes[c] / 4; descs.push_back(d); }
+        if (descs.size() != s->h_cols.size() || memcmp(descs.data(), s->h_cols.data(), sizeof(ColumnDesc) * descs.size())) {
+            s->h_cols = descs;      // same buffers as last run (the usual case): nothing to upload
+            REQ_CUDA(cudaMemcpyAsync(s->d_cols, s->h_cols.data(), sizeof(ColumnDesc) * descs.size(), cudaMemcpyHostToDevice, st));
+        }
         auto launch = [&](int first, int count) {
             int64_t max_words = 0;
             for (int k = first; k < first + count; k++)
