@@ -54,7 +54,7 @@ class ClockSampler:
         try:
             self.proc = subprocess.Popen(
                 ["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + self.Q,
-                 "--format=csv,noheader,nounits", "-lms", "100"],
+                 "--format=csv,noheader,nounits", "-lms", "50"],
                 stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.t = threading.Thread(target=self._read, daemon=True)
             self.t.start()
@@ -65,6 +65,17 @@ class ClockSampler:
         for line in self.proc.stdout:
             self.rows.append([x.strip() for x in line.split(",")])
 
+    def wait_ready(self, timeout=8.0):
+        """nvidia-smi needs 0.1-1 s to come up (longer with 8 ranks starting one each): the sampler is
+        started during the warm-up and the timed region begins once the first row has arrived."""
+        t0 = time.perf_counter()
+        while self.proc and not self.rows and time.perf_counter() - t0 < timeout:
+            time.sleep(0.02)
+
+    def mark(self):
+        """Start of the timed region: earlier rows (warm-up, also under load) are dropped if later ones exist."""
+        self.first = len(self.rows)
+
     def stop(self):
         if not self.proc:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
@@ -74,6 +85,9 @@ class ClockSampler:
         except Exception:
             self.proc.kill()
         self.t.join(timeout=2)
+        first = getattr(self, "first", 0)
+        if len(self.rows) > first:
+            self.rows = self.rows[first:]
         sm, mx, reasons = [], [], set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         for r in self.rows:
@@ -182,11 +196,13 @@ def run_ours(args):
         ex.sync()
 
     # ---- device-resident throughput -------------------------------------
+    sampler = ClockSampler(local)
+    sampler.start()
     ex.run(args.warmup)
     ex.kernel_ms()
-    sampler = ClockSampler(local)
+    sampler.wait_ready()
     barrier()
-    sampler.start()
+    sampler.mark()
     t0 = time.perf_counter()
     ex.run_async(args.steps)
     ex.sync()

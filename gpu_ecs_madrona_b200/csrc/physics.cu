@@ -13,6 +13,7 @@
 #include "phys_lidar.cuh"
 #include "phys_feeder.cuh"
 #include "phys_assets.hpp"
+#include "obj_hull.hpp"
 #include "phys_cols.hpp"
 
 using namespace mdr;
@@ -714,6 +715,55 @@ int32_t mdr_phys_get_hull(mdr_phys *p, int32_t obj, uint32_t *half_edges, uint32
     if (polys) memcpy(polys, p->assets.polys.data() + o.face_off, 4 * (size_t)o.num_faces);
     if (planes) memcpy(planes, p->assets.planes.data() + 4 * (size_t)o.face_off, 16 * (size_t)o.num_faces);
     return MDR_OK;
+}
+
+static int32_t handOverHull(const ObjHull &h, bool ok, float *verts, int32_t *num_verts, uint32_t *poly_words,
+                            int32_t *num_poly_words, float aabb[6], char *err, int32_t err_cap)
+{
+    if (err && err_cap > 0) snprintf(err, (size_t)err_cap, "%s", h.error.c_str());
+    if (!ok) return MDR_EINVAL;
+    const int32_t nv = (int32_t)(h.verts.size() / 3), nw = (int32_t)h.words.size();
+    const bool query = !verts || !poly_words;
+    const bool fits = query || (*num_verts >= nv && *num_poly_words >= nw);
+    *num_verts = nv;
+    *num_poly_words = nw;
+    if (aabb) memcpy(aabb, h.aabb, sizeof(h.aabb));
+    if (query) return MDR_OK;
+    if (!fits) return MDR_EOVERFLOW;
+    memcpy(verts, h.verts.data(), 12 * (size_t)nv);
+    memcpy(poly_words, h.words.data(), 4 * (size_t)nw);
+    return MDR_OK;
+}
+
+int32_t mdr_load_hull_obj(const char *obj_text, int64_t num_bytes, float *verts, int32_t *num_verts,
+                          uint32_t *poly_words, int32_t *num_poly_words, float aabb[6], char *err, int32_t err_cap)
+{
+    if (!obj_text || num_bytes < 0 || !num_verts || !num_poly_words) return MDR_EINVAL;
+    ObjHull h;
+    const bool ok = loadObjHull(obj_text, (size_t)num_bytes, h);
+    return handOverHull(h, ok, verts, num_verts, poly_words, num_poly_words, aabb, err, err_cap);
+}
+
+int32_t mdr_load_hull_obj_file(const char *path, float *verts, int32_t *num_verts, uint32_t *poly_words,
+                               int32_t *num_poly_words, float aabb[6], char *err, int32_t err_cap)
+{
+    if (!path || !num_verts || !num_poly_words) return MDR_EINVAL;
+    ObjHull h;
+    std::string text;
+    bool ok = false;
+    const char *dot = strrchr(path, '.');
+    if (!dot || strcmp(dot + 1, "obj") != 0) {
+        h.error = "not an .obj path (importObject reads nothing else, importer.cpp:423-434)";
+    } else if (FILE *f = fopen(path, "rb")) {
+        char buf[1 << 16];
+        size_t n;
+        while ((n = fread(buf, 1, sizeof(buf), f)) > 0) text.append(buf, n);
+        fclose(f);
+        ok = loadObjHull(text.data(), text.size(), h);
+    } else {
+        h.error = "cannot open the file";
+    }
+    return handOverHull(h, ok, verts, num_verts, poly_words, num_poly_words, aabb, err, err_cap);
 }
 
 int32_t mdr_phys_launch_info(mdr_phys *p, int32_t info[6])

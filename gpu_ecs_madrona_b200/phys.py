@@ -76,6 +76,9 @@ def bind(lib):
     lib.mdr_phys_read_bvh.argtypes = [vp, vp, vp, vp]
     lib.mdr_phys_get_hull.argtypes = [vp, i32, vp, vp, vp, vp, vp]
     lib.mdr_version.restype = C.c_char_p
+    if hasattr(lib, "mdr_load_hull_obj"):
+        lib.mdr_load_hull_obj.argtypes = [C.c_char_p, C.c_int64, vp, vp, vp, vp, vp, C.c_char_p, i32]
+        lib.mdr_load_hull_obj_file.argtypes = [C.c_char_p, vp, vp, vp, vp, vp, C.c_char_p, i32]
     if hasattr(lib, "mdr_phys_pack_instances"):
         lib.mdr_phys_pack_instances.argtypes = [vp, vp, vp, vp]
         lib.mdr_phys_pack_views.argtypes = [vp, i32, vp, vp, vp, vp, vp]

@@ -198,6 +198,58 @@ def tumble(num_worlds, num_bodies=24, seed=1, num_substeps=4, max_contacts=512,
                  pos, rot, scale, vel, obj_ids, response, f, t, name=f"tumble-{num_bodies}")
 
 
+HULL_SHAPES = ("cube", "dodeca", "frustum", "hex_prism", "oct_frustum", "octa", "pyramid", "rock",
+               "tetra", "tri_prism")
+
+
+def hull_pile(num_worlds, num_bodies=20, seed=11, num_substeps=4, max_contacts=512, spread=1.5,
+              hull_dir=None, shapes=HULL_SHAPES):
+    """Non-cube convex hulls loaded from OBJ files through the asset pipeline (SURVEY 8f rank 4:
+    gpu_ecs_madrona_b200.assets -> mdr_load_hull_obj_file), dropped in a pile over a plane:
+    triangles to octagons as faces, 4 to 20 vertices, non-parallel faces, different masses and
+    friction, non-uniform scales. Exercises the general hull paths of the narrowphase (face
+    queries over unequal face counts, edge-edge over unequal edge counts, clipping of n-gons,
+    manifold reduction). Parity-test scene only; the OBJ fixtures live in tests/golden/hulls."""
+    import os
+    from . import assets
+    if hull_dir is None:
+        hull_dir = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))),
+                                "tests", "golden", "hulls")
+    objects = [assets.hull_object(os.path.join(hull_dir, n + ".obj"), inv_mass=0.5 + 0.25 * (k % 4),
+                                  mu=0.3 + 0.1 * (k % 3)) for k, n in enumerate(shapes)]
+    objects.append(plane_object())
+    H = len(shapes)
+    W, N = num_worlds, num_bodies + 1
+    seeds = (np.arange(W, dtype=np.uint64) * np.uint64(3935559000) + np.uint64(seed)) & np.uint64(0xFFFFFFFF)
+    u = _lcg_uniform(seeds, 16 * num_bodies).reshape(W, num_bodies, 16)
+    p = np.empty((W, num_bodies, 3))
+    p[..., 0] = (u[..., 0] * 2 - 1) * spread
+    p[..., 1] = (u[..., 1] * 2 - 1) * spread
+    p[..., 2] = 0.7 + u[..., 2] * 2.5
+    q = u[..., 3:7] * 2 - 1
+    q /= np.linalg.norm(q, axis=-1, keepdims=True)
+    v = np.concatenate([(u[..., 7:10] * 2 - 1) * 2.0, (u[..., 10:13] * 2 - 1) * 3.0], -1)
+    sc = 0.7 + 0.6 * u[..., 13:16]
+    pos = np.zeros((W, N, 3), np.float32)
+    rot = np.zeros((W, N, 4), np.float32)
+    rot[..., 0] = 1.0
+    scale = np.ones((W, N, 3), np.float32)
+    vel = np.zeros((W, N, 6), np.float32)
+    pos[:, 1:] = p.astype(np.float32)
+    rot[:, 1:] = q.astype(np.float32)
+    scale[:, 1:] = sc.astype(np.float32)
+    vel[:, 1:] = v.astype(np.float32)
+    obj_ids = np.zeros((W, N), np.int32)
+    # every world starts the cycle of shapes somewhere else
+    obj_ids[:, 1:] = (np.arange(num_bodies)[None] + np.arange(W)[:, None]) % H
+    obj_ids[:, 0] = H
+    response = np.zeros((W, N), np.uint32)
+    response[:, 0] = STATIC
+    z = np.zeros((W, N, 3), np.float32)
+    return Scene(W, N, num_substeps, max_contacts, 1.0 / 60.0, (0.0, 0.0, -9.8), objects,
+                 pos, rot, scale, vel, obj_ids, response, z, z.copy(), name=f"hull-pile-{num_bodies}")
+
+
 def jointed(num_worlds, seed=7, num_substeps=4, max_contacts=256, loose=6, hinges=False):
     """Joint constraints (SURVEY 8f rank 3; JointConstraint::setupFixed / setupHinge,
     include/madrona/physics.inl:151-191) next to contacts. Per world, over a static plane:

@@ -220,6 +220,21 @@ int32_t mdr_phys_read_bvh(mdr_phys *p, float *slot_boxes, float *leaf_aabbs, uin
  * 54-146): counts[4] = half-edges, edges, faces, vertices. */
 int32_t mdr_phys_get_hull(mdr_phys *p, int32_t obj, uint32_t *half_edges, uint32_t *edges,
                           uint32_t *polys, float *planes, int32_t *counts);
+/* Collision hull from a Wavefront OBJ: PhysicsLoader::loadHullFromDisk (src/physics/
+ * physics_assets.cpp:205-252) over imp::ImportedObject::importObject (src/common/importer.cpp:
+ * 35-437). Host only, no device needed. Produces what an mdr_object of type MDR_PRIM_HULL takes:
+ * vertices (merged by byte equality and numbered in order of first mention by the faces, as the
+ * reference's importer does), FastPolygonList words and the object-space AABB {min, max}.
+ * Two-call pattern: verts / poly_words may be NULL to query the counts; with arrays, *num_verts
+ * and *num_poly_words hold their capacities on entry (MDR_EOVERFLOW if too small) and the counts
+ * on return. Parse errors (everything the reference answers with FATAL / assert): MDR_EINVAL,
+ * with a message in err (may be NULL). `mdr_load_hull_obj_file` reads the file at `path`. */
+int32_t mdr_load_hull_obj(const char *obj_text, int64_t num_bytes, float *verts, int32_t *num_verts,
+                          uint32_t *poly_words, int32_t *num_poly_words, float aabb[6],
+                          char *err, int32_t err_cap);
+int32_t mdr_load_hull_obj_file(const char *path, float *verts, int32_t *num_verts,
+                               uint32_t *poly_words, int32_t *num_poly_words, float aabb[6],
+                               char *err, int32_t err_cap);
 /* Launch geometry chosen at creation: [0] blocks, [1] threads per block,
  * [2] dynamic shared memory bytes per block, [3] resident blocks per SM,
  * [4] threads per world, [5] worlds per block. */

@@ -45,8 +45,10 @@ def emu_lib():
         os.path.join(ROOT, "gpu_ecs_madrona_b200", "csrc", f)
         for f in os.listdir(os.path.join(ROOT, "gpu_ecs_madrona_b200", "csrc"))]
     if not os.path.exists(out) or any(os.path.getmtime(s) > os.path.getmtime(out) for s in srcs):
+        tmp = "%s.%d.tmp" % (out, os.getpid())
         subprocess.run(["g++", "-std=c++17", "-O2", "-march=x86-64-v3", "-ffp-contract=off", "-fPIC",
-                        "-shared", "-x", "c++", os.path.join(emu, "emu.cpp"), "-o", out], check=True)
+                        "-shared", "-x", "c++", os.path.join(emu, "emu.cpp"), "-o", tmp], check=True)
+        os.replace(tmp, out)    # atomic: concurrent xdist workers never load a half-written file
     return phys.bind(ctypes.CDLL(out))
 
 

@@ -25,12 +25,17 @@ CASES = {
     # joint constraints (Fixed) beside contacts; hinges only while the reference keeps them finite
     "jointed": (scenes.jointed, dict(num_worlds=6), (1, 10, 60), 3),
     "jointed_hinges": (scenes.jointed, dict(num_worlds=4, hinges=True), (1, 4, 7), 1),
+    # non-cube hulls loaded from OBJ files through the asset pipeline (tests/golden/hulls, make_asset_golden.py)
+    "hull_pile": (scenes.hull_pile, dict(num_worlds=8), (1, 10, 45), 2),
 }
 
 
 def main():
     orc.build("ref")
+    only = set(sys.argv[1:])          # `make_golden.py hull_pile`: (re)generate the named cases only
     for name, (fn, kw, snaps, pw) in CASES.items():
+        if only and name not in only:
+            continue
         sc = fn(**kw)
         ref = orc.Oracle(sc, "reference")
         # the probe step doubles as step 1

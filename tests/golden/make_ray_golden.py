@@ -22,7 +22,10 @@ SEED = 23
 
 def main():
     orc.build("ref")
+    only = set(sys.argv[1:])          # `make_ray_golden.py hull_pile`: the named cases only
     for name, (fn, kw, snaps, _) in CASES.items():
+        if only and name not in only:
+            continue
         sc = fn(**kw)
         ref = orc.Oracle(sc, "reference")
         rng = np.random.default_rng(SEED)
