@@ -254,6 +254,18 @@ def run_ours(args):
     e2e_value = world * W * e2e_steps / e2e_s
     finite = bool(np.isfinite(outs[0][1].view(np.float32)[:, :N_ROWS]).all())
 
+    # ---- episode statistics: the path's one (optional) collective, off the step -------------
+    # every rank's small statistics vector all-gathered over NCCL; not timed.
+    episode = None
+    try:
+        from gpu_ecs_madrona_b200 import sharding
+        es = sharding.EpisodeStats(every=args.steps, device=f"cuda:{local}")
+        es.launch(sharding.local_statistics(ex, args.warmup + args.steps + 3 + e2e_steps,
+                                            outs[0][1].view(np.float32)[:, :N_ROWS]))
+        episode = {k: float(v) for k, v in sharding.EpisodeStats.totals(es.result()).items()}
+    except Exception as e:      # statistics must never cost the bench line
+        episode = {"error": repr(e)}
+
     if rank == 0:
         peak, peak_src = measured_peak()
         A = algorithmic_bytes(P, C)
@@ -277,7 +289,8 @@ def run_ours(args):
                        "l2": "state tables (%.0f MB per GPU) exceed the 126 MB L2; no flush needed"
                              % (W * ex.row_stride() * 290 / 1e6),
                        "launch": info, "wall_ms_per_step": 1e3 * wall / args.steps,
-                       "parallelism": f"worlds sharded over {world} GPU(s), no per-step communication"},
+                       "parallelism": f"worlds sharded over {world} GPU(s), no per-step communication",
+                       "episode_stats_all_gather": episode},
             "gpu_launches": args.steps,
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d,
                     "d2h_bytes_per_step": d2h, "steps": e2e_steps, "finite": finite},
