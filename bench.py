@@ -219,6 +219,13 @@ def run_ours(args):
     value = world * W * args.steps / (dev_ms * 1e-3)
 
     # ---- end to end through the public API with host buffers ------------
+    # A fresh executor on the same scene, so that the end-to-end figure covers the SAME step range
+    # as `value` (warm-up steps, then K timed steps): the cost of a step depends on how far the cubes
+    # have fallen (falling 1.4 ms, settled 2.8 ms), and a region tacked on after the device-timed one
+    # would time a different workload.
+    ex.close()
+    ex = phys.PhysExecutor(sc, gpu_id=local, block_threads=args.threads,
+                           worlds_per_block=args.worlds_per_block, smem_contacts=args.smem_contacts)
     # per step: actions in (ExternalForce, ExternalTorque) from pinned host memory,
     # one step, observations out (Position, Rotation, Velocity) to pinned host memory.
     ins = [(c, ex.pinned(c)) for c in (phys.COL_EXT_FORCE, phys.COL_EXT_TORQUE)]
@@ -239,10 +246,10 @@ def run_ours(args):
                 ex.read_raw_async(c, a)
         ex.sync()
 
-    for _ in range(3):
+    for _ in range(args.warmup):
         e2e_step()
     barrier()
-    e2e_steps = max(10, args.steps // 4)
+    e2e_steps = args.steps
     t0 = time.perf_counter()
     for _ in range(e2e_steps):
         e2e_step()
@@ -260,7 +267,7 @@ def run_ours(args):
     try:
         from gpu_ecs_madrona_b200 import sharding
         es = sharding.EpisodeStats(every=args.steps, device=f"cuda:{local}")
-        es.launch(sharding.local_statistics(ex, args.warmup + args.steps + 3 + e2e_steps,
+        es.launch(sharding.local_statistics(ex, args.warmup + e2e_steps,
                                             outs[0][1].view(np.float32)[:, :N_ROWS]))
         episode = {k: float(v) for k, v in sharding.EpisodeStats.totals(es.result()).items()}
     except Exception as e:      # statistics must never cost the bench line
