@@ -200,3 +200,55 @@ def test_cuda_hull_tables_match_reference_fixture(cuda_lib):
         for t in ("half_edges", "edges", "polys"):
             assert np.array_equal(got[t], g[f"{name}_{t}"]), (name, t)
         assert np.array_equal(bits(got["planes"]), bits(g[f"{name}_planes"])), name
+
+
+def _capacity_scene(n_sides, num_worlds):
+    """A pile of n-gon prisms (2n vertices, n + 2 faces) and rocks over a plane."""
+    v, f = mag.prism(n_sides, r=0.55, h=0.35)
+    text = mag.obj_text(f"prism{n_sides}", v, f, 7, extras=False)
+    sc = scenes.hull_pile(num_worlds, num_bodies=10, seed=23, spread=1.0)
+    big = assets.hull_object(text, inv_mass=0.8, mu=0.4)
+    sc.objects = [big, sc.objects[7]] + [sc.objects[-1]]          # the prism, the rock, the plane
+    sc.obj_ids[:, 1:] = (np.arange(10)[None] + np.arange(num_worlds)[:, None]) % 2
+    sc.obj_ids[:, 0] = 2
+    return sc
+
+
+def test_hull_at_capacity_and_beyond(port_oracle, emu_lib):
+    """MDR_MAX_HULL_VERTS / FACES = 32 (one vertex / face per lane of the warp-per-pair SAT): a 32-vertex hull
+    steps bit for bit, a 34-vertex one is refused at creation (no silent truncation)."""
+    sc = _capacity_scene(16, 3)
+    assert len(sc.objects[0].verts) == 32 and len(sc.objects[0].polys) == 18
+    o = port_oracle.Oracle(sc, "port")
+    e = phys.PhysExecutor(sc, lib=emu_lib)
+    for st in range(25):
+        o.step()
+        e.run()
+        assert_state_equal(e.state(), o.state(), None, f"32-vertex hulls step {st}")
+    with pytest.raises(phys.MadronaError):
+        phys.PhysExecutor(_capacity_scene(17, 1), lib=emu_lib)
+
+
+def test_port_matches_compiled_reference_at_hull_capacity(port_oracle, ref_oracle):
+    sc = _capacity_scene(16, 6)
+    r = ref_oracle.Oracle(sc, "reference")
+    p = port_oracle.Oracle(sc, "port")
+    for st in range(30):
+        r.step()
+        p.step()
+        det = p.indeterminate() == 0
+        assert_state_equal(p.state(), r.state(), det, f"32-vertex hulls step {st}")
+    assert det.sum() >= 3
+
+
+@pytest.mark.gpu
+def test_cuda_hull_at_capacity_and_beyond(cuda_lib, port_oracle):
+    sc = _capacity_scene(16, 24)
+    o = port_oracle.Oracle(sc, "port")
+    e = phys.PhysExecutor(sc)
+    for st in range(40):
+        o.step(1, 8)
+        e.run()
+        assert_state_equal(e.state(), o.state(), None, f"32-vertex hulls step {st}")
+    with pytest.raises(phys.MadronaError):
+        phys.PhysExecutor(_capacity_scene(17, 1))
