@@ -158,10 +158,22 @@ __global__ void __launch_bounds__(1024) ecsExportOffsets(const EcsDev *__restric
     const int W = E->num_worlds, lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     if (threadIdx.x == 0) carry = 0;
     __syncthreads();
-    for (int base = 0; base < W; base += 1024) {
-        const int w = base + threadIdx.x;
-        const int64_t v = w < W ? counts[w] : 0;
-        int64_t incl = v;
+    // kPer consecutive worlds per thread: 8192 worlds are one pass of the block (three barriers in all)
+    constexpr int kPer = 8;
+    for (int base = 0; base < W; base += 1024 * kPer) {
+        const int w0 = base + (int)threadIdx.x * kPer;
+        int32_t v[kPer];
+        if (w0 + kPer <= W && (((uintptr_t)(counts + w0)) & 15u) == 0) {
+            const int4 a = *(const int4 *)(counts + w0), b = *(const int4 *)(counts + w0 + 4);
+            v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+        } else {
+#pragma unroll
+            for (int k = 0; k < kPer; k++) v[k] = w0 + k < W ? counts[w0 + k] : 0;
+        }
+        int64_t mine = 0;
+#pragma unroll
+        for (int k = 0; k < kPer; k++) mine += v[k];
+        int64_t incl = mine;
         for (int o = 1; o < 32; o <<= 1) {
             const int64_t t = __shfl_up_sync(kFull, incl, o);
             if (lane >= o) incl += t;
@@ -178,9 +190,14 @@ __global__ void __launch_bounds__(1024) ecsExportOffsets(const EcsDev *__restric
         }
         __syncthreads();
         const int64_t c = carry;
-        if (w < W) x.offsets[w] = c + warp_sums[wid] + incl - v;
+        int64_t run = c + warp_sums[wid] + incl - mine;
+#pragma unroll
+        for (int k = 0; k < kPer; k++) {
+            if (w0 + k < W) x.offsets[w0 + k] = run;
+            run += v[k];
+        }
         __syncthreads();
-        if (threadIdx.x == 1023) carry = c + warp_sums[wid] + incl;
+        if (threadIdx.x == 1023) carry = run;
         __syncthreads();
     }
     if (threadIdx.x == 0) x.offsets[W] = carry;
@@ -188,6 +205,18 @@ __global__ void __launch_bounds__(1024) ecsExportOffsets(const EcsDev *__restric
 
 // One warp per world; every non-fixed export: tile rows -> contiguous buffer
 // (to_buffer) or back (the reference's copy-in of actions before the step).
+// A world's share is a few KB at an offset that is only word-aligned: words,
+// four loads in flight per lane before the first store.
+__device__ __forceinline__ void copyWordsWarp(uint32_t *__restrict__ dst, const uint32_t *__restrict__ src, int total, int lane)
+{
+    int i = lane;
+    for (; i + 96 < total; i += 128) {
+        const uint32_t a = src[i], b = src[i + 32], c = src[i + 64], d = src[i + 96];
+        dst[i] = a; dst[i + 32] = b; dst[i + 64] = c; dst[i + 96] = d;
+    }
+    for (; i < total; i += 32) dst[i] = src[i];
+}
+
 __global__ void __launch_bounds__(256) ecsExportCopy(const EcsDev *__restrict__ E, int to_buffer)
 {
     const int w = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
@@ -201,9 +230,9 @@ __global__ void __launch_bounds__(256) ecsExportCopy(const EcsDev *__restrict__ 
         const int words = x.bytes >> 2;
         uint32_t *tile = (uint32_t *)(A.col[x.col] + (size_t)w * A.stride * x.bytes);
         uint32_t *buf = (uint32_t *)x.buffer + off * words;
-        const int64_t total = (int64_t)n * words;
-        if (to_buffer) for (int64_t i = lane; i < total; i += 32) buf[i] = tile[i];
-        else for (int64_t i = lane; i < total; i += 32) tile[i] = buf[i];
+        const int total = n * words;
+        if (to_buffer) copyWordsWarp(buf, tile, total, lane);
+        else copyWordsWarp(tile, buf, total, lane);
     }
 }
 
