@@ -20,6 +20,7 @@
 #include "ecs_apps.cuh"
 
 using namespace mdr::ecs;
+using namespace mdr;       // static_map.hpp
 
 #define REQ_CUDA(expr)                                                                   \
     do {                                                                                 \
@@ -236,6 +237,13 @@ __global__ void __launch_bounds__(256) ecsExportCopy(const EcsDev *__restrict__ 
     }
 }
 
+// Device-side column lookups through the uploaded maps (what Context::get<T>(Loc) does per call).
+__global__ void ecsColumnLookupKernel(const EcsDev *__restrict__ E, int arch, const int32_t *comps, int n, int32_t *out)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) out[i] = comps[i] < 0 ? -1 : E->col_maps[arch].lookup((uint32_t)comps[i]);
+}
+
 // Replicates the id nodes every world starts with (singleton entities).
 __global__ void ecsBroadcastNodes(IdNode *dst, int32_t id_cap, const IdNode *src, int32_t n, int32_t num_worlds)
 {
@@ -261,6 +269,7 @@ struct mdr_ecs {
     std::vector<HostExport> exports;    // by slot
     bool built = false;
     EcsDev host {};                     // host copy of the device descriptor
+    std::vector<ColumnMapDev> col_maps; // per archetype, built at mdr_ecs_build
     EcsDev *dev = nullptr;
     std::vector<void *> allocs;
     cudaStream_t stream = nullptr;
@@ -292,6 +301,16 @@ int colOf(const HostArchetype &a, int32_t comp)
     for (size_t i = 0; i < a.comps.size(); i++)
         if (a.comps[i] == comp) return (int)i + 1;
     return -1;
+}
+
+// The archetype's column map: Entity (component 0) -> column 0, user components -> 1.. in registration order
+// (the lookupInputs of StateManager::registerArchetype, src/core/state.cpp:383-404).
+bool buildArchColumnMap(ColumnMapDev &m, const HostArchetype &a)
+{
+    std::vector<uint32_t> keys { 0u }, vals { 0u };
+    for (size_t i = 0; i < a.comps.size(); i++) { keys.push_back((uint32_t)a.comps[i]); vals.push_back((uint32_t)i + 1); }
+    memset(&m, 0, sizeof(m));
+    return buildColumnMap(m, keys.data(), vals.data(), (uint32_t)keys.size());
 }
 
 bool depsOk(const mdr_ecs *e, const int32_t *deps, int32_t ndeps)
@@ -486,6 +505,11 @@ int32_t mdr_ecs_build(mdr_ecs *e)
     H.app = e->cfg.app;
     int64_t total_rows = 0;
     int num_singletons = 0;
+    e->col_maps.resize(H.num_arch);
+    for (int a = 0; a < H.num_arch; a++)
+        if (!buildArchColumnMap(e->col_maps[a], e->archs[a])) return MDR_ECAPACITY;   // the reference FATALs
+    H.col_maps = e->dalloc<ColumnMapDev>((size_t)H.num_arch, false);
+    REQ_CUDA(cudaMemcpy(H.col_maps, e->col_maps.data(), sizeof(ColumnMapDev) * (size_t)H.num_arch, cudaMemcpyHostToDevice));
     for (int a = 0; a < H.num_arch; a++) {
         const HostArchetype &ha = e->archs[a];
         ArchDev &A = H.arch[a];
@@ -569,13 +593,15 @@ int32_t mdr_ecs_build(mdr_ecs *e)
         }
         if (hn.kind != kNodeParallelFor) continue;
         for (int a = 0; a < H.num_arch; a++) {
+            // StateManager::makeQuery (src/core/state.cpp:305-356): columnLookup.exists, then columnLookup[]
+            const ColumnMapDev &cm = e->col_maps[a];
             bool has = true;
-            for (int32_t c : hn.comps) has = has && colOf(e->archs[a], c) >= 0;
+            for (int32_t c : hn.comps) has = has && cm.exists((uint32_t)c);
             if (!has) continue;
             if (N.num_match >= kMaxMatch) return MDR_ECAPACITY;
             MatchDev &M = N.match[N.num_match++];
             M.arch = a;
-            for (size_t k = 0; k < hn.comps.size(); k++) M.col[k] = colOf(e->archs[a], hn.comps[k]);
+            for (size_t k = 0; k < hn.comps.size(); k++) M.col[k] = (int32_t)cm.at((uint32_t)hn.comps[k]);
         }
     }
     H.num_exports = (int32_t)e->exports.size();
@@ -823,6 +849,52 @@ int32_t mdr_ecs_launches_per_step(mdr_ecs *e)
     for (int s = 0; s < e->host.num_exports; s++)
         if (!e->host.exports[s].fixed) return 4;
     return 1;
+}
+
+int32_t mdr_static_map_build(const uint32_t *keys, const uint32_t *values, int32_t n,
+                             uint32_t *key_storage, uint32_t *value_storage)
+{
+    if (!keys || !values || !key_storage || !value_storage || n < 0) return MDR_EINVAL;
+    if ((uint32_t)n > kMapMaxKeys) return MDR_ECAPACITY;
+    for (int i = 0; i < n; i++) if (keys[i] == kMapInvalidKey) return MDR_EINVAL;
+    ColumnMapDev m;
+    memset(&m, 0, sizeof(m));
+    if (!buildColumnMap(m, keys, values, (uint32_t)n)) return MDR_ECAPACITY;
+    memcpy(key_storage, m.keys, sizeof(m.keys));
+    memcpy(value_storage, m.values, sizeof(m.values));
+    return MDR_OK;
+}
+
+int32_t mdr_static_map_lookup(const uint32_t *key_storage, const uint32_t *value_storage, uint32_t key)
+{
+    if (!key_storage || !value_storage) return MDR_EINVAL;
+    const uint32_t idx = staticMapIndex(key, key_storage[kMapShiftIdx], key_storage[kMapConstIdx]);
+    if (idx >= kMapSlots || key_storage[idx] != key) return -1;
+    return (int32_t)value_storage[idx];
+}
+
+int32_t mdr_ecs_column_map(mdr_ecs *e, int32_t arch, uint32_t *key_storage, uint32_t *value_storage)
+{
+    if (!e || !e->built || arch < 0 || arch >= (int)e->col_maps.size() || !key_storage || !value_storage) return MDR_EINVAL;
+    memcpy(key_storage, e->col_maps[arch].keys, sizeof(uint32_t) * kMapSlots);
+    memcpy(value_storage, e->col_maps[arch].values, sizeof(uint32_t) * kMapSlots);
+    return MDR_OK;
+}
+
+int32_t mdr_ecs_lookup_columns(mdr_ecs *e, int32_t arch, const int32_t *comp_ids, int32_t n, int32_t *out_cols)
+{
+    if (!e || !e->built || arch < 0 || arch >= e->host.num_arch || !comp_ids || !out_cols || n < 0) return MDR_EINVAL;
+    if (n == 0) return MDR_OK;
+    REQ_CUDA(cudaSetDevice(e->cfg.gpu_id));
+    int32_t *d = nullptr;
+    REQ_CUDA(cudaMalloc(&d, 8 * (size_t)n));
+    REQ_CUDA(cudaMemcpy(d, comp_ids, 4 * (size_t)n, cudaMemcpyHostToDevice));
+    ecsColumnLookupKernel<<<(n + 127) / 128, 128, 0, e->stream>>>(e->dev, arch, d, n, d + n);
+    REQ_CUDA(cudaGetLastError());
+    REQ_CUDA(cudaStreamSynchronize(e->stream));
+    REQ_CUDA(cudaMemcpy(out_cols, d + n, 4 * (size_t)n, cudaMemcpyDeviceToHost));
+    REQ_CUDA(cudaFree(d));
+    return MDR_OK;
 }
 
 void *mdr_ecs_get_exported(mdr_ecs *e, int32_t slot)

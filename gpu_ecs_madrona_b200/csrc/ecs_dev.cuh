@@ -18,6 +18,7 @@
 #include <utility>
 
 #include "../../include/madrona_b200_apps.h"
+#include "static_map.hpp"
 
 namespace mdr {
 namespace ecs {
@@ -73,6 +74,7 @@ struct EcsDev {
     Entity *handles;                // script app: [num_worlds][max_handles]
     int32_t *num_handles;           // [num_worlds]
     int32_t *error;                 // one word of kErr* flags
+    ColumnMapDev *col_maps;         // [num_arch]: component id -> column (ColumnMap columnLookup, state.hpp:245-293)
 };
 
 // Per-warp shared memory: the world's row counts and id caches live here for the
@@ -242,6 +244,15 @@ struct Context {
     }
     // Context::getDirect (include/madrona/state.inl:292-303)
     template <typename T> __device__ __forceinline__ T &getDirect(int col, Loc l) const { return column<T>((int)l.archetype, col)[l.row]; }
+    // Context::get<T>(Loc) (state.inl:240-262): the component's column in the entity's archetype through the
+    // archetype's perfect-hash column map; nullptr when the archetype has no such component (ResultRef).
+    __device__ __forceinline__ int32_t columnOf(int arch, uint32_t comp_id) const { return E->col_maps[arch].lookup(comp_id); }
+    template <typename T> __device__ __forceinline__ T *get(Loc l, uint32_t comp_id) const
+    {
+        if (l.archetype == kNoArch) return nullptr;
+        const int32_t col = columnOf((int)l.archetype, comp_id);
+        return col < 0 ? nullptr : &column<T>((int)l.archetype, col)[l.row];
+    }
     // Context::getSingleton (state.inl:205-215): column 1, row 0 of the singleton archetype
     template <typename T> __device__ __forceinline__ T &getSingleton(int arch) const { return column<T>(arch, 1)[0]; }
 

@@ -66,6 +66,10 @@ def _lib():
         lib.mdr_ecs_step_ms.argtypes = [vp, vp]
         lib.mdr_ecs_step_ms.restype = C.c_float
         lib.mdr_ecs_get_exported.argtypes = [vp, i32]
+        lib.mdr_static_map_build.argtypes = [vp, vp, i32, vp, vp]
+        lib.mdr_static_map_lookup.argtypes = [vp, vp, C.c_uint32]
+        lib.mdr_ecs_column_map.argtypes = [vp, i32, vp, vp]
+        lib.mdr_ecs_lookup_columns.argtypes = [vp, i32, vp, i32, vp]
         lib.mdr_ecs_get_exported.restype = vp
         lib.mdr_ecs_export_rows.argtypes = [vp, i32]
         lib.mdr_ecs_export_rows.restype = C.c_int64
@@ -220,6 +224,21 @@ class EcsRegistry:
     def launches_per_step(self):
         return self.lib.mdr_ecs_launches_per_step(self.h)
 
+    def column_map(self, arch):
+        """The archetype's perfect-hash column map (ColumnMap columnLookup of the reference): (keys[128], values[128])."""
+        k, v = np.zeros(128, np.uint32), np.zeros(128, np.uint32)
+        _check(self.lib.mdr_ecs_column_map(self.h, arch, k.ctypes.data, v.ctypes.data), "mdr_ecs_column_map")
+        return k, v
+
+    def lookup_columns(self, arch, comp_ids):
+        """Column index of every component id in `arch` (-1: absent), resolved ON THE DEVICE through the
+        uploaded map, as Context::get<T>(Loc) does."""
+        ids = np.ascontiguousarray(comp_ids, np.int32)
+        out = np.zeros(len(ids), np.int32)
+        _check(self.lib.mdr_ecs_lookup_columns(self.h, arch, ids.ctypes.data, len(ids), out.ctypes.data),
+               "mdr_ecs_lookup_columns")
+        return out
+
     def get_exported(self, slot):
         """(device pointer, rows, bytes per row) of an exported column: getExported(slot)."""
         return (self.lib.mdr_ecs_get_exported(self.h, slot), self.lib.mdr_ecs_export_rows(self.h, slot),
@@ -269,3 +288,20 @@ class EcsExecutor(EcsRegistry):
         """{(arch, col): [W, stride, bytes]} of every column, one device copy each."""
         return {(a, c): self.read_column_all(a, c) for a in range(self.num_archetypes)
                 for c in range(len(self.col_bytes[a]))}
+
+
+def static_map_build(keys, values, lib=None):
+    """StaticIntegerMap<128>(keys, values) of the reference: (key_storage[128], value_storage[128]).
+    Host code of the library (csrc/static_map.hpp); raises where the reference FATALs."""
+    lib = lib or _lib()
+    k = np.ascontiguousarray(keys, np.uint32)
+    v = np.ascontiguousarray(values, np.uint32)
+    ks, vs = np.zeros(128, np.uint32), np.zeros(128, np.uint32)
+    _check(lib.mdr_static_map_build(k.ctypes.data, v.ctypes.data, len(k), ks.ctypes.data, vs.ctypes.data),
+           "mdr_static_map_build")
+    return ks, vs
+
+
+def static_map_lookup(key_storage, value_storage, key, lib=None):
+    lib = lib or _lib()
+    return int(lib.mdr_static_map_lookup(key_storage.ctypes.data, value_storage.ctypes.data, int(key)))

@@ -321,6 +321,19 @@ int32_t mdr_ecs_sync(mdr_ecs *e);
 void *mdr_ecs_stream(mdr_ecs *e);
 float mdr_ecs_step_ms(mdr_ecs *e, int32_t *steps);
 int32_t mdr_ecs_launches_per_step(mdr_ecs *e);
+/* Archetype column map, SURVEY 8 row a2: StaticIntegerMap<128> (include/madrona/hashmap.hpp:26-58, hashmap.inl:
+ * 14-74, src/common/hashmap.cpp:17-116), kept per archetype as `ColumnMap columnLookup` (state.hpp:245-293).
+ * `mdr_static_map_build` (host) fills both 128-word storage arrays exactly as the reference's constructor does
+ * (perfect multiplicative hash, shift and multiplier in slots 14 / 15 of both); MDR_ECAPACITY where the reference
+ * FATALs (no perfect hash within 128 slots, or more than 126 keys), MDR_EINVAL for key 0xffffffff.
+ * `mdr_static_map_lookup` = lookup(): the value, or -1. `mdr_ecs_column_map` hands out the map built for archetype
+ * `arch` at mdr_ecs_build (component id -> column; Entity = component 0 -> column 0); `mdr_ecs_lookup_columns`
+ * resolves component ids ON THE DEVICE through the uploaded map, as Context::get<T>(Loc) does (state.inl:240-262). */
+int32_t mdr_static_map_build(const uint32_t *keys, const uint32_t *values, int32_t n,
+                             uint32_t *key_storage, uint32_t *value_storage);
+int32_t mdr_static_map_lookup(const uint32_t *key_storage, const uint32_t *value_storage, uint32_t key);
+int32_t mdr_ecs_column_map(mdr_ecs *e, int32_t arch, uint32_t *key_storage, uint32_t *value_storage);
+int32_t mdr_ecs_lookup_columns(mdr_ecs *e, int32_t arch, const int32_t *comp_ids, int32_t n, int32_t *out_cols);
 /* getExported(slot): device pointer; staged exports hold mdr_ecs_export_rows rows
  * (world-major concatenation), fixed ones alias the table. */
 void *mdr_ecs_get_exported(mdr_ecs *e, int32_t slot);

@@ -39,6 +39,9 @@ void eorc_read_idmap(void *h, int32_t world, int32_t *a, int32_t *b, uint32_t *g
 /* Exported column `slot`: the world-major concatenation of StateManager::
  * copyOutExportedColumns (src/core/state.cpp:516-563). Returns bytes. */
 int64_t eorc_export(void *h, int32_t slot, void *out, int64_t max_bytes);
+/* Reference checker only: StaticIntegerMap<128>(keys, values) -> both storage arrays [128]. */
+void eorc_static_map_build(const uint32_t *keys, const uint32_t *values, uint32_t n,
+                           uint32_t *out_keys, uint32_t *out_values);
 
 #ifdef __cplusplus
 }

@@ -29,6 +29,7 @@
 #include <vector>
 
 #include <madrona/taskgraph.hpp>
+#include <madrona/hashmap.hpp>
 #include <madrona/custom_context.hpp>
 #include <madrona/components.hpp>
 
@@ -481,6 +482,19 @@ int64_t eorc_export(void *hp, int32_t slot, void *out, int64_t max_bytes)
         off += nb;
     }
     return off;
+}
+
+// The reference's own StaticIntegerMap<128> (include/madrona/hashmap.hpp, src/common/hashmap.cpp:17-116):
+// builds the map and hands back both storage arrays, for pinning csrc/static_map.hpp. The caller keeps to
+// key sets the reference can hash (it FATALs otherwise).
+void eorc_static_map_build(const uint32_t *keys, const uint32_t *values, uint32_t n,
+                           uint32_t *out_keys /*[128]*/, uint32_t *out_values /*[128]*/)
+{
+    std::vector<IntegerMapPair> in(n);
+    for (uint32_t i = 0; i < n; i++) in[i] = IntegerMapPair { keys[i], values[i] };
+    StaticIntegerMap<128> m(in.data(), n);
+    memcpy(out_keys, m.keys_.data(), 4 * 128);
+    memcpy(out_values, m.values_.data(), 4 * 128);
 }
 
 }  // extern "C"
