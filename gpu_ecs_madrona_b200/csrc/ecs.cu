@@ -149,6 +149,7 @@ ecsScriptKernel(const EcsDev *__restrict__ E, const mdr_script_op *__restrict__ 
 // StateManager::copyOutExportedColumns (src/core/state.cpp:516-563) /
 // madronaMWGPUExportBlockSums + ExportCopyOut (src/mw/device/consts.cpp:137-273):
 // offsets[w] = rows of the export's archetype in worlds < w. One block per slot.
+template <int kPer>
 __global__ void __launch_bounds__(1024) ecsExportOffsets(const EcsDev *__restrict__ E)
 {
     __shared__ int64_t warp_sums[32];
@@ -159,14 +160,16 @@ __global__ void __launch_bounds__(1024) ecsExportOffsets(const EcsDev *__restric
     const int W = E->num_worlds, lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     if (threadIdx.x == 0) carry = 0;
     __syncthreads();
-    // kPer consecutive worlds per thread: 8192 worlds are one pass of the block (three barriers in all)
-    constexpr int kPer = 8;
+    // kPer consecutive worlds per thread: with 8, 8192 worlds are one pass of the block (three barriers in
+    // all); up to 1024 worlds one world per thread is the shorter chain (launchExportOffsets picks).
     for (int base = 0; base < W; base += 1024 * kPer) {
         const int w0 = base + (int)threadIdx.x * kPer;
         int32_t v[kPer];
-        if (w0 + kPer <= W && (((uintptr_t)(counts + w0)) & 15u) == 0) {
+        if (kPer == 8 && w0 + kPer <= W && (((uintptr_t)(counts + w0)) & 15u) == 0) {
             const int4 a = *(const int4 *)(counts + w0), b = *(const int4 *)(counts + w0 + 4);
-            v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+            const int32_t t[8] = { a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w };
+#pragma unroll
+            for (int k = 0; k < kPer; k++) v[k] = t[k];
         } else {
 #pragma unroll
             for (int k = 0; k < kPer; k++) v[k] = w0 + k < W ? counts[w0 + k] : 0;
@@ -202,6 +205,12 @@ __global__ void __launch_bounds__(1024) ecsExportOffsets(const EcsDev *__restric
         __syncthreads();
     }
     if (threadIdx.x == 0) x.offsets[W] = carry;
+}
+
+static void launchExportOffsets(const EcsDev *dev, int num_exports, int num_worlds, cudaStream_t stream)
+{
+    if (num_worlds <= 1024) ecsExportOffsets<1><<<num_exports, 1024, 0, stream>>>(dev);
+    else ecsExportOffsets<8><<<num_exports, 1024, 0, stream>>>(dev);
 }
 
 // One warp per world; every non-fixed export: tile rows -> contiguous buffer
@@ -338,7 +347,7 @@ void closeTiming(mdr_ecs *e)
 void refreshExports(mdr_ecs *e)
 {
     if (e->host.num_exports > 0) {
-        ecsExportOffsets<<<e->host.num_exports, 1024, 0, e->stream>>>(e->dev);
+        launchExportOffsets(e->dev, e->host.num_exports, e->host.num_worlds, e->stream);
         ecsExportCopy<<<(e->host.num_worlds + 7) / 8, 256, 0, e->stream>>>(e->dev, 1);
         REQ_CUDA(cudaGetLastError());
     }
@@ -797,7 +806,7 @@ int32_t mdr_ecs_step_async(mdr_ecs *e, int32_t num_steps)
         if (staged) ecsExportCopy<<<(e->host.num_worlds + 7) / 8, 256, 0, e->stream>>>(e->dev, 0);
         e->step_kernel<<<e->blocks, 32 * kWarpsPerBlock, 0, e->stream>>>(e->dev);
         if (staged) {
-            ecsExportOffsets<<<e->host.num_exports, 1024, 0, e->stream>>>(e->dev);
+            launchExportOffsets(e->dev, e->host.num_exports, e->host.num_worlds, e->stream);
             ecsExportCopy<<<(e->host.num_worlds + 7) / 8, 256, 0, e->stream>>>(e->dev, 1);
         }
         REQ_CUDA(cudaStreamEndCapture(e->stream, &g));
