@@ -209,12 +209,12 @@ def hull_pile(num_worlds, num_bodies=20, seed=11, num_substeps=4, max_contacts=5
     triangles to octagons as faces, 4 to 20 vertices, non-parallel faces, different masses and
     friction, non-uniform scales. Exercises the general hull paths of the narrowphase (face
     queries over unequal face counts, edge-edge over unequal edge counts, clipping of n-gons,
-    manifold reduction). Parity-test scene only; the OBJ fixtures live in tests/golden/hulls."""
+    manifold reduction). Parity-test scene only; the OBJ files live in gpu_ecs_madrona_b200/hulls
+    (written by tests/golden/make_asset_golden.py)."""
     import os
     from . import assets
     if hull_dir is None:
-        hull_dir = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))),
-                                "tests", "golden", "hulls")
+        hull_dir = os.path.join(os.path.dirname(os.path.abspath(__file__)), "hulls")
     objects = [assets.hull_object(os.path.join(hull_dir, n + ".obj"), inv_mass=0.5 + 0.25 * (k % 4),
                                   mu=0.3 + 0.1 * (k % 3)) for k, n in enumerate(shapes)]
     objects.append(plane_object())

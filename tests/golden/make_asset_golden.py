@@ -1,6 +1,7 @@
 """Generates the collision-hull fixtures of SURVEY §8f rank 4:
 
-  tests/golden/hulls/*.obj     convex test shapes as Wavefront OBJ (written here, committed)
+  gpu_ecs_madrona_b200/hulls/*.obj  convex test shapes as Wavefront OBJ (written here, committed; package data,
+                               scenes.hull_pile loads them)
   tests/golden/assets_ref.npz  what the UNMODIFIED reference makes of each file:
                                PhysicsLoader::loadHullFromDisk (src/physics/physics_assets.cpp:205-252)
                                through oracle/_ref/libmadrona_assets_ref.so (oracle/Makefile, `assets_ref`)
@@ -21,7 +22,7 @@ import numpy as np
 ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path.insert(0, ROOT)
 HERE = os.path.dirname(os.path.abspath(__file__))
-HULLS = os.path.join(HERE, "hulls")
+HULLS = os.path.join(ROOT, "gpu_ecs_madrona_b200", "hulls")
 REF_LIB = os.path.join(ROOT, "oracle", "_ref", "libmadrona_assets_ref.so")
 
 TRIANGULAR = ("tetra", "octa", "rock")

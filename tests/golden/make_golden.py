@@ -25,7 +25,7 @@ CASES = {
     # joint constraints (Fixed) beside contacts; hinges only while the reference keeps them finite
     "jointed": (scenes.jointed, dict(num_worlds=6), (1, 10, 60), 3),
     "jointed_hinges": (scenes.jointed, dict(num_worlds=4, hinges=True), (1, 4, 7), 1),
-    # non-cube hulls loaded from OBJ files through the asset pipeline (tests/golden/hulls, make_asset_golden.py)
+    # non-cube hulls loaded from OBJ files through the asset pipeline (gpu_ecs_madrona_b200/hulls, make_asset_golden.py)
     "hull_pile": (scenes.hull_pile, dict(num_worlds=8), (1, 10, 45), 2),
 }
 
