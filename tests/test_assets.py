@@ -252,3 +252,41 @@ def test_cuda_hull_at_capacity_and_beyond(cuda_lib, port_oracle):
         assert_state_equal(e.state(), o.state(), None, f"32-vertex hulls step {st}")
     with pytest.raises(phys.MadronaError):
         phys.PhysExecutor(_capacity_scene(17, 1))
+
+
+def test_obj_loader_dialect_matches_compiled_reference(host_lib, tmp_path):
+    """Things real OBJ files carry that the reader must take exactly as the reference's does: other statement
+    kinds (g, usemtl, mtllib, vp, l), a fourth coordinate / vertex colours on `v` lines, `vn` / `vt` lines
+    nobody refers to, trailing blanks, blank lines, a file without a final newline, an `o` line first."""
+    if not os.path.exists(mag.REF_LIB):
+        pytest.skip("compiled reference asset loader not available on this machine")
+    v, f, _ = mag.shapes()["frustum"]
+    base = mag.obj_text("frustum", v, f, 77, extras=True).splitlines()
+    variants = {}
+    lines = []
+    for ln in base:
+        if ln.startswith("v "):
+            ln = ln + " 1.0 0.25 0.5 0.75"             # w + colour
+        if ln.startswith("f "):
+            ln = ln + "   "                             # trailing blanks
+        lines.append(ln)
+        if ln.startswith("o "):
+            lines += ["mtllib none.mtl", "g group0", "usemtl stone", "", "vp 0.1 0.2", "l 1 2"]
+    lines.insert(5, "vn 0 0 1")
+    lines.insert(6, "vt 0.5 0.5")
+    variants["statements"] = "\n".join(lines) + "\n"
+    variants["no_final_newline"] = "\n".join(base)
+    variants["uv_only_corners"] = "\n".join(
+        ("f " + " ".join(c + "/1" for c in ln.split()[1:])) if ln.startswith("f ") else ln for ln in base
+    ).replace("s off", "vt 0.25 0.75\ns off") + "\n"
+    variants["normal_only_corners"] = "\n".join(
+        ("f " + " ".join(c + "//1" for c in ln.split()[1:])) if ln.startswith("f ") else ln for ln in base
+    ).replace("s off", "vn 0 1 0\ns off") + "\n"
+    for name, text in variants.items():
+        path = tmp_path / (name + ".obj")
+        path.write_bytes(text.encode())
+        want = mag.ref_load(str(path))
+        verts, polys, lo, hi = assets.load_hull_obj(str(path), host_lib)
+        assert np.array_equal(bits(verts), bits(want["verts"])), name
+        assert polys == polys_of(want["half_edges"], want["polys"]), name
+        assert np.array_equal(bits(np.array(lo + hi, np.float32)), bits(want["aabb"])), name
