@@ -16,7 +16,11 @@ import os
 import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libmadrona_b200.so")
+# MDR_LIB selects another build of the same library (e.g. the FMA-contracted
+# tolerance build libmadrona_b200_fma.so); the default is the bit-exact build.
+LIB_PATH = os.environ.get("MDR_LIB") or os.path.join(HERE, "libmadrona_b200.so")
+if not os.path.isabs(LIB_PATH):
+    LIB_PATH = os.path.join(HERE, LIB_PATH)
 
 COL_BYTES = [8, 12, 16, 12, 24, 4, 4, 28, 28, 24, 12, 12, 4]
 (COL_ENTITY, COL_POSITION, COL_ROTATION, COL_SCALE, COL_VELOCITY, COL_OBJECT_ID,
