@@ -99,11 +99,14 @@ MDR_HD void stepWorld(const BlockCtx &c, WorldView &v, const StepParams &p, int 
     v.n = v.active ? p.t.row_count[w] : 0;
     if (v.n > v.np) v.n = v.np;
     c.syncBlock();                           // world slots re-align once per step
+    MDR_PHASE_BEGIN
     if (c.tid() == 0) *group_level = 0;     // every slot writes the same value
     loadWorld(c, v, p, w);
     c.sync();
+    MDR_PHASE(0);
     updateLeavesAndRefit(c, v, p);
     c.sync();
+    MDR_PHASE(1);
     findPairs(c, v, p, w);
     if (c.lockstep() && c.tid() == 0 && v.misc[1] > 0) {
 #if defined(__CUDA_ARCH__)
@@ -113,26 +116,34 @@ MDR_HD void stepWorld(const BlockCtx &c, WorldView &v, const StepParams &p, int 
 #endif
     }
     c.sync();
+    MDR_PHASE(2);
     const int max_level = c.lockstep() ? *group_level : v.misc[1];
     const bool probing = v.active && p.probe.world == w;
     for (int sub = 0; sub < p.substeps; sub++) {
         substepBodies(c, v, p, w, sub);
         worldBoxes(c, v, p, sub);
         c.sync();
+        MDR_PHASE(3);
         const int np = v.misc[0];
         for (int i = c.tid(); i < np; i += c.nthreads()) narrowphasePair(v, p, i, probing, sub);
         c.sync();
+        MDR_PHASE(4);
 #if defined(__CUDA_ARCH__)
         satQueueWarp(c, v, p, probing, sub);
         c.sync();
+        MDR_PHASE(5);
 #endif
 #if defined(__CUDA_ARCH__)
         if (bs && buildLevelLists(c, v, bs, slot, max_level)) {
+            MDR_PHASE(6);
             solveDense<false>(bs, p, max_level);
+            MDR_PHASE(7);
             if (kJoints) solveJoints(c, v, p, w);
             setVelocities(c, v, p, sub);
             c.sync();
+            MDR_PHASE(8);
             solveDense<true>(bs, p, max_level);
+            MDR_PHASE(9);
             continue;
         }
 #endif
@@ -156,10 +167,13 @@ MDR_HD void stepWorld(const BlockCtx &c, WorldView &v, const StepParams &p, int 
         p.world_contacts[w] = nc;
     }
 #endif
+    MDR_PHASE(10);
     updateLeavesAndRefitGlobal(c, v, p, w);
     c.sync();
+    MDR_PHASE(11);
     storeWorld(c, v, p.t, w);
     c.sync();
+    MDR_PHASE(12);
 }
 
 // ------------------------------------------------------------ BVH rebuild ---

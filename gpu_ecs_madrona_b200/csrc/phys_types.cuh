@@ -123,6 +123,10 @@ struct StepParams {
     const JointDev *joints;       // [W][joint_stride]; joint_stride 0: the batch has no joints
     const int32_t *joint_count;   // [W]
     int32_t joint_stride;
+#ifdef MDR_PHASE_CLOCKS
+    // profiling builds only (profiles/exp): clock64 ticks per phase of stepWorld, summed over blocks
+    unsigned long long *phase_clocks;
+#endif
 };
 
 enum { MDR_ERR_PAIR_OVERFLOW = 1 };

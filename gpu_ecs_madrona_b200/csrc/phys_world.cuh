@@ -104,6 +104,25 @@ struct WorldView {
 constexpr uint32_t PAIR_SAT = 1u << 31;
 MDR_HD int pairLevel(uint32_t word) { return (int)((word >> 20) & 0x7ffu); }
 
+MDR_HD int popcount32(uint32_t m)
+{
+#if defined(__CUDA_ARCH__)
+    return __popc(m);
+#else
+    return __builtin_popcount(m);
+#endif
+}
+// Position of the j-th (0-based) set bit of m; m has more than j set bits.
+MDR_HD int nthSetBit(uint32_t m, int j)
+{
+#if defined(__CUDA_ARCH__)
+    return (int)__fns(m, 0u, j + 1);
+#else
+    for (; j > 0; j--) m &= m - 1;
+    return __builtin_ctz(m);
+#endif
+}
+
 MDR_HD size_t alignUp(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
 // Carves the view out of one SMEM (or host) buffer; returns bytes used. With
@@ -216,6 +235,22 @@ MDR_HD bool staticStable(V3 x, Q4 q)
     for (int i = 0; i < 7; i++) neg_zero = neg_zero || (f[i] == 0.f && signbit(f[i]));
     return !neg_zero && qBitsEqual(qnormalize(q), q);
 }
+
+// Profiling builds (profiles/exp, -DMDR_PHASE_CLOCKS): clock64 between block barriers, per phase.
+#if defined(MDR_PHASE_CLOCKS) && defined(__CUDA_ARCH__)
+#define MDR_PHASE(k)                                                                     \
+    do {                                                                                 \
+        if (threadIdx.x == 0) {                                                          \
+            const long long now_ = clock64();                                            \
+            atomicAdd(&p.phase_clocks[k], (unsigned long long)(now_ - phase_last_));     \
+            phase_last_ = now_;                                                          \
+        }                                                                                \
+    } while (0)
+#define MDR_PHASE_BEGIN long long phase_last_ = clock64();
+#else
+#define MDR_PHASE(k) do { } while (0)
+#define MDR_PHASE_BEGIN
+#endif
 
 // ------------------------------------------------------------- load/store ---
 MDR_HD void loadWorld(const BlockCtx &c, WorldView &v, const StepParams &p, int w)
@@ -356,11 +391,16 @@ MDR_HD void raiseError(const StepParams &p, int bit)
 
 // One rank-ordered broadphase entry against row a's current box.
 struct alignas(16) RankEntry { float lx, ly, lz; int32_t ent; float hx, hy, hz; uint32_t info; };
+// Branch-free (no short circuit): tests of consecutive ranks are independent instruction
+// streams the scheduler can overlap.
 MDR_HD bool pairTest(const float *rbox, int r, const Box &q, int a_id, bool a_static)
 {
     const RankEntry e = *reinterpret_cast<const RankEntry *>(rbox + 8 * r);
-    return a_id < e.ent && !(a_static && (e.info >> 15)) &&
-           q.lo.x < e.hx && e.lx < q.hi.x && q.lo.y < e.hy && e.ly < q.hi.y && q.lo.z < e.hz && e.lz < q.hi.z;
+    const int ids = (int)(a_id < e.ent) & (int)!(a_static & (bool)(e.info >> 15));
+    const int x = (int)(q.lo.x < e.hx) & (int)(e.lx < q.hi.x);
+    const int y = (int)(q.lo.y < e.hy) & (int)(e.ly < q.hi.y);
+    const int z = (int)(q.lo.z < e.hz) & (int)(e.lz < q.hi.z);
+    return (ids & x & y & z) != 0;
 }
 
 // findOverlappingEntry + BVH::findOverlaps (broadphase.cpp:897-932,
@@ -372,6 +412,7 @@ MDR_HD void findPairs(const BlockCtx &c, WorldView &v, const StepParams &p, int 
 {
     const int n = v.n;
     const size_t r0 = (size_t)w * p.t.stride;
+    MDR_PHASE_BEGIN
     // Rows are taken one per thread; the rows left over after the last full pass
     // (row 64 of 65 with 64 threads) are swept by the whole group instead, one rank
     // per thread, so that no thread walks all ranks alone while the others wait.
@@ -384,12 +425,19 @@ MDR_HD void findPairs(const BlockCtx &c, WorldView &v, const StepParams &p, int 
         const Box q = ldBox(v.box, a);
         const int a_id = v.ent_id[a];
         const bool a_static = (v.meta[a] & META_STATIC) != 0;
+        // one mask word at a time, eight independent tests in flight (the rank entries are
+        // two 16-byte SMEM loads each; ranks past n repeat the last one and are masked off)
         int count = 0;
-        uint32_t word = 0;
-        for (int r = 0; r < n; r++) {
-            const bool hit = pairTest(v.rbox, r, q, a_id, a_static);
-            if (hit) { word |= 1u << (r & 31); count++; }
-            if ((r & 31) == 31 || r == n - 1) { v.mask[a * v.mask_words + (r >> 5)] = word; word = 0; }
+        for (int wd = 0; wd * 32 < n; wd++) {
+            uint32_t word = 0;
+#pragma unroll 8
+            for (int b = 0; b < 32; b++) {
+                const int r = wd * 32 + b;
+                const bool hit = pairTest(v.rbox, r < n ? r : n - 1, q, a_id, a_static);
+                word |= (uint32_t)(hit & (r < n)) << b;
+            }
+            v.mask[a * v.mask_words + wd] = word;
+            count += popcount32(word);
         }
         v.cnt[a] = count;
         v.last_level[a] = 0;
@@ -402,6 +450,7 @@ MDR_HD void findPairs(const BlockCtx &c, WorldView &v, const StepParams &p, int 
         if (!((v.meta[a] & META_STATIC) && staticStable(ld3(v.pos, a), ld4(v.rot, a)))) v.meta[a] |= META_DEP;
     }
     c.sync();       // every world slot of the block takes this barrier, tail rows or not
+    MDR_PHASE(16);
     if (full < n) {
         const int padded = (n + 31) & ~31;
         for (int a = full; a < n; a++) {
@@ -421,45 +470,63 @@ MDR_HD void findPairs(const BlockCtx &c, WorldView &v, const StepParams &p, int 
 #endif
     if (v.active) copyWords(c, p.t.slot_box + 6 * r0, v.slot, 6 * n);
     c.sync();
+    MDR_PHASE(17);
     groupExclusiveScan(c, v.cnt, n);
     c.sync();
+    MDR_PHASE(18);
     const int total = v.cnt[n];
-    // one (row, mask word) per thread: a row with many pairs is shared by several threads
-    const int words = (n + 31) / 32;
-    for (int task = c.tid(); task < n * words; task += c.nthreads()) {
-        const int a = task / words, wd = task - a * words;
-        uint32_t m = v.mask[a * v.mask_words + wd];
-        if (!m) continue;
-        int off = v.cnt[a];
-        for (int e = 0; e < wd; e++) {
-#if defined(__CUDA_ARCH__)
-            off += __popc(v.mask[a * v.mask_words + e]);
-#else
-            off += __builtin_popcount(v.mask[a * v.mask_words + e]);
-#endif
+    // One pair slot per thread: its row by bisection of the prefix sums, its partner the
+    // j-th set bit of the row's hit mask (a row with many pairs, the ground plane's 64,
+    // is shared by as many threads).
+    const int fill = total < p.max_pairs ? total : p.max_pairs;
+    for (int k = c.tid(); k < fill; k += c.nthreads()) {
+        int lo = 0, hi = n - 1;              // largest row a with cnt[a] <= k
+        while (lo < hi) {
+            const int mid = (lo + hi + 1) >> 1;
+            if (v.cnt[mid] <= k) lo = mid; else hi = mid - 1;
         }
-        while (m) {
-#if defined(__CUDA_ARCH__)
-            int bit = __ffs(m) - 1;
-#else
-            int bit = __builtin_ctz(m);
-#endif
-            m &= m - 1;
-            if (off < p.max_pairs) v.pairs[off] = (uint32_t)a | ((uint32_t)v.order[wd * 32 + bit] << 10);
-            off++;
+        const int a = lo;
+        int j = k - v.cnt[a], wd = 0;
+        uint32_t m = v.mask[a * v.mask_words];
+        for (int cbits = popcount32(m); j >= cbits; cbits = popcount32(m)) {
+            j -= cbits;
+            m = v.mask[a * v.mask_words + ++wd];
         }
+        v.pairs[k] = (uint32_t)a | ((uint32_t)v.order[wd * 32 + nthSetBit(m, j)] << 10);
     }
     c.sync();
+    MDR_PHASE(19);
     // A stable static body (see staticStable) comes out of every substep exactly as it
     // went in, so the per-row substep loops only visit it in the first substep: such
     // rows go to the end of the row order (misc[3] = rows before them). Built by the
     // second warp's first lane while thread 0 assigns the levels.
-    if (c.tid() == (c.nthreads() > 32 ? 32 : 0)) {
+#if defined(__CUDA_ARCH__)
+    if ((c.tid() >> 5) == (c.nthreads() > 32 ? 1 : 0)) {
+        const int lane = c.tid() & 31;
+        int deps = 0;
+        for (int base = 0; base < n; base += 32)
+            deps += __popc(__ballot_sync(0xffffffffu, base + lane < n && (v.meta[base + lane] & META_DEP)));
+        int at_dep = 0, at_rest = deps;
+        for (int base = 0; base < n; base += 32) {
+            const int i = base + lane;
+            const bool live = i < n, dep = live && (v.meta[i] & META_DEP);
+            const uint32_t md = __ballot_sync(0xffffffffu, dep), mr = __ballot_sync(0xffffffffu, live && !dep);
+            const uint32_t below = (1u << lane) - 1u;
+            if (dep) v.row_perm[at_dep + __popc(md & below)] = (uint16_t)i;
+            else if (live) v.row_perm[at_rest + __popc(mr & below)] = (uint16_t)i;
+            at_dep += __popc(md);
+            at_rest += __popc(mr);
+        }
+        if (lane == 0) v.misc[3] = deps;
+    }
+#else
+    {
         int k = 0;
         for (int i = 0; i < n; i++) if (v.meta[i] & META_DEP) v.row_perm[k++] = (uint16_t)i;
         v.misc[3] = k;
         for (int i = 0; i < n; i++) if (!(v.meta[i] & META_DEP)) v.row_perm[k++] = (uint16_t)i;
     }
+#endif
     // Level of a pair = 1 + the latest earlier pair sharing an ordering body: a walk over
     // the pairs in order. The pairs of one row are contiguous and their second bodies
     // all differ, so when the row itself does not order contacts (a stable static: the
@@ -551,6 +618,7 @@ MDR_HD void findPairs(const BlockCtx &c, WorldView &v, const StepParams &p, int 
     }
     }
     c.sync();
+    MDR_PHASE(20);
 }
 
 }  // namespace mdr

@@ -213,6 +213,9 @@ int32_t mdr_phys_create(const mdr_phys_config *cfg, const mdr_object *objs, int3
     p->d_err = p->dalloc<int32_t>(1);
     sp.error_flags = p->d_err;
     sp.probe.world = -1;
+#ifdef MDR_PHASE_CLOCKS
+    sp.phase_clocks = p->dalloc<unsigned long long>(32);
+#endif
 
     // Launch geometry. A block steps `worlds_per_block` worlds side by side with
     // `threads_per_world` threads each; the grid is the resident capacity of the GPU.
@@ -425,6 +428,18 @@ void *mdr_phys_column_ptr(mdr_phys *p, int32_t col)
     void **s = colSlot(p->params.t, col);
     return s ? *s : nullptr;
 }
+
+#ifdef MDR_PHASE_CLOCKS
+// profiling builds only: reads and clears the per-phase clock64 sums (32 slots)
+int32_t mdr_phys_phase_clocks(mdr_phys *p, unsigned long long *out)
+{
+    REQ_CUDA(cudaSetDevice(p->cfg.gpu_id));
+    REQ_CUDA(cudaStreamSynchronize(p->stream));
+    REQ_CUDA(cudaMemcpy(out, p->params.phase_clocks, 32 * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+    REQ_CUDA(cudaMemset(p->params.phase_clocks, 0, 32 * sizeof(unsigned long long)));
+    return MDR_OK;
+}
+#endif
 
 int32_t mdr_phys_flag_rebuild(mdr_phys *p)
 {
