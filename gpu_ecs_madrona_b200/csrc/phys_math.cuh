@@ -21,6 +21,19 @@
 
 namespace mdr {
 
+// Arithmetic that is never contracted into an FMA, whatever -fmad says: the AABB math
+// below decides the broadphase pair list (integer state, bit-exact in every build), so
+// the FMA-contracted tolerance build (libmadrona_b200_fma.so, -fmad=true) keeps it exact.
+#if defined(__CUDA_ARCH__)
+MDR_HD float xmul(float a, float b) { return __fmul_rn(a, b); }
+MDR_HD float xadd(float a, float b) { return __fadd_rn(a, b); }
+MDR_HD float xsub(float a, float b) { return __fsub_rn(a, b); }
+#else
+MDR_HD float xmul(float a, float b) { return a * b; }
+MDR_HD float xadd(float a, float b) { return a + b; }
+MDR_HD float xsub(float a, float b) { return a - b; }
+#endif
+
 struct V3 { float x, y, z; };
 struct Q4 { float w, x, y, z; };
 struct Box { V3 lo, hi; };
@@ -98,17 +111,17 @@ MDR_HD M3 matFromQuat(Q4 r)
     m.c[2] = mk3(2.f * (xz + wy), 2.f * (yz - wx), 1.f - 2.f * (x2 + y2));
     return m;
 }
-// math.hpp:835-866
+// math.hpp:835-866 (only the AABB transform uses it: never contracted, see xmul)
 MDR_HD M3 matFromRS(Q4 r, V3 s)
 {
-    float x2 = r.x * r.x, y2 = r.y * r.y, z2 = r.z * r.z;
-    float xz = r.x * r.z, xy = r.x * r.y, yz = r.y * r.z;
-    float wx = r.w * r.x, wy = r.w * r.y, wz = r.w * r.z;
-    V3 ds = mk3(s.x * 2.f, s.y * 2.f, s.z * 2.f);
+    float x2 = xmul(r.x, r.x), y2 = xmul(r.y, r.y), z2 = xmul(r.z, r.z);
+    float xz = xmul(r.x, r.z), xy = xmul(r.x, r.y), yz = xmul(r.y, r.z);
+    float wx = xmul(r.w, r.x), wy = xmul(r.w, r.y), wz = xmul(r.w, r.z);
+    V3 ds = mk3(xmul(s.x, 2.f), xmul(s.y, 2.f), xmul(s.z, 2.f));
     M3 m;
-    m.c[0] = mk3(s.x - ds.x * (y2 + z2), ds.x * (xy + wz), ds.x * (xz - wy));
-    m.c[1] = mk3(ds.y * (xy - wz), s.y - ds.y * (x2 + z2), ds.y * (yz + wx));
-    m.c[2] = mk3(ds.z * (xz + wy), ds.z * (yz - wx), s.z - ds.z * (x2 + y2));
+    m.c[0] = mk3(xsub(s.x, xmul(ds.x, xadd(y2, z2))), xmul(ds.x, xadd(xy, wz)), xmul(ds.x, xsub(xz, wy)));
+    m.c[1] = mk3(xmul(ds.y, xsub(xy, wz)), xsub(s.y, xmul(ds.y, xadd(x2, z2))), xmul(ds.y, xadd(yz, wx)));
+    m.c[2] = mk3(xmul(ds.z, xadd(xz, wy)), xmul(ds.z, xsub(yz, wx)), xsub(s.z, xmul(ds.z, xadd(x2, y2))));
     return m;
 }
 MDR_HD V3 matMul(const M3 &m, V3 v) { return m.c[0] * v.x + m.c[1] * v.y + m.c[2] * v.z; }
@@ -141,10 +154,10 @@ MDR_HD Box applyTRS(const Box &b, V3 t, Q4 r, V3 s)
 #pragma unroll
         for (int j = 0; j < 3; j++) {
             float mji = comp(m.c[j], i);
-            float e = mji * bl[j];
-            float f = mji * bh[j];
-            if (e < f) { lo[i] += e; hi[i] += f; }
-            else { lo[i] += f; hi[i] += e; }
+            float e = xmul(mji, bl[j]);
+            float f = xmul(mji, bh[j]);
+            if (e < f) { lo[i] = xadd(lo[i], e); hi[i] = xadd(hi[i], f); }
+            else { lo[i] = xadd(lo[i], f); hi[i] = xadd(hi[i], e); }
         }
     }
     o.lo = mk3(lo[0], lo[1], lo[2]);
@@ -159,11 +172,11 @@ MDR_HD Box expandWithMotion(Box b, V3 v, float vf, float af)
     const float vv[3] = { v.x, v.y, v.z };
 #pragma unroll
     for (int i = 0; i < 3; i++) {
-        float pos_delta = vf * vv[i];
-        float min_delta = pos_delta - af;
-        float max_delta = pos_delta + af;
-        if (min_delta < 0.f) lo[i] += min_delta;
-        if (max_delta > 0.f) hi[i] += max_delta;
+        float pos_delta = xmul(vf, vv[i]);
+        float min_delta = xsub(pos_delta, af);
+        float max_delta = xadd(pos_delta, af);
+        if (min_delta < 0.f) lo[i] = xadd(lo[i], min_delta);
+        if (max_delta > 0.f) hi[i] = xadd(hi[i], max_delta);
     }
     b.lo = mk3(lo[0], lo[1], lo[2]);
     b.hi = mk3(hi[0], hi[1], hi[2]);
