@@ -22,6 +22,9 @@
 using namespace mdr::ecs;
 using namespace mdr;       // static_map.hpp
 
+// physics.cu: one rigid-body step of `p` enqueued on `stream` (capturable), the physics node of an ECS graph
+int32_t mdrPhysEnqueueStep(mdr_phys *p, cudaStream_t stream);
+
 #define REQ_CUDA(expr)                                                                   \
     do {                                                                                 \
         cudaError_t e_ = (expr);                                                         \
@@ -34,31 +37,24 @@ using namespace mdr;       // static_map.hpp
 
 namespace {
 
-constexpr int kWarpsPerBlock = 8;
-
 // ------------------------------------------------------------------ kernels --
+// The megakernel itself is mdr::ecs::ecsGraphKernel (include/madrona/b200/ecs_device.cuh); this is its
+// instantiation for the built-in worlds, whose systems are named by func id (csrc/ecs_apps.cuh). A world
+// whose systems live in another translation unit brings its own instantiation (mdr_ecs_set_step_launcher).
+struct AppsBuiltin {
+    __device__ __forceinline__ void operator()(Context &ctx, const NodeDev &nd) const { apps::dispatchParallelFor(ctx, nd); }
+};
 template <int kMinBlocks>
 __global__ void __launch_bounds__(32 * kWarpsPerBlock, kMinBlocks)
-ecsStepKernel(const EcsDev *__restrict__ E)
+ecsStepKernel(const EcsDev *__restrict__ E, int first, int last)
 {
     __shared__ WarpShared shared[kWarpsPerBlock];
     WarpShared *ws = &shared[threadIdx.x >> 5];
     const int warps = gridDim.x * kWarpsPerBlock;
-    const int num_nodes = E->num_nodes;
     Context ctx;
     for (int w = blockIdx.x * kWarpsPerBlock + (threadIdx.x >> 5); w < E->num_worlds; w += warps) {
         loadWorld(ctx, E, ws, w);
-        // TaskGraph::run (src/core/taskgraph.cpp:117-122): nodes in sorted order
-        for (int ni = 0; ni < num_nodes; ni++) {
-            const NodeDev &nd = E->node[ni];
-            switch (nd.kind) {
-            case kNodeParallelFor: apps::dispatchParallelFor(ctx, nd); break;
-            case kNodeClearTmp: clearArchetype(ctx, nd.arch, true); break;      // taskgraph.inl:88-92
-            case kNodeSort: sortArchetype(ctx, nd.arch, nd.key_col, nd.remap != 0); break;
-            default: break;                                                     // ResetTmpAllocNode: no bump allocator to reset
-            }
-            __syncwarp();
-        }
+        runNodes(ctx, E, first, last, AppsBuiltin());
         storeWorld(ctx);
     }
 }
@@ -265,7 +261,7 @@ __global__ void ecsBroadcastNodes(IdNode *dst, int32_t id_cap, const IdNode *src
 // ---------------------------------------------------------------- host side --
 struct HostComponent { int32_t bytes, align; };
 struct HostArchetype { std::vector<int32_t> comps; int32_t max_rows, flags; bool singleton; };
-struct HostNode { int32_t kind, func, arch, key_comp, remap; std::vector<int32_t> comps, deps; };
+struct HostNode { int32_t kind, func, arch, key_comp, remap; std::vector<int32_t> comps, deps; void *fn = nullptr; };
 struct HostExport { int32_t arch, comp; };
 
 }  // namespace
@@ -285,7 +281,11 @@ struct mdr_ecs {
     cudaGraphExec_t graph = nullptr;
     bool exports_dirty = true;
     int blocks = 0;
-    void (*step_kernel)(const EcsDev *) = nullptr;
+    void (*step_kernel)(const EcsDev *, int, int) = nullptr;
+    mdr_ecs_launch_fn launcher = nullptr;   // megakernel instantiated in the user's translation unit
+    void *launcher_user = nullptr;
+    int32_t tmp_bytes = 0, world_data_bytes = 0;
+    std::vector<mdr_phys *> physics;        // by node index (kNodePhysics), attached after build
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     double timed_ms = 0;
     int timed_steps = 0, pending_steps = 0;
@@ -479,6 +479,92 @@ int32_t mdr_ecs_add_parallel_for(mdr_ecs *e, int32_t func, const int32_t *comps,
     return addNode(e, node, deps, ndeps);
 }
 
+int32_t mdr_ecs_add_parallel_for_fn(mdr_ecs *e, const void *device_fn, const int32_t *comps, int32_t n,
+                                    const int32_t *deps, int32_t ndeps)
+{
+    if (!e || !comps || n <= 0 || n > kMaxQueryComps || !device_fn) return MDR_EINVAL;
+    HostNode node { kNodeParallelFor, 0, -1, -1, 0, {}, {} };
+    node.fn = (void *)device_fn;
+    for (int i = 0; i < n; i++) {
+        if (comps[i] < 0 || comps[i] >= (int32_t)e->comps.size()) return MDR_EINVAL;
+        node.comps.push_back(comps[i]);
+    }
+    return addNode(e, node, deps, ndeps);
+}
+
+int32_t mdr_ecs_add_physics(mdr_ecs *e, const int32_t *deps, int32_t ndeps)
+{
+    return addNode(e, HostNode { kNodePhysics, 0, -1, -1, 0, {}, {} }, deps, ndeps);
+}
+
+int32_t mdr_ecs_attach_physics(mdr_ecs *e, int32_t node, mdr_phys *p)
+{
+    if (!e || !p) return MDR_EINVAL;
+    if (!e->built) return MDR_ESTATE;
+    if (node < 0 || node >= (int32_t)e->nodes.size() || e->nodes[node].kind != kNodePhysics) return MDR_EINVAL;
+    e->physics.resize(e->nodes.size(), nullptr);
+    e->physics[node] = p;
+    if (e->graph) { cudaGraphExecDestroy(e->graph); e->graph = nullptr; }
+    return MDR_OK;
+}
+
+// RigidBodyPhysicsSystem on an archetype of this ECS: the archetype must start with the twelve physics
+// components in phys::Cols order after Entity (include/madrona/physics.hpp:449-464), byte sizes checked.
+int32_t mdr_phys_create_on_ecs(const mdr_phys_config *cfg, const mdr_object *objs, int32_t num_objs,
+                               const float *verts, const uint32_t *poly_words, mdr_ecs *e, int32_t arch,
+                               mdr_phys **out)
+{
+    if (!cfg || !e || !out) return MDR_EINVAL;
+    if (!e->built) return MDR_ESTATE;
+    if (arch < 0 || arch >= e->host.num_arch) return MDR_EINVAL;
+    const ArchDev &A = e->host.arch[arch];
+    if (A.num_cols < MDR_NUM_PHYS_COLS || cfg->num_worlds != e->host.num_worlds || cfg->gpu_id != e->cfg.gpu_id ||
+        cfg->max_bodies_per_world != A.max_rows)
+        return MDR_EINVAL;
+    void *cols[MDR_NUM_PHYS_COLS];
+    for (int c = 0; c < MDR_NUM_PHYS_COLS; c++) {
+        if (A.col_bytes[c] != mdr_phys_column_bytes(c)) return MDR_EINVAL;
+        cols[c] = A.col[c];
+    }
+    return mdr_phys_create_on_columns(cfg, objs, num_objs, verts, poly_words, A.stride, cols, A.row_count, out);
+}
+
+int32_t mdr_ecs_set_step_launcher(mdr_ecs *e, mdr_ecs_launch_fn fn, void *user)
+{
+    if (!e) return MDR_EINVAL;
+    e->launcher = fn;
+    e->launcher_user = user;
+    if (e->graph) { cudaGraphExecDestroy(e->graph); e->graph = nullptr; }
+    return MDR_OK;
+}
+
+int32_t mdr_ecs_set_tmp_bytes(mdr_ecs *e, int32_t bytes_per_world)
+{
+    if (!e || bytes_per_world < 0) return MDR_EINVAL;
+    if (e->built) return MDR_ESTATE;
+    e->tmp_bytes = (bytes_per_world + 15) / 16 * 16;
+    return MDR_OK;
+}
+
+int32_t mdr_ecs_set_world_data_bytes(mdr_ecs *e, int32_t bytes_per_world)
+{
+    if (!e || bytes_per_world < 0) return MDR_EINVAL;
+    if (e->built) return MDR_ESTATE;
+    e->world_data_bytes = (bytes_per_world + 15) / 16 * 16;
+    return MDR_OK;
+}
+
+const void *mdr_ecs_device_descriptor(mdr_ecs *e) { return e && e->built ? e->dev : nullptr; }
+int32_t mdr_ecs_num_worlds(mdr_ecs *e) { return e ? e->cfg.num_worlds : MDR_EINVAL; }
+
+int32_t mdr_ecs_tables_written(mdr_ecs *e)
+{
+    if (!e) return MDR_EINVAL;
+    if (!e->built) return MDR_ESTATE;
+    e->exports_dirty = true;
+    return MDR_OK;
+}
+
 int32_t mdr_ecs_add_clear_tmp(mdr_ecs *e, int32_t arch, const int32_t *deps, int32_t ndeps)
 {
     if (!e || arch < 0 || arch >= (int32_t)e->archs.size()) return MDR_EINVAL;
@@ -539,6 +625,13 @@ int32_t mdr_ecs_build(mdr_ecs *e)
     H.id_nodes = e->dalloc<IdNode>((size_t)W * H.id_cap);
     H.id_state = e->dalloc<IdState>(W);
     H.error = e->dalloc<int32_t>(1);
+    H.tmp_bytes = e->tmp_bytes;
+    if (H.tmp_bytes > 0) {
+        H.tmp_arena = e->dalloc<char>((size_t)W * H.tmp_bytes, false);
+        H.tmp_used = e->dalloc<int32_t>(W);
+    }
+    H.world_data_bytes = e->world_data_bytes;
+    if (H.world_data_bytes > 0) H.world_data = e->dalloc<char>((size_t)W * H.world_data_bytes);
     H.max_handles = e->cfg.max_script_handles;
     if (H.max_handles > 0) {
         H.handles = e->dalloc<Entity>((size_t)W * H.max_handles);
@@ -586,6 +679,7 @@ int32_t mdr_ecs_build(mdr_ecs *e)
         const HostNode &hn = e->nodes[ni];
         NodeDev &N = H.node[ni];
         N.kind = hn.kind; N.func = hn.func; N.arch = hn.arch; N.remap = hn.remap;
+        N.fn = (NodeFn)hn.fn;
         if (hn.kind == kNodeSort) {
             N.key_col = colOf(e->archs[hn.arch], hn.key_comp);
             SortScratch &S = H.sort[hn.arch];
@@ -742,6 +836,7 @@ int32_t mdr_ecs_row_counts(mdr_ecs *e, int32_t arch, int32_t *host)
     return MDR_OK;
 }
 
+int32_t mdr_ecs_num_components(mdr_ecs *e) { return e ? (int32_t)e->comps.size() : MDR_EINVAL; }
 int32_t mdr_ecs_num_archetypes(mdr_ecs *e) { return e ? (int32_t)e->archs.size() : MDR_EINVAL; }
 int32_t mdr_ecs_num_columns(mdr_ecs *e, int32_t arch)
 {
@@ -804,12 +899,34 @@ int32_t mdr_ecs_step_async(mdr_ecs *e, int32_t num_steps)
         cudaGraph_t g = nullptr;
         REQ_CUDA(cudaStreamBeginCapture(e->stream, cudaStreamCaptureModeThreadLocal));
         if (staged) ecsExportCopy<<<(e->host.num_worlds + 7) / 8, 256, 0, e->stream>>>(e->dev, 0);
-        e->step_kernel<<<e->blocks, 32 * kWarpsPerBlock, 0, e->stream>>>(e->dev);
+        // The megakernel walks maximal runs of in-kernel nodes; a physics node is a launch of the
+        // rigid-body step kernel on the same tables between two such runs (the reference's generated
+        // megakernel takes the same (start_node, end_node) pair, src/mw/cuda_exec.cpp:728-745).
+        int32_t rc_launch = MDR_OK;
+        auto segment = [&](int first, int last) {
+            if (first >= last) return;
+            if (e->launcher) {
+                const int32_t r = e->launcher(e->dev, first, last, e->host.num_worlds, (void *)e->stream, e->launcher_user);
+                if (r != MDR_OK) rc_launch = r;
+            } else {
+                e->step_kernel<<<e->blocks, 32 * kWarpsPerBlock, 0, e->stream>>>(e->dev, first, last);
+            }
+        };
+        int first = 0;
+        for (int ni = 0; ni < e->host.num_nodes; ni++) {
+            if (e->host.node[ni].kind != kNodePhysics) continue;
+            segment(first, ni);
+            first = ni + 1;
+            mdr_phys *ph = ni < (int)e->physics.size() ? e->physics[ni] : nullptr;
+            if (!ph || mdrPhysEnqueueStep(ph, e->stream) != MDR_OK) rc_launch = MDR_ESTATE;
+        }
+        segment(first, e->host.num_nodes);
         if (staged) {
             launchExportOffsets(e->dev, e->host.num_exports, e->host.num_worlds, e->stream);
             ecsExportCopy<<<(e->host.num_worlds + 7) / 8, 256, 0, e->stream>>>(e->dev, 1);
         }
         REQ_CUDA(cudaStreamEndCapture(e->stream, &g));
+        if (rc_launch != MDR_OK) { cudaGraphDestroy(g); return rc_launch; }
         REQ_CUDA(cudaGraphInstantiate(&e->graph, g, 0));
         REQ_CUDA(cudaGraphDestroy(g));
     }
@@ -855,9 +972,15 @@ float mdr_ecs_step_ms(mdr_ecs *e, int32_t *steps)
 int32_t mdr_ecs_launches_per_step(mdr_ecs *e)
 {
     if (!e || !e->built) return MDR_EINVAL;
+    int n = 0, run = 0;
+    for (int ni = 0; ni < e->host.num_nodes; ni++) {
+        if (e->host.node[ni].kind == kNodePhysics) { n += 2 + (run > 0); run = 0; }   // BVH rebuild check + step kernel
+        else run++;
+    }
+    n += run > 0 || e->host.num_nodes == 0;
     for (int s = 0; s < e->host.num_exports; s++)
-        if (!e->host.exports[s].fixed) return 4;
-    return 1;
+        if (!e->host.exports[s].fixed) return n + 3;
+    return n;
 }
 
 int32_t mdr_static_map_build(const uint32_t *keys, const uint32_t *values, int32_t n,

@@ -7,6 +7,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <algorithm>
 #include <vector>
 
 #include "phys_kernel.cuh"
@@ -82,6 +83,7 @@ struct mdr_phys {
     int pending_launches = 0;
     double timed_ms = 0.0;
     int timed_launches = 0;
+    bool external_tables = false;            // columns and row counts belong to an ECS archetype
     StepKernel kernel = nullptr;             // the variant in use: kernel_plain, or kernel_joints once joints are set
     StepKernel kernel_plain = nullptr, kernel_joints = nullptr;
     int threads = 0, blocks = 0, blocks_per_sm = 0, overflow_per_slot = 0;
@@ -94,11 +96,17 @@ struct mdr_phys {
     JointDev *d_joints = nullptr;       // mdr_phys_set_joints
     int32_t *d_joint_count = nullptr;
 
+    bool alloc_failed = false;   // a table did not fit the device: creation returns MDR_ECAPACITY
     template <typename T> T *dalloc(size_t n, bool zero = true)
     {
         void *p = nullptr;
         size_t bytes = (n ? n : 1) * sizeof(T);
-        REQ_CUDA(cudaMalloc(&p, bytes));
+        if (alloc_failed) return nullptr;
+        if (cudaMalloc(&p, bytes) != cudaSuccess) {
+            cudaGetLastError();          // out of memory is not sticky
+            alloc_failed = true;
+            return nullptr;
+        }
         if (zero) REQ_CUDA(cudaMemset(p, 0, bytes));
         allocs.push_back(p);
         return (T *)p;
@@ -106,7 +114,7 @@ struct mdr_phys {
     template <typename T> T *upload(const std::vector<T> &v)
     {
         T *d = dalloc<T>(v.size(), false);
-        REQ_CUDA(cudaMemcpy(d, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice));
+        if (d) REQ_CUDA(cudaMemcpy(d, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice));
         return d;
     }
 };
@@ -156,8 +164,14 @@ int32_t mdr_phys_column_bytes(int32_t col)
     return col >= 0 && col < MDR_NUM_PHYS_COLS ? kColBytes[col] : 0;
 }
 
-int32_t mdr_phys_create(const mdr_phys_config *cfg, const mdr_object *objs, int32_t num_objs,
-                        const float *verts, const uint32_t *poly_words, mdr_phys **out)
+}   // extern "C"
+
+// `ext` non-null: the rigid-body columns are somebody else's tables (an ECS archetype,
+// mdr_phys_create_on_columns); only the BVH singleton state and scratch are allocated here.
+struct ExternalTables { int32_t stride; void *const *cols; int32_t *row_count; };
+
+static int32_t createImpl(const mdr_phys_config *cfg, const mdr_object *objs, int32_t num_objs,
+                          const float *verts, const uint32_t *poly_words, const ExternalTables *ext, mdr_phys **out)
 {
     if (!cfg || !out || !objs || num_objs <= 0 || cfg->num_worlds <= 0 ||
         cfg->max_bodies_per_world <= 0 || cfg->max_bodies_per_world > MDR_MAX_BODIES ||
@@ -184,13 +198,15 @@ int32_t mdr_phys_create(const mdr_phys_config *cfg, const mdr_object *objs, int3
     StepParams &sp = p->params;
     fillStepConstants(sp, *cfg);
     const int W = cfg->num_worlds;
-    const int stride = (cfg->max_bodies_per_world + 3) / 4 * 4;   // every column tile 16 B aligned
+    const int stride = ext ? ext->stride : (cfg->max_bodies_per_world + 3) / 4 * 4;   // every column tile 16 B aligned
+    if (stride < cfg->max_bodies_per_world || stride % 4) { delete p; return MDR_EINVAL; }
     const size_t R = (size_t)W * stride;
     PhysTables &t = sp.t;
     t.stride = stride;
     t.num_worlds = W;
-    for (int c = 0; c < MDR_NUM_PHYS_COLS; c++) *colSlot(t, c) = p->dalloc<char>(R * kColBytes[c]);
-    t.row_count = p->dalloc<int32_t>(W);
+    for (int c = 0; c < MDR_NUM_PHYS_COLS; c++) *colSlot(t, c) = ext ? ext->cols[c] : (void *)p->dalloc<char>(R * kColBytes[c]);
+    t.row_count = ext ? ext->row_count : p->dalloc<int32_t>(W);
+    p->external_tables = ext != nullptr;
     t.leaf_aabb = p->dalloc<float>(R * 6);
     t.slot_box = p->dalloc<float>(R * 6);
     t.order = p->dalloc<uint16_t>(R);
@@ -277,6 +293,12 @@ int32_t mdr_phys_create(const mdr_phys_config *cfg, const mdr_object *objs, int3
     p->blocks = (int)grid;
     p->overflow_per_slot = sp.max_pairs - sp.smem_contacts;
     sp.overflow = p->dalloc<SolverContact>((size_t)p->blocks * wpb * (p->overflow_per_slot + 1), false);
+    if (p->alloc_failed) {
+        fprintf(stderr, "madrona_b200: %d worlds x %d bodies (%d contact slots) do not fit the device memory\n",
+                W, cfg->max_bodies_per_world, sp.max_pairs);
+        mdr_phys_destroy(p);
+        return MDR_ECAPACITY;
+    }
 
     REQ_CUDA(cudaStreamCreateWithFlags(&p->stream, cudaStreamNonBlocking));
     REQ_CUDA(cudaEventCreate(&p->ev0));
@@ -284,6 +306,37 @@ int32_t mdr_phys_create(const mdr_phys_config *cfg, const mdr_object *objs, int3
     memset(&p->d_probe, 0, sizeof(p->d_probe));
     *out = p;
     return MDR_OK;
+}
+
+// The physics node of an ECS task graph (mdr_ecs_add_physics): the BVH rebuild check and one step on
+// the caller's stream, capturable into its run graph. Timing belongs to the caller.
+int32_t mdrPhysEnqueueStep(mdr_phys *p, cudaStream_t stream)
+{
+    if (!p) return MDR_EINVAL;
+    const int W = p->cfg.num_worlds;
+    bvhRebuildKernel<<<(W + 63) / 64, 64, 0, stream>>>(p->params);
+    p->kernel<<<p->blocks, p->threads, p->smem_bytes, stream>>>(
+        p->params, p->threads_per_world, (int)p->slot_bytes, p->overflow_per_slot, p->lockstep, 0, W);
+    return cudaGetLastError() == cudaSuccess ? MDR_OK : MDR_ESTATE;
+}
+
+extern "C" {
+
+int32_t mdr_phys_create(const mdr_phys_config *cfg, const mdr_object *objs, int32_t num_objs,
+                        const float *verts, const uint32_t *poly_words, mdr_phys **out)
+{
+    return createImpl(cfg, objs, num_objs, verts, poly_words, nullptr, out);
+}
+
+int32_t mdr_phys_create_on_columns(const mdr_phys_config *cfg, const mdr_object *objs, int32_t num_objs,
+                                   const float *verts, const uint32_t *poly_words, int32_t row_stride,
+                                   void *const *columns, int32_t *row_counts, mdr_phys **out)
+{
+    if (!columns || !row_counts || row_stride <= 0) return MDR_EINVAL;
+    for (int c = 0; c < MDR_NUM_PHYS_COLS; c++)
+        if (!columns[c] || ((uintptr_t)columns[c] & 15u)) return MDR_EINVAL;
+    const ExternalTables ext { row_stride, columns, row_counts };
+    return createImpl(cfg, objs, num_objs, verts, poly_words, &ext, out);
 }
 
 void mdr_phys_destroy(mdr_phys *p)
@@ -303,9 +356,30 @@ void mdr_phys_destroy(mdr_phys *p)
     delete p;
 }
 
+// One world's row count (entity ids and leaf ids 0..rows-1, as mdr_phys_set_row_counts gives every world)
+// and its BVH flagged for rebuild: the structural half of a per-world reset.
+int32_t mdr_phys_set_world_rows(mdr_phys *p, int32_t world, int32_t rows)
+{
+    if (!p || world < 0 || world >= p->cfg.num_worlds || rows < 0 || rows > p->cfg.max_bodies_per_world) return MDR_EINVAL;
+    if (p->external_tables) return MDR_ESTATE;      // the ECS owns entities and row counts
+    REQ_CUDA(cudaSetDevice(p->cfg.gpu_id));
+    PhysTables &t = p->params.t;
+    std::vector<int32_t> ent((size_t)t.stride * 2), leaf((size_t)t.stride);
+    for (int i = 0; i < t.stride; i++) {
+        ent[2 * i] = 0;
+        ent[2 * i + 1] = leaf[i] = i < rows ? i : -1;
+    }
+    REQ_CUDA(cudaStreamSynchronize(p->stream));
+    REQ_CUDA(cudaMemcpy(t.row_count + world, &rows, 4, cudaMemcpyHostToDevice));
+    REQ_CUDA(cudaMemcpy(t.entity + 2 * (size_t)world * t.stride, ent.data(), ent.size() * 4, cudaMemcpyHostToDevice));
+    REQ_CUDA(cudaMemcpy(t.leaf_id + (size_t)world * t.stride, leaf.data(), leaf.size() * 4, cudaMemcpyHostToDevice));
+    return mdr_phys_reset_worlds(p, &world, 1);
+}
+
 int32_t mdr_phys_set_row_counts(mdr_phys *p, const int32_t *rows)
 {
     if (!p || !rows) return MDR_EINVAL;
+    if (p->external_tables) return MDR_ESTATE;      // the ECS owns entities and row counts
     REQ_CUDA(cudaSetDevice(p->cfg.gpu_id));
     PhysTables &t = p->params.t;
     const int W = t.num_worlds;
@@ -367,6 +441,11 @@ int32_t mdr_phys_write_column(mdr_phys *p, int32_t col, const void *src)
     if (!s) return MDR_EINVAL;
     REQ_CUDA(cudaSetDevice(p->cfg.gpu_id));
     const size_t nb = kColBytes[col], n = p->cfg.max_bodies_per_world;
+    if (col == MDR_COL_OBJECT_ID) {     // the step indexes the shared object table with it
+        const int32_t *ids = (const int32_t *)src;
+        for (size_t i = 0; i < n * (size_t)p->cfg.num_worlds; i++)
+            if (ids[i] < 0 || ids[i] >= p->params.a.num_objs) return MDR_EINVAL;
+    }
     REQ_CUDA(cudaMemcpy2DAsync(*s, p->params.t.stride * nb, src, n * nb, n * nb, p->cfg.num_worlds,
                                cudaMemcpyHostToDevice, p->stream));
     REQ_CUDA(cudaStreamSynchronize(p->stream));
@@ -447,6 +526,64 @@ int32_t mdr_phys_flag_rebuild(mdr_phys *p)
     REQ_CUDA(cudaSetDevice(p->cfg.gpu_id));
     REQ_CUDA(cudaMemsetAsync(p->params.t.rebuild_flag, 1, p->cfg.num_worlds, p->stream));
     p->maybe_rebuild = true;
+    return MDR_OK;
+}
+
+// RigidBodyPhysicsSystem::reset of the listed worlds only (physics.cpp:1038-1043: the context's own BVH is
+// flagged, nobody else's): their slot boxes are reset and their traversal order rebuilt before the next
+// step; every other world keeps its grown boxes and its pair order, as in the reference.
+int32_t mdr_phys_reset_worlds(mdr_phys *p, const int32_t *worlds, int32_t n)
+{
+    if (!p || n < 0 || (n > 0 && !worlds)) return MDR_EINVAL;
+    const int W = p->cfg.num_worlds;
+    for (int i = 0; i < n; i++) if (worlds[i] < 0 || worlds[i] >= W) return MDR_EINVAL;
+    if (n == 0) return MDR_OK;
+    REQ_CUDA(cudaSetDevice(p->cfg.gpu_id));
+    // runs of consecutive worlds become one memset each (an episode reset names few worlds)
+    std::vector<int32_t> sorted(worlds, worlds + n);
+    std::sort(sorted.begin(), sorted.end());
+    for (int i = 0; i < n;) {
+        int j = i + 1;
+        while (j < n && sorted[j] <= sorted[j - 1] + 1) j++;
+        REQ_CUDA(cudaMemsetAsync(p->params.t.rebuild_flag + sorted[i], 1, (size_t)(sorted[j - 1] - sorted[i] + 1), p->stream));
+        i = j;
+    }
+    p->maybe_rebuild = true;
+    return MDR_OK;
+}
+
+// One world's rows of a column, host -> device ([rows][bytes], rows <= max_bodies_per_world): the
+// per-world half of an episode reset (the reference writes components through ctx.getUnsafe in the
+// world's own reset code).
+int32_t mdr_phys_write_world_column(mdr_phys *p, int32_t col, int32_t world, int32_t rows, const void *src)
+{
+    if (!p || !src || world < 0 || world >= p->cfg.num_worlds || rows < 0 || rows > p->cfg.max_bodies_per_world)
+        return MDR_EINVAL;
+    void **s = colSlot(p->params.t, col);
+    if (!s) return MDR_EINVAL;
+    if (col == MDR_COL_OBJECT_ID) {
+        const int32_t *ids = (const int32_t *)src;
+        for (int i = 0; i < rows; i++) if (ids[i] < 0 || ids[i] >= p->params.a.num_objs) return MDR_EINVAL;
+    }
+    REQ_CUDA(cudaSetDevice(p->cfg.gpu_id));
+    const size_t nb = kColBytes[col];
+    REQ_CUDA(cudaMemcpyAsync((char *)*s + (size_t)world * p->params.t.stride * nb, src, rows * nb,
+                             cudaMemcpyHostToDevice, p->stream));
+    REQ_CUDA(cudaStreamSynchronize(p->stream));
+    return MDR_OK;
+}
+
+int32_t mdr_phys_read_world_column(mdr_phys *p, int32_t col, int32_t world, int32_t rows, void *dst)
+{
+    if (!p || !dst || world < 0 || world >= p->cfg.num_worlds || rows < 0 || rows > p->cfg.max_bodies_per_world)
+        return MDR_EINVAL;
+    void **s = colSlot(p->params.t, col);
+    if (!s) return MDR_EINVAL;
+    REQ_CUDA(cudaSetDevice(p->cfg.gpu_id));
+    const size_t nb = kColBytes[col];
+    REQ_CUDA(cudaMemcpyAsync(dst, (const char *)*s + (size_t)world * p->params.t.stride * nb, rows * nb,
+                             cudaMemcpyDeviceToHost, p->stream));
+    REQ_CUDA(cudaStreamSynchronize(p->stream));
     return MDR_OK;
 }
 

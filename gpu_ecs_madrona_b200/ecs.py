@@ -105,10 +105,22 @@ class EcsRegistry:
         _check(self.lib.mdr_ecs_create(C.byref(cfg), C.byref(h)), "mdr_ecs_create")
         self.h = h
 
+    @classmethod
+    def attach(cls, handle, num_worlds, gpu_id=0):
+        """View of an executor somebody else owns (an out-of-tree world's TaskGraphExecutor, examples/):
+        the state accessors of this class on its mdr_ecs handle; close() leaves it alone."""
+        self = cls.__new__(cls)
+        self.lib = _lib()
+        self.num_worlds, self.gpu_id = num_worlds, gpu_id
+        self.h = C.c_void_p(handle)
+        self._borrowed = True
+        self._describe()
+        return self
+
     def close(self):
-        if self.h:
+        if self.h and not getattr(self, "_borrowed", False):
             self.lib.mdr_ecs_destroy(self.h)
-            self.h = None
+        self.h = None
 
     def __del__(self):
         try:

@@ -129,6 +129,25 @@ int32_t mdr_phys_column_bytes(int32_t col);
 /* RigidBodyPhysicsSystem::reset semantics for the BVH (physics.cpp:1038-1043,
  * include/madrona/physics.inl:109-112): rebuild on the next step. */
 int32_t mdr_phys_flag_rebuild(mdr_phys *p);
+/* The same for the listed worlds only: RigidBodyPhysicsSystem::reset is per world (it flags the
+ * context's own BVH, physics.cpp:1038-1043, include/madrona/physics.inl:109-112). Worlds that are
+ * not named keep their grown slot boxes and traversal order, hence their pair order. */
+int32_t mdr_phys_reset_worlds(mdr_phys *p, const int32_t *worlds, int32_t n);
+/* Per-world halves of an episode reset: one world's rows of a column ([rows][bytes] on the host;
+ * the reference writes components through ctx.getUnsafe in the world's own reset code), and one
+ * world's row count (ids 0..rows-1; flags that world's BVH). */
+int32_t mdr_phys_write_world_column(mdr_phys *p, int32_t col, int32_t world, int32_t rows, const void *src);
+int32_t mdr_phys_read_world_column(mdr_phys *p, int32_t col, int32_t world, int32_t rows, void *dst);
+int32_t mdr_phys_set_world_rows(mdr_phys *p, int32_t world, int32_t rows);
+/* The rigid-body step over columns that live elsewhere (an ECS archetype's tables, so that physics
+ * is a node of the same task graph as user systems: RigidBodyPhysicsSystem::setup*Tasks add their
+ * nodes to the user's builder, src/physics/physics.cpp:1142-1205). columns[MDR_NUM_PHYS_COLS] are
+ * device pointers [num_worlds][row_stride][column bytes] in phys::Cols order (include/madrona/
+ * physics.hpp:449-464), 16-byte aligned; row_counts [num_worlds] on the device. The owner creates
+ * entities and sets row counts; mdr_phys_set_row_counts answers MDR_ESTATE here. */
+int32_t mdr_phys_create_on_columns(const mdr_phys_config *cfg, const mdr_object *objs, int32_t num_objs,
+                                   const float *verts, const uint32_t *poly_words, int32_t row_stride,
+                                   void *const *columns, int32_t *row_counts, mdr_phys **out);
 
 /* Joint constraints: the ConstraintData archetype (one JointConstraint per
  * entity, include/madrona/physics.hpp:196-240), collected every substep by
@@ -284,6 +303,35 @@ int32_t mdr_ecs_export_column(mdr_ecs *e, int32_t arch, int32_t comp, int32_t sl
 /* builder.addToGraph<ParallelForNode<Ctx, fn, Cs...>>(deps); returns the node id */
 int32_t mdr_ecs_add_parallel_for(mdr_ecs *e, int32_t func, const int32_t *comps, int32_t n, const int32_t *deps,
                                  int32_t ndeps);
+/* The same for a system compiled in the caller's translation unit: `device_fn` is the device address of
+ * an mdr::ecs::NodeFn (include/madrona/b200/ecs_device.cuh) -- the whole row loop of the node for one
+ * world, systems inlined. Needs mdr_ecs_set_step_launcher: a device function can only be called from a
+ * kernel of its own module (the reference links user code and megakernel into one cubin at run time,
+ * src/mw/cuda_exec.cpp:553-818; here they are compiled together ahead of time). */
+int32_t mdr_ecs_add_parallel_for_fn(mdr_ecs *e, const void *device_fn, const int32_t *comps, int32_t n,
+                                    const int32_t *deps, int32_t ndeps);
+/* Launches the caller's instantiation of mdr::ecs::ecsGraphKernel over nodes [first_node, last_node)
+ * on `stream`; called while the run graph is captured. Returns MDR_OK. */
+typedef int32_t (*mdr_ecs_launch_fn)(const void *device_descriptor, int32_t first_node, int32_t last_node,
+                                     int32_t num_worlds, void *stream, void *user);
+int32_t mdr_ecs_set_step_launcher(mdr_ecs *e, mdr_ecs_launch_fn fn, void *user);
+/* RigidBodyPhysicsSystem::setup*Tasks as ONE node: the rigid-body step kernel runs on the archetype's
+ * own columns between the megakernel launches of the nodes before and after it. The physics object is
+ * attached after mdr_ecs_build (it needs the column addresses): mdr_phys_create_on_ecs. */
+int32_t mdr_ecs_add_physics(mdr_ecs *e, const int32_t *deps, int32_t ndeps);
+int32_t mdr_ecs_attach_physics(mdr_ecs *e, int32_t node, mdr_phys *p);
+int32_t mdr_phys_create_on_ecs(const mdr_phys_config *cfg, const mdr_object *objs, int32_t num_objs,
+                               const float *verts, const uint32_t *poly_words, mdr_ecs *e, int32_t arch,
+                               mdr_phys **out);
+/* Context::tmpAlloc arena (src/core/state.cpp:83-127) and per-world user data (WorldT, Context::data()):
+ * bytes per world, before mdr_ecs_build. */
+int32_t mdr_ecs_set_tmp_bytes(mdr_ecs *e, int32_t bytes_per_world);
+int32_t mdr_ecs_set_world_data_bytes(mdr_ecs *e, int32_t bytes_per_world);
+/* For kernels the caller launches itself on mdr_ecs_stream (world constructors): the device-side
+ * descriptor (const mdr::ecs::EcsDev *), and the note that tables changed (exports are refreshed). */
+const void *mdr_ecs_device_descriptor(mdr_ecs *e);
+int32_t mdr_ecs_num_worlds(mdr_ecs *e);
+int32_t mdr_ecs_tables_written(mdr_ecs *e);
 /* ClearTmpNode<Archetype>, ResetTmpAllocNode (include/madrona/taskgraph.inl:83-101) */
 int32_t mdr_ecs_add_clear_tmp(mdr_ecs *e, int32_t arch, const int32_t *deps, int32_t ndeps);
 int32_t mdr_ecs_add_reset_tmp_alloc(mdr_ecs *e, const int32_t *deps, int32_t ndeps);
@@ -303,6 +351,7 @@ int32_t mdr_ecs_script(mdr_ecs *e, const mdr_script_op *ops, const int32_t *offs
 int32_t mdr_ecs_write_column(mdr_ecs *e, int32_t arch, int32_t col, int32_t rows, const void *host);
 int32_t mdr_ecs_read_column(mdr_ecs *e, int32_t arch, int32_t col, int32_t rows, void *host);
 int32_t mdr_ecs_row_counts(mdr_ecs *e, int32_t arch, int32_t *host);
+int32_t mdr_ecs_num_components(mdr_ecs *e);     /* registered so far, Entity included */
 int32_t mdr_ecs_num_archetypes(mdr_ecs *e);
 int32_t mdr_ecs_num_columns(mdr_ecs *e, int32_t arch);
 int32_t mdr_ecs_column_bytes(mdr_ecs *e, int32_t arch, int32_t col);
