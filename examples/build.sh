@@ -5,7 +5,7 @@
 set -e
 cd "$(dirname "$0")/.."
 LIBDIR=$PWD/gpu_ecs_madrona_b200
-for ex in simple_taskgraph/simple force_field/force_field; do
+for ex in simple_taskgraph/simple force_field/force_field churn/churn; do
   src=examples/$ex.cu
   out=examples/$(dirname $ex)/lib$(basename $ex)_world.so
   if [ ! -f "$out" ] || [ "$src" -nt "$out" ] || [ -n "$(find include -newer "$out" -type f | head -1)" ]; then

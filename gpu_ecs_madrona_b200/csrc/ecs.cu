@@ -542,7 +542,7 @@ int32_t mdr_ecs_set_tmp_bytes(mdr_ecs *e, int32_t bytes_per_world)
 {
     if (!e || bytes_per_world < 0) return MDR_EINVAL;
     if (e->built) return MDR_ESTATE;
-    e->tmp_bytes = (bytes_per_world + 15) / 16 * 16;
+    e->tmp_bytes = (bytes_per_world + 255) / 256 * 256;
     return MDR_OK;
 }
 
@@ -1070,7 +1070,7 @@ int32_t mdr_ecs_export_bytes_per_row(mdr_ecs *e, int32_t slot)
 // constructor do, expressed through the C ABI above --------------------------------
 int32_t mdr_app_setup(mdr_ecs *e, int32_t app, const int32_t *params, int32_t nparams)
 {
-    if (!e || app < 0 || app >= MDR_NUM_APPS) return MDR_EINVAL;
+    if (!e || app < 0 || app >= MDR_APP_CHURN) return MDR_EINVAL;
     if (e->built) return MDR_ESTATE;
     auto P = [&](int i, int32_t dflt) { return params && i < nparams ? params[i] : dflt; };
     using namespace mdr::ecs::apps;

@@ -6,7 +6,7 @@ include/madrona_b200_apps.h; this file only makes input data (numpy, host side).
 """
 import numpy as np
 
-APP_SCRIPT, APP_TASKGRAPH, APP_FANOUT, APP_FVS = range(4)
+APP_SCRIPT, APP_TASKGRAPH, APP_FANOUT, APP_FVS, APP_CHURN = range(5)   # churn: out-of-tree world (examples/churn)
 APP_NAMES = {APP_SCRIPT: "script", APP_TASKGRAPH: "simple_taskgraph", APP_FANOUT: "simple_jobs_fanout",
              APP_FVS: "fantasy_vs"}
 DEFAULT_PARAMS = {APP_SCRIPT: [1], APP_TASKGRAPH: [100], APP_FANOUT: [100], APP_FVS: [50, 200]}

@@ -71,6 +71,11 @@ def bind(lib):
     lib.mdr_phys_write_column.argtypes = [vp, i32, vp]
     lib.mdr_phys_read_column.argtypes = [vp, i32, vp]
     lib.mdr_phys_flag_rebuild.argtypes = [vp]
+    if hasattr(lib, "mdr_phys_reset_worlds"):
+        lib.mdr_phys_reset_worlds.argtypes = [vp, vp, i32]
+        lib.mdr_phys_write_world_column.argtypes = [vp, i32, i32, i32, vp]
+        lib.mdr_phys_read_world_column.argtypes = [vp, i32, i32, i32, vp]
+        lib.mdr_phys_set_world_rows.argtypes = [vp, i32, i32]
     lib.mdr_phys_set_joints.argtypes = [vp, i32, vp, vp]
     lib.mdr_phys_step.argtypes = [vp, i32]
     lib.mdr_phys_step_async.argtypes = [vp, i32]
@@ -251,6 +256,23 @@ class PhysExecutor:
 
     def flag_rebuild(self):
         self._check(self.lib.mdr_phys_flag_rebuild(self.h), "flag_rebuild")
+
+    def reset_worlds(self, worlds):
+        """RigidBodyPhysicsSystem::reset of the listed worlds: only their BVHs are rebuilt before the next step."""
+        w = np.ascontiguousarray(worlds, np.int32)
+        self._check(self.lib.mdr_phys_reset_worlds(self.h, w.ctypes.data, len(w)), "reset_worlds")
+
+    def write_world(self, col, world, arr):
+        """One world's rows of a column ([rows, ...] of the column's element type)."""
+        a = np.ascontiguousarray(arr)
+        rows = a.nbytes // COL_BYTES[col]
+        self._check(self.lib.mdr_phys_write_world_column(self.h, col, world, rows, a.ctypes.data), "write_world_column")
+
+    def read_world(self, col, world, rows=None):
+        rows = self.N if rows is None else rows
+        out = np.empty((rows, COL_BYTES[col]), np.uint8)
+        self._check(self.lib.mdr_phys_read_world_column(self.h, col, world, rows, out.ctypes.data), "read_world_column")
+        return out
 
     def probe_step(self, world, max_pairs=4096):
         S, MC = self.scene.num_substeps, self.scene.max_contacts

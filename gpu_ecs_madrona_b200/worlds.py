@@ -49,6 +49,31 @@ class SimpleTaskgraphWorld:
             self.h = None
 
 
+class ChurnWorld:
+    """examples/churn/churn.cu: immediate-mode makeEntityNow / destroyEntityNow churn."""
+
+    def __init__(self, num_worlds, num_spawners=24, max_bullets=640, first_world=0):
+        lib = _load("churn/libchurn_world.so")
+        lib.churn_create.restype = C.c_void_p
+        lib.churn_create.argtypes = [C.c_int32] * 4
+        lib.churn_run.argtypes = [C.c_void_p, C.c_int32]
+        lib.churn_ecs.restype = C.c_void_p
+        lib.churn_ecs.argtypes = [C.c_void_p]
+        lib.churn_destroy.argtypes = [C.c_void_p]
+        self.lib = lib
+        self.h = lib.churn_create(num_worlds, num_spawners, max_bullets, first_world)
+        self.ecs = EcsRegistry.attach(lib.churn_ecs(self.h), num_worlds)
+
+    def run(self, steps=1):
+        self.lib.churn_run(self.h, steps)
+
+    def close(self):
+        if self.h:
+            self.ecs.close()
+            self.lib.churn_destroy(self.h)
+            self.h = None
+
+
 class ForceFieldWorld:
     """examples/force_field/force_field.cu: a scenes.Scene stepped as forceSystem -> physics -> obsSystem."""
     NUM_PHYS_COLS = 13

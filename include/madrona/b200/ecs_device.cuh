@@ -356,11 +356,12 @@ struct Context {
         idRelease(nodes, ws->ids, ws->ids.cache, e.id, e.gen);
         __threadfence_block();
     }
-    // Context::tmpAlloc: 16-byte aligned bytes from the world's arena, valid until the next
-    // ResetTmpAllocNode; nullptr (and kErrTmpAllocOverflow) when the arena is full.
+    // Context::tmpAlloc: bytes from the world's arena in 256-byte grains (TmpAllocator::alloc rounds the
+    // same way, src/core/state.cpp:95-115), valid until the next ResetTmpAllocNode; nullptr (and
+    // kErrTmpAllocOverflow) when the arena is full.
     __device__ __forceinline__ void *tmpAlloc(uint64_t num_bytes) const
     {
-        const int32_t need = (int32_t)((num_bytes + 15u) & ~(uint64_t)15u);
+        const int32_t need = (int32_t)((num_bytes + 255u) & ~(uint64_t)255u);
         const int32_t at = atomicAdd(&ws->tmp_used, need);
         if (at + need > E->tmp_bytes) {
             atomicSub(&ws->tmp_used, need);

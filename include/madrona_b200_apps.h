@@ -23,7 +23,10 @@
 #define MDR_APP_FN static inline
 #endif
 
-enum { MDR_APP_SCRIPT = 0, MDR_APP_TASKGRAPH = 1, MDR_APP_FANOUT = 2, MDR_APP_FVS = 3, MDR_NUM_APPS = 4 };
+enum { MDR_APP_SCRIPT = 0, MDR_APP_TASKGRAPH = 1, MDR_APP_FANOUT = 2, MDR_APP_FVS = 3,
+       /* churn: not a built-in world of the library -- examples/churn/churn.cu (out of tree) and the
+        * reference-driven harness only: any number of makeEntityNow / destroyEntityNow per invocation */
+       MDR_APP_CHURN = 4, MDR_NUM_APPS = 5 };
 
 /* ---- component payloads (byte layouts shared by all three sides) ---------- */
 typedef struct { float x, y, z; } mdr_vec3;                 /* Position, 12 B  */
@@ -82,6 +85,17 @@ MDR_APP_FN void mdr_tg_clamp(mdr_vec3 *p)   /* simple.cpp:22-35 */
     p->x = mdr_clampf(p->x, MDR_BOUNDS_MIN_X, MDR_BOUNDS_MAX_X);
     p->y = mdr_clampf(p->y, MDR_BOUNDS_MIN_Y, MDR_BOUNDS_MAX_Y);
     p->z = mdr_clampf(p->z, MDR_BOUNDS_MIN_Z, MDR_BOUNDS_MAX_Z);
+}
+
+/* ================= churn (immediate-mode structural calls) ================== */
+/* pairs of bullets a spawner makes this tick (0..2) and the life of bullet k of the pair list */
+MDR_APP_FN int32_t mdr_churn_pairs(uint32_t world, uint32_t tick, int32_t spawner_id)
+{
+    return (int32_t)(mdr_hash4(world, tick, (uint32_t)spawner_id, 0x51u) % 3u);
+}
+MDR_APP_FN int32_t mdr_churn_life(uint32_t world, uint32_t tick, int32_t spawner_id, int32_t k)
+{
+    return 1 + (int32_t)(mdr_hash4(world, tick, (uint32_t)spawner_id, 0x100u + (uint32_t)k) % 6u);
 }
 
 /* ================= config 2: fan-out ======================================= */

@@ -350,7 +350,7 @@ const char *eorc_kind(void) { return "port"; }
 
 void *eorc_create(int32_t app, int32_t num_worlds, int32_t first_world, const int32_t *params, int32_t nparams)
 {
-    if (app < 0 || app >= MDR_NUM_APPS || num_worlds <= 0) return nullptr;
+    if (app < 0 || app >= MDR_APP_CHURN || num_worlds <= 0) return nullptr;   // churn: compiled reference only
     Handle *h = new Handle;
     h->app = app;
     h->params.assign(params, params + (params ? nparams : 0));

@@ -61,6 +61,11 @@ struct CompA { uint32_t v; };
 struct CompB { float v[3]; };
 struct alignas(16) CompC { float v[4]; };
 struct ScriptSingleton { int32_t v; };
+struct Seed { uint32_t spawned; uint32_t checksum; };
+struct Life { int32_t ticks; };
+struct Buddy { Entity e; };
+struct DeadRef { Entity e; Entity buddy; };
+struct ChurnTick { uint32_t tick; };
 
 // ---- archetypes ----
 struct Sphere : Archetype<PositionT<1>, RotationT<1>> {};
@@ -74,6 +79,9 @@ struct ArchX : Archetype<CompA> {};
 struct ArchY : Archetype<CompA, CompB> {};
 struct ArchZ : Archetype<CompA, CompB, CompC> {};
 struct ArchT : Archetype<CompA> {};
+struct Spawner : Archetype<Seed> {};
+struct Bullet : Archetype<Life, Buddy> {};
+struct DeadTmp : Archetype<DeadRef, SortKeyT<4>> {};
 
 struct Sim;
 class Engine : public CustomContext<Engine, Sim> {
@@ -195,6 +203,45 @@ inline void fvsRespawn(Engine &ctx, CleanupEntity &c)
 }
 inline void fvsTickSystem(Engine &, GameState &g) { g.tick += 1; }
 
+// =========================== churn ==========================================
+// Any number of makeEntityNow / destroyEntityNow per invocation, the returned Entity used at once
+// (getUnsafe), tmpAlloc scratch, stale handles: the world of examples/churn/churn.cu, statement for statement.
+inline void churnSpawn(Engine &ctx, Entity &e, Seed &s)
+{
+    const uint32_t world = ctx.data().world, tick = ctx.getSingleton<ChurnTick>().tick;
+    const int32_t pairs = mdr_churn_pairs(world, tick, e.id);
+    uint32_t *scratch = (uint32_t *)ctx.tmpAlloc(sizeof(uint32_t) * (2 * (uint64_t)pairs + 1));
+    for (int32_t k = 0; k < pairs; k++) {
+        Entity a = ctx.makeEntityNow<Bullet>();
+        Entity b = ctx.makeEntityNow<Bullet>();
+        ctx.getUnsafe<Life>(a).ticks = mdr_churn_life(world, tick, e.id, 2 * k);
+        ctx.getUnsafe<Life>(b).ticks = mdr_churn_life(world, tick, e.id, 2 * k + 1);
+        ctx.getUnsafe<Buddy>(a).e = b;
+        ctx.getUnsafe<Buddy>(b).e = a;
+        scratch[2 * k] = (uint32_t)a.id;
+        scratch[2 * k + 1] = (uint32_t)b.id;
+    }
+    uint32_t sum = 0;
+    for (int32_t k = 0; k < 2 * pairs; k++) sum = sum * 31u + scratch[k];
+    s.spawned += 2u * (uint32_t)pairs;
+    s.checksum ^= sum;
+}
+inline void churnAge(Engine &, Life &l) { l.ticks -= 1; }
+inline void churnMark(Engine &ctx, Entity &e, Life &l, Buddy &b)
+{
+    if (l.ticks > 0) return;
+    Loc at = ctx.getLoc(e);
+    Loc t = ctx.makeTemporary<DeadTmp>();
+    ctx.getUnsafe<DeadRef>(t) = DeadRef { e, b.e };
+    ctx.getUnsafe<SortKeyT<4>>(t).key = (uint32_t)at.row;
+}
+inline void churnReap(Engine &ctx, DeadRef &d)
+{
+    ctx.destroyEntityNow(d.e);
+    ctx.destroyEntityNow(d.buddy);     // often stale already: the reference returns on an invalid Loc
+}
+inline void churnTickSystem(Engine &, ChurnTick &t) { t.tick += 1; }
+
 template <auto Fn, typename... Cs> using PF = ParallelForNode<Engine, Fn, Cs...>;
 
 void setupWorld(Handle *h, World &w, uint32_t world_idx, const int32_t *params, int32_t nparams)
@@ -255,6 +302,20 @@ void setupWorld(Handle *h, World &w, uint32_t world_idx, const int32_t *params, 
                 archId<StateManager::SingletonArchetype<GameState>>() };
         h->exports = { { archId<Dragon>(), 2, 4 }, { archId<Knight>(), 1, 12 } };
         break;
+    case MDR_APP_CHURN:
+        reg.registerComponent<Seed>();
+        reg.registerComponent<Life>();
+        reg.registerComponent<Buddy>();
+        reg.registerComponent<DeadRef>();
+        reg.registerComponent<SortKeyT<4>>();
+        reg.registerArchetype<Spawner>();
+        reg.registerArchetype<Bullet>();
+        reg.registerArchetype<DeadTmp>();
+        reg.registerSingleton<ChurnTick>();
+        ids = { archId<Spawner>(), archId<Bullet>(), archId<DeadTmp>(),
+                archId<StateManager::SingletonArchetype<ChurnTick>>() };
+        h->exports = { { archId<Spawner>(), 1, 8 }, { archId<Bullet>(), 1, 4 } };
+        break;
     default:
         abort();
     }
@@ -301,6 +362,20 @@ void setupWorld(Handle *h, World &w, uint32_t world_idx, const int32_t *params, 
         auto n5 = b.addToGraph<PF<fvsRespawn, CleanupEntity>>({ n4 });
         auto n6 = b.addToGraph<ClearTmpNode<CleanupTracker>>({ n5 });
         b.addToGraph<PF<fvsTickSystem, GameState>>({ n6 });
+    } break;
+    case MDR_APP_CHURN: {
+        ctx.getSingleton<ChurnTick>().tick = 0;
+        for (int i = 0, n = P(0, 24); i < n; i++) {
+            Entity s = ctx.makeEntityNow<Spawner>();
+            ctx.getUnsafe<Seed>(s) = Seed { 0u, 0u };
+        }
+        auto n0 = b.addToGraph<PF<churnSpawn, Entity, Seed>>({});
+        auto n1 = b.addToGraph<PF<churnAge, Life>>({ n0 });
+        auto n2 = b.addToGraph<PF<churnMark, Entity, Life, Buddy>>({ n1 });
+        auto n3 = b.addToGraph<PF<churnReap, DeadRef>>({ n2 });
+        auto n4 = b.addToGraph<ClearTmpNode<DeadTmp>>({ n3 });
+        auto n5 = b.addToGraph<ResetTmpAllocNode>({ n4 });
+        b.addToGraph<PF<churnTickSystem, ChurnTick>>({ n5 });
     } break;
     }
     // Builder::build() dereferences the first staged node: no graph for the node-less script app.

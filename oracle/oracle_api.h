@@ -106,6 +106,8 @@ int32_t orc_probe_step(void *h, int32_t world, orc_probe *out);
 /* Flags a BVH rebuild for every world (RigidBodyPhysicsSystem::reset semantics
  * without clearing leaves: bvh.rebuildOnUpdate()). */
 void orc_flag_rebuild(void *h);
+/* The same for one world (an episode reset of a subset of worlds). */
+void orc_flag_rebuild_world(void *h, int32_t world);
 /* Half-edge mesh tables the checker built for object obj (for pinning our own
  * HalfEdgeMesh construction): returns counts, copies up to cap entries. */
 int32_t orc_get_hull(void *h, int32_t obj,

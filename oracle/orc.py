@@ -99,6 +99,7 @@ class Oracle:
         L.orc_probe_step.argtypes = [C.c_void_p, C.c_int32, C.c_void_p]
         L.orc_probe_step.restype = C.c_int32
         L.orc_flag_rebuild.argtypes = [C.c_void_p]
+        L.orc_flag_rebuild_world.argtypes = [C.c_void_p, C.c_int32]
         L.orc_get_hull.argtypes = [C.c_void_p, C.c_int32] + [C.c_void_p] * 5
         L.orc_indeterminate.argtypes = [C.c_void_p, C.c_void_p]
         L.orc_trace_rays.argtypes = [C.c_void_p, C.c_int32, C.c_int32] + [C.c_void_p] * 6
@@ -132,8 +133,12 @@ class Oracle:
     def step(self, num_steps=1, num_threads=1):
         self.lib.orc_step(self.h, num_steps, num_threads)
 
-    def flag_rebuild(self):
-        self.lib.orc_flag_rebuild(self.h)
+    def flag_rebuild(self, worlds=None):
+        if worlds is None:
+            self.lib.orc_flag_rebuild(self.h)
+        else:
+            for w in worlds:
+                self.lib.orc_flag_rebuild_world(self.h, int(w))
 
     def read(self, col):
         W, N = self.scene.num_worlds, self.scene.bodies_per_world

@@ -1270,6 +1270,8 @@ void orc_flag_rebuild(void *h)
     for (World &w : ((Sim *)h)->worlds) w.force_rebuild = true;
 }
 
+void orc_flag_rebuild_world(void *h, int32_t world) { ((Sim *)h)->worlds[world].force_rebuild = true; }
+
 void orc_set_joints(void *h, int32_t max_joints, const int32_t *counts, const orc_joint *joints)
 {
     Sim *s = (Sim *)h;

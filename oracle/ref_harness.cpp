@@ -216,6 +216,12 @@ void orc_flag_rebuild(void *hp)
     }
 }
 
+// RigidBodyPhysicsSystem::reset is per world: only this context's BVH is flagged (physics.cpp:1038-1043).
+void orc_flag_rebuild_world(void *hp, int32_t world)
+{
+    ((Handle *)hp)->worlds[world].ctx->getSingleton<broadphase::BVH>().rebuildOnUpdate();
+}
+
 // applyJointAxisConstraint (src/physics/physics.cpp:529-531) prints both axes of
 // every hinge in every substep: stdout goes to /dev/null while such worlds step.
 struct QuietStdout {

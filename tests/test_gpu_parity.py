@@ -236,3 +236,36 @@ def test_step_io_pipeline_matches_plain_step(cuda_lib, chunks):
             got = arr.view(np.float32).reshape(sc.num_worlds, b.row_stride(), -1)[:, :sc.bodies_per_world]
             assert np.array_equal(bits(got), bits(want)), (st, c)
     assert_state_equal(b.state(), a.state(), None, "after pipelined steps")
+
+
+def test_partial_reset_rebuilds_only_the_named_worlds(cuda_lib, port_oracle):
+    """An RL episode reset of a subset of worlds (RigidBodyPhysicsSystem::reset is per world,
+    physics.cpp:1038-1043): their poses go back to the start and only THEIR BVHs are rebuilt; every
+    other world keeps its grown slot boxes and traversal order, hence its pair order and its bits."""
+    sc = scenes.collisions64(40)
+    o = port_oracle.Oracle(sc, "port")
+    e = phys.PhysExecutor(sc)
+    o.step(25, 8)
+    e.run(25)
+    assert_state_equal(e.state(), o.state(), None, "before the reset")
+    subset = [1, 5, 6, 7, 20, 39]
+    vel0 = np.ascontiguousarray(sc.vel, np.float32)
+    for col, init in ((phys.COL_POSITION, sc.pos), (phys.COL_ROTATION, sc.rot), (phys.COL_VELOCITY, vel0)):
+        full = o.read_f32(col).copy()
+        for w in subset:
+            full[w] = np.asarray(init, np.float32)[w].reshape(full[w].shape)
+            e.write_world(col, w, np.asarray(init, np.float32)[w])
+        o.write(col, full)
+    o.flag_rebuild(subset)
+    e.reset_worlds(subset)
+    slot_before = e.read_bvh()[0]
+    for st in range(30):
+        o.step(1, 8)
+        e.run()
+        assert_state_equal(e.state(), o.state(), None, f"step {st} after the reset")
+    # a world that was not reset still carries boxes at least as large as before (grow-only)
+    slot_after = e.read_bvh()[0]
+    others = [w for w in range(40) if w not in subset]
+    assert (slot_after[others][..., 3:] >= slot_before[others][..., 3:]).all()
+    assert (slot_after[others][..., :3] <= slot_before[others][..., :3]).all()
+    assert e.lib.mdr_phys_reset_worlds(e.h, np.array([40], np.int32).ctypes.data, 1) == phys.MDR_EINVAL

@@ -73,3 +73,27 @@ def test_hull_tables_match_reference(port_oracle, ref_oracle):
         for k in ("half_edges", "edges", "polys"):
             assert np.array_equal(a[k], b[k]), k
         assert np.array_equal(bits(a["planes"]), bits(b["planes"]))
+
+
+def test_port_matches_reference_across_a_partial_reset():
+    """Per-world reset (bvh.rebuildOnUpdate() of some contexts only): the restatement keeps its
+    per-world rebuild flag in step with the compiled reference."""
+    from oracle import orc
+    if not orc.available("reference"):
+        pytest.skip("compiled reference not built here")
+    from gpu_ecs_madrona_b200 import scenes
+    sc = scenes.collisions64(12)
+    a, b = orc.Oracle(sc, "port"), orc.Oracle(sc, "reference")
+    subset = [0, 3, 4, 11]
+    for o in (a, b):
+        o.step(20, 4)
+        for col, init in ((1, sc.pos), (2, sc.rot), (4, np.ascontiguousarray(sc.vel, np.float32))):
+            full = o.read_f32(col).copy()
+            for w in subset:
+                full[w] = np.asarray(init, np.float32)[w].reshape(full[w].shape)
+            o.write(col, full)
+        o.flag_rebuild(subset)
+        o.step(25, 4)
+    for x, y in zip(a.state(), b.state()):
+        assert np.array_equal(x.view(np.uint32), y.view(np.uint32))
+    a.close(); b.close()
