@@ -956,6 +956,7 @@ int32_t mdr_ecs_step(mdr_ecs *e, int32_t num_steps)
 }
 
 void *mdr_ecs_stream(mdr_ecs *e) { return e ? (void *)e->stream : nullptr; }
+void *mdr_ecs_done_event(mdr_ecs *e) { return e ? (void *)e->ev1 : nullptr; }
 
 float mdr_ecs_step_ms(mdr_ecs *e, int32_t *steps)
 {

@@ -501,6 +501,14 @@ void *mdr_host_alloc(uint64_t bytes)
 
 void mdr_host_free(void *ptr) { if (ptr) cudaFreeHost(ptr); }
 
+void *mdr_phys_done_event(mdr_phys *p) { return p ? (void *)p->ev1 : nullptr; }
+
+int32_t mdr_stream_wait_event(void *stream, void *event)
+{
+    if (!event) return MDR_EINVAL;
+    return cudaStreamWaitEvent((cudaStream_t)stream, (cudaEvent_t)event, 0) == cudaSuccess ? MDR_OK : MDR_ESTATE;
+}
+
 void *mdr_phys_column_ptr(mdr_phys *p, int32_t col)
 {
     if (!p) return nullptr;

@@ -323,6 +323,20 @@ class PhysExecutor:
         shape = (self.W, self.row_stride(), COL_BYTES[col] // np.dtype(dtype).itemsize)
         return as_torch(self.column_ptr(col), shape, dtype, self.gpu_id, owner=self)
 
+    def tensor(self, col, dtype=np.float32):
+        """madrona_python.Tensor of an exported column (what Executor::getExported is wrapped in)."""
+        from .tensor import as_tensor
+        shape = (self.W, self.row_stride(), COL_BYTES[col] // np.dtype(dtype).itemsize)
+        return as_tensor(self.column_ptr(col), shape, dtype, self.gpu_id)
+
+    def cuda_sync(self):
+        """madrona_python.CudaSync on the executor's stream: .wait(torch.cuda.current_stream().cuda_stream)
+        orders a consumer's stream after the steps enqueued so far (run_async), without a host sync."""
+        from .tensor import cuda_sync
+        self.lib.mdr_phys_done_event.restype = C.c_void_p
+        self.lib.mdr_phys_done_event.argtypes = [C.c_void_p]
+        return cuda_sync(self.lib.mdr_phys_done_event(self.h))
+
     def row_stride(self):
         return int(self.lib.mdr_phys_row_stride(self.h))
 

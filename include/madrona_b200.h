@@ -254,6 +254,11 @@ int32_t mdr_load_hull_obj(const char *obj_text, int64_t num_bytes, float *verts,
 int32_t mdr_load_hull_obj_file(const char *path, float *verts, int32_t *num_verts,
                                uint32_t *poly_words, int32_t *num_poly_words, float aabb[6],
                                char *err, int32_t err_cap);
+/* Stream-ordered hand-off to a consumer on another stream (py::CudaSync of the reference,
+ * include/madrona/python.hpp:23-40, src/python/utils.cpp:15-44): the event recorded after the last step
+ * enqueued on the executor's stream, and "make `stream` wait for `event`" (no host synchronisation). */
+void *mdr_phys_done_event(mdr_phys *p);
+int32_t mdr_stream_wait_event(void *stream, void *event);
 /* Launch geometry chosen at creation: [0] blocks, [1] threads per block,
  * [2] dynamic shared memory bytes per block, [3] resident blocks per SM,
  * [4] threads per world, [5] worlds per block. */
@@ -368,6 +373,7 @@ int32_t mdr_ecs_step(mdr_ecs *e, int32_t num_steps);
 int32_t mdr_ecs_step_async(mdr_ecs *e, int32_t num_steps);
 int32_t mdr_ecs_sync(mdr_ecs *e);
 void *mdr_ecs_stream(mdr_ecs *e);
+void *mdr_ecs_done_event(mdr_ecs *e);
 float mdr_ecs_step_ms(mdr_ecs *e, int32_t *steps);
 int32_t mdr_ecs_launches_per_step(mdr_ecs *e);
 /* Archetype column map, SURVEY 8 row a2: StaticIntegerMap<128> (include/madrona/hashmap.hpp:26-58, hashmap.inl:
