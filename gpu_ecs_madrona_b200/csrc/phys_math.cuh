@@ -82,6 +82,12 @@ MDR_HD Q4 operator*(Q4 a, Q4 b)
                (a.w * b.z + a.x * b.y - a.y * b.x + a.z * b.w));
 }
 MDR_HD Q4 qinv(Q4 q) { return mk4(q.w, -q.x, -q.y, -q.z); }
+// math.hpp:550-561
+MDR_HD Q4 qangleAxis(float angle, V3 normal)
+{
+    const float coshalf = cosf(angle / 2.f), sinhalf = sinf(angle / 2.f);
+    return mk4(coshalf, normal.x * sinhalf, normal.y * sinhalf, normal.z * sinhalf);
+}
 // math.hpp:500-520
 MDR_HD Q4 qnormalize(Q4 q)
 {

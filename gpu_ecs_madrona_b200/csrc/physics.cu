@@ -501,6 +501,24 @@ void *mdr_host_alloc(uint64_t bytes)
 
 void mdr_host_free(void *ptr) { if (ptr) cudaFreeHost(ptr); }
 
+// The step's quaternion arithmetic (csrc/phys_math.cuh, the host instantiation of the same source) for the
+// reference's known-answer tests (tests/math.cpp:26-51): op 0 angleAxis(a[0], a[1..3]), 1 a * b, 2 rotateVec(a, b[0..2]),
+// 3 normalize(a), 4 inv(a).
+int32_t mdr_math_quat(int32_t op, const float *a, const float *b, float *out)
+{
+    if (!a || !out || op < 0 || op > 4 || ((op == 1 || op == 2) && !b)) return MDR_EINVAL;
+    Q4 r = mk4(0.f, 0.f, 0.f, 0.f);
+    switch (op) {
+    case 0: r = qangleAxis(a[0], mk3(a[1], a[2], a[3])); break;
+    case 1: r = mk4(a[0], a[1], a[2], a[3]) * mk4(b[0], b[1], b[2], b[3]); break;
+    case 2: { V3 v = rotate(mk4(a[0], a[1], a[2], a[3]), mk3(b[0], b[1], b[2])); r = mk4(0.f, v.x, v.y, v.z); } break;
+    case 3: r = qnormalize(mk4(a[0], a[1], a[2], a[3])); break;
+    case 4: r = qinv(mk4(a[0], a[1], a[2], a[3])); break;
+    }
+    out[0] = r.w; out[1] = r.x; out[2] = r.y; out[3] = r.z;
+    return MDR_OK;
+}
+
 void *mdr_phys_done_event(mdr_phys *p) { return p ? (void *)p->ev1 : nullptr; }
 
 int32_t mdr_stream_wait_event(void *stream, void *event)

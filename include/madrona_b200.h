@@ -254,6 +254,10 @@ int32_t mdr_load_hull_obj(const char *obj_text, int64_t num_bytes, float *verts,
 int32_t mdr_load_hull_obj_file(const char *path, float *verts, int32_t *num_verts,
                                uint32_t *poly_words, int32_t *num_poly_words, float aabb[6],
                                char *err, int32_t err_cap);
+/* Quaternion arithmetic of the step (math::Quat, include/madrona/math.hpp:478-730), host evaluation of the
+ * library's own source, for the reference's known-answer tests (tests/math.cpp:26-51). op 0: angleAxis(a[0],
+ * axis a[1..3]); 1: a * b; 2: a.rotateVec(b[0..2]) (in out[1..3]); 3: normalize; 4: inv. Quats are w,x,y,z. */
+int32_t mdr_math_quat(int32_t op, const float *a, const float *b, float *out);
 /* Stream-ordered hand-off to a consumer on another stream (py::CudaSync of the reference,
  * include/madrona/python.hpp:23-40, src/python/utils.cpp:15-44): the event recorded after the last step
  * enqueued on the executor's stream, and "make `stream` wait for `event`" (no host synchronisation). */

@@ -1,7 +1,10 @@
 """TEST INFRASTRUCTURE ONLY: numpy restatement of the reference's archetype sort
-(src/mw/device/sort_archetype.cpp:960-1392). PARITY UNPINNED: that file is an orphan of the
-snapshot (no build target compiles it, it needs CUB and a GPU), and the reference holds no test
-or golden vector for it; this restates its specification:
+(src/mw/device/sort_archetype.cpp:960-1392). That file is an orphan of the snapshot (no build target
+compiles it, it needs CUB and a GPU) and the reference holds no test or golden vector for it.
+PARITY PINNED on the third-party algorithm it adapts: cub::DeviceRadixSort::SortPairs (the CUB of CUDA 12.9;
+the reference's vendored external/cub @ 09686d2 does not compile against this toolkit), run on a B200 by
+oracle/_ref/cub_sort_ref; keys -> (sorted keys, permutation) fixtures in tests/golden/sort_cub.npz
+(tests/golden/make_sort_golden.py), checked in tests/test_table_sort.py. What is restated:
   * sortSetup / addToGraph :1290-1299: passes = ceil(bits(num_worlds + 1) / 8) for a WorldID
     sort, else 4;
   * histogram + binScan + onesweep per pass :1083-1214: a least-significant-digit radix sort of

@@ -105,6 +105,36 @@ def test_state_indexing_like_reference_test():
     U.assert_same(U.snapshot(ck), gpu_snapshot(ex, A.APP_SCRIPT), A.APP_SCRIPT)
 
 
+def test_state_indexing_at_the_reference_scale():
+    """tests/state.cpp:38-128 (State.Indexing) at its own size: 1 000 000 entities created, every 10th destroyed,
+    refilled to 2 000 000, every 5th destroyed -- one world, every id, generation, row and free-list link
+    against the checker."""
+    from gpu_ecs_madrona_b200.ecs import EcsExecutor
+    N = 1_000_000
+    ops = np.zeros(N + N // 10 + N + N // 10 + (2 * N) // 5, eorc.OP_DTYPE)
+    k = 0
+    def put(op, a, b):
+        nonlocal k
+        n = len(a)
+        ops["op"][k:k + n], ops["a"][k:k + n], ops["b"][k:k + n] = op, a, b
+        k += n
+    ar = np.arange
+    put(eorc.OP_CREATE, np.ones(N, np.int32), ar(N))
+    put(eorc.OP_DESTROY, ar(0, N, 10), 0)
+    put(eorc.OP_CREATE, np.ones(N + N // 10, np.int32), N + ar(N + N // 10))
+    put(eorc.OP_DESTROY, ar(0, 2 * N + N // 10, 5)[: (2 * N) // 5], 0)
+    assert k == len(ops)
+    cap = 2 * N + 64
+    ex = EcsExecutor(A.APP_SCRIPT, 1, [1, cap, 2 * N + N // 10 + 64])
+    ck = U.make_oracle(_kind(), A.APP_SCRIPT, 1, [1])
+    ex.script([ops])
+    ck.script(0, ops)
+    assert ex.row_counts()[0, 1] == 2 * N - (2 * N) // 5
+    U.assert_same(U.snapshot(ck), gpu_snapshot(ex, A.APP_SCRIPT), A.APP_SCRIPT)
+    ex.close()
+    ck.close()
+
+
 def test_capacity_overflow_is_reported():
     from gpu_ecs_madrona_b200.ecs import EcsExecutor
     from gpu_ecs_madrona_b200 import MadronaError

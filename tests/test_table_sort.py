@@ -113,3 +113,101 @@ def test_cuda_sort_full_size_properties(cuda_lib):
     first_payload = d_out[2][:rows, 0].cpu().numpy().view(np.uint32)
     assert np.array_equal(first_payload, (ids.cpu().numpy().astype(np.uint32) * np.uint32(2654435761)))
     s.close()
+
+
+# ---- pinned on cub::DeviceRadixSort::SortPairs (tests/golden/sort_cub.npz, generated on a B200 by
+# tests/golden/make_sort_golden.py through oracle/_ref/cub_sort_ref): the third-party algorithm the reference's
+# sort nodes adapt (src/mw/device/sort_archetype.cpp:960-1392) ------------------------------------------------
+import hashlib
+import os
+
+from tests.golden import make_sort_golden as msg
+
+CUB = np.load(os.path.join(os.path.dirname(__file__), "golden", "sort_cub.npz"))
+
+
+def _sha(a):
+    return np.frombuffer(hashlib.sha256(np.ascontiguousarray(a).tobytes()).digest(), np.uint8)
+
+
+def _check_against_cub(name, keys, sorted_keys, perm):
+    if name + "_perm" in CUB:
+        assert np.array_equal(keys, CUB[name + "_keys"]), "fixture keys"
+        assert np.array_equal(sorted_keys, CUB[name + "_sorted"]), name
+        assert np.array_equal(perm, CUB[name + "_perm"]), name
+    else:
+        assert np.array_equal(_sha(sorted_keys), CUB[name + "_sorted_sha"]), name
+        assert np.array_equal(_sha(np.asarray(perm, np.int32)), CUB[name + "_perm_sha"]), name
+
+
+def test_numpy_oracle_pinned_on_cub():
+    """oracle/sort_oracle.py (stable sort by the low end_bit bits) == CUB, keys and permutation, every fixture."""
+    for name, (keys, end_bit, _) in msg.cases().items():
+        assert int(CUB[name + "_end_bit"]) == end_bit
+        mask = np.uint32(0xFFFFFFFF if end_bit == 32 else (1 << end_bit) - 1)
+        perm = np.argsort(keys & mask, kind="stable").astype(np.int32)
+        _check_against_cub(name, keys, keys[perm], perm)
+        if len(keys) <= 5000:
+            assert np.array_equal(sort_oracle.lsd_reference(keys, end_bit // 8), perm)
+
+
+@pytest.mark.gpu
+def test_cuda_global_sort_pinned_on_cub(cuda_lib):
+    """mdr_sort_run on the fixture keys: sorted keys and the permutation (an iota payload column) == CUB."""
+    import torch
+    for name, (keys, end_bit, _) in msg.cases().items():
+        n = len(keys)
+        if n == 0:
+            continue
+        num_worlds = 0
+        if name.startswith("world_"):
+            num_worlds = int(name.split("_")[1].split("x")[0])
+            assert 8 * sort_oracle.num_passes(num_worlds) == end_bit
+        ent = np.stack([np.zeros(n, np.int32), np.arange(n, dtype=np.int32)], 1)
+        iota = np.arange(n, dtype=np.int32)
+        cols = [ent, keys.view(np.int32), iota]
+        s = table_sort.TableSort(n, [8, 4, 4], 1, num_worlds)
+        d_in = _device_columns(cols, torch)
+        d_out = [torch.empty_like(c) for c in d_in]
+        s.run(d_in, d_out, n)
+        _check_against_cub(name, keys, d_out[1].cpu().numpy().view(np.uint32), d_out[2].cpu().numpy())
+        s.close()
+
+
+@pytest.mark.gpu
+def test_megakernel_sort_node_pinned_on_cub(cuda_lib):
+    """The per-world SortArchetypeNode inside the task-graph megakernel (csrc ecs sortArchetype): one world per
+    fixture key set, sorted keys and permutation == CUB."""
+    from gpu_ecs_madrona_b200.ecs import EcsRegistry
+    names = [n for n, (k, e, full) in msg.cases().items() if full and e == 32 and 0 < len(k) <= 4097]
+    sets = [msg.cases()[n][0] for n in names]
+    cap = max(len(k) for k in sets)
+    r = EcsRegistry(len(sets))
+    key, pay = r.register_component(4), r.register_component(4)
+    arch = r.register_archetype([key, pay], cap)
+    r.sort_archetype(arch, key, remap_entities=True)
+    r.build()
+    keys = np.zeros((len(sets), cap), np.uint32)
+    iota = np.tile(np.arange(cap, dtype=np.int32), (len(sets), 1))
+    from oracle import eorc
+    ops = []
+    for w, k in enumerate(sets):
+        keys[w, :len(k)] = k
+        o = np.zeros(len(k), eorc.OP_DTYPE)
+        o["op"], o["a"] = eorc.OP_CREATE, arch
+        ops.append(o)
+    r.script(ops)                       # len(k) rows in world w (immediate-mode creates)
+    r.write_column_all(arch, 1, keys)
+    r.write_column_all(arch, 2, iota)
+    r.run(1)
+    got_k = r.read_column_all(arch, 1).view(np.uint32)[..., 0]
+    got_p = r.read_column_all(arch, 2).view(np.int32)[..., 0]
+    for w, (name, k) in enumerate(zip(names, sets)):
+        _check_against_cub(name, k, got_k[w, :len(k)], got_p[w, :len(k)])
+    # entities followed their rows: the id map points at the sorted positions
+    ents = r.read_column_all(arch, 0).view(np.int32)
+    for w, k in enumerate(sets[:3]):
+        a, b, gen, st = r.idmap(w)
+        ids = ents[w, :len(k), 1]
+        assert np.array_equal(b[ids], np.arange(len(k)))
+    r.close()
