@@ -111,11 +111,16 @@ def dist_env():
     return rank, world, local
 
 
-def cpu_baseline(steps, warmup, worlds_per_thread=256, kind=None):
+PREROLL = 60     # untimed steps before warm-up: the cubes have landed, contacts per world have plateaued
+
+
+def cpu_baseline(steps, warmup, worlds_per_thread=256, kind=None, preroll=PREROLL, min_seconds=1.5):
     """Times the reference's CPU implementation of the path on this host's cores:
     the unmodified reference compiled into oracle/_ref when it travelled here,
     else the oracle restatement. A bounded sample of the same workload: the same
-    per-world scene and the same step range, fewer worlds."""
+    per-world scene in the same regime (the same untimed pre-roll and warm-up), fewer
+    worlds, and at least `min_seconds` of timed wall clock (the settled scene is
+    stationary, so extra steps time the same work)."""
     from gpu_ecs_madrona_b200 import scenes
     from oracle import orc
     if kind is None:
@@ -129,15 +134,20 @@ def cpu_baseline(steps, warmup, worlds_per_thread=256, kind=None):
     worlds = max(cores, worlds // cores * cores)
     sc = scenes.collisions64(worlds)
     o = orc.Oracle(sc, kind)
-    o.step(warmup, cores)
+    o.step(preroll + warmup, cores)
+    timed = 0
     t0 = time.perf_counter()
-    o.step(steps, cores)
-    dt = time.perf_counter() - t0
+    while True:
+        o.step(steps, cores)
+        timed += steps
+        dt = time.perf_counter() - t0
+        if dt >= min_seconds:
+            break
     o.close()
-    return {"value": worlds * steps / dt, "unit": UNIT, "cores": cores, "kind": kind,
-            "sample": f"{worlds} worlds x {steps} steps after {warmup} warm-up steps (the same step range), "
-                      f"collisions-64, {cores} threads ({dt:.1f} s wall); worlds capped at 1024 by the "
-                      "reference's 48 GB address-space reservation per world"}, dt
+    return {"value": worlds * timed / dt, "unit": UNIT, "cores": cores, "kind": kind,
+            "sample": f"{worlds} worlds x {timed} steps after {preroll} pre-roll + {warmup} warm-up steps (settled regime, "
+                      f"as the GPU arm), collisions-64, {cores} threads ({dt:.1f} s wall); worlds capped at 1024 by the "
+                      "reference's 48 GB address-space reservation per world"}, dt / timed
 
 
 def mean_pairs_contacts(args, gpu):
@@ -147,7 +157,7 @@ def mean_pairs_contacts(args, gpu):
     from gpu_ecs_madrona_b200 import phys, scenes
     sc = scenes.collisions64(256, max_contacts=args.max_contacts)
     ex = phys.PhysExecutor(sc, gpu_id=gpu)
-    ex.run(args.warmup)
+    ex.run(args.preroll + args.warmup)
     ps, cs = [], []
     for _ in range(args.steps):
         ex.run(1)
@@ -158,14 +168,45 @@ def mean_pairs_contacts(args, gpu):
     return float(np.mean(ps)), float(np.mean(cs))
 
 
+def timed_window(scene, gpu, skip, steps, lib=None, **shape):
+    """Device-timed M world-steps/s of `steps` steps after `skip` untimed ones, fresh executor (sub-records)."""
+    from gpu_ecs_madrona_b200 import phys
+    ex = phys.PhysExecutor(scene, gpu_id=gpu, lib=lib, **shape)
+    ex.run(skip)
+    ex.kernel_ms()
+    ex.run_async(steps)
+    ex.sync()
+    ms, n = ex.kernel_ms()
+    ex.close()
+    return {"value": scene.num_worlds * 1e3 / ms, "unit": UNIT, "ms_per_step": ms, "steps": n, "after_steps": skip}
+
+
+def extra_records(args, sc, local, world, rank, shape):
+    """Sub-records of the line (rank 0 fills them; every rank runs the configs[4]-sized leg at N > 1)."""
+    import ctypes as C
+    from gpu_ecs_madrona_b200 import phys, scenes
+    out = {}
+    if rank == 0:
+        # the two regimes of the scene: the headline is the settled one whatever --steps / --warmup say
+        out["regimes"] = {"falling": dict(timed_window(sc, local, 5, 20, **shape), note="steps 5-25: a third of the cubes rest on the plane"),
+                          "settled": dict(timed_window(sc, local, args.preroll + 50, 20, **shape), note="steps 110-130")}
+        fma = os.path.join(os.path.dirname(phys.LIB_PATH), "libmadrona_b200_fma.so")
+        if os.path.exists(fma):
+            rec = timed_window(sc, local, args.preroll + args.warmup, args.steps, lib=phys.bind(C.CDLL(fma)), **shape)
+            rec["build"] = ("-fmad=true (FMA-contracted; pair lists / counts bit-exact, positions and rotations <= 1e-5 after one "
+                            "step, velocities NOT: tests/test_fma_build.py) -- reported, not the headline")
+            out["fma_build"] = rec
+    return out
+
+
 def run_reference(args):
     rank, world, _ = dist_env()
     if rank != 0:
         return
-    base, dt = cpu_baseline(args.steps, args.warmup)
+    base, s_per_step = cpu_baseline(args.steps, args.warmup, preroll=args.preroll)
     line = {"impl": "reference", "metric": METRIC, "value": base["value"], "unit": UNIT,
             "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True, "scaling": "weak",
+            "ms_per_step": 1e3 * s_per_step, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": "collisions-64 (64 dynamic unit cubes + 1 static plane per world, "
                                    "4 substeps, dt 1/60), bounded sample: " + base["sample"]},
@@ -198,7 +239,7 @@ def run_ours(args):
     # ---- device-resident throughput -------------------------------------
     sampler = ClockSampler(local)
     sampler.start()
-    ex.run(args.warmup)
+    ex.run(args.preroll + args.warmup)
     ex.kernel_ms()
     sampler.wait_ready()
     barrier()
@@ -246,6 +287,7 @@ def run_ours(args):
                 ex.read_raw_async(c, a)
         ex.sync()
 
+    ex.run(args.preroll)
     for _ in range(args.warmup):
         e2e_step()
     barrier()
@@ -267,24 +309,55 @@ def run_ours(args):
     try:
         from gpu_ecs_madrona_b200 import sharding
         es = sharding.EpisodeStats(every=args.steps, device=f"cuda:{local}")
-        es.launch(sharding.local_statistics(ex, args.warmup + e2e_steps,
+        es.launch(sharding.local_statistics(ex, args.preroll + args.warmup + e2e_steps,
                                             outs[0][1].view(np.float32)[:, :N_ROWS]))
         episode = {k: float(v) for k, v in sharding.EpisodeStats.totals(es.result()).items()}
     except Exception as e:      # statistics must never cost the bench line
         episode = {"error": repr(e)}
 
+    ex.close()
+    shape = dict(block_threads=args.threads, worlds_per_block=args.worlds_per_block, smem_contacts=args.smem_contacts)
+    extras = {}
+    if not args.no_extra:
+        extras = extra_records(args, sc, local, world, rank, shape)
+        if world > 1:
+            # BASELINE.json configs[4]: collisions-64 x 1 048 576 worlds sharded over the N GPUs of the job
+            # (every rank steps its 1 M / N worlds; settled regime; device-timed, max over ranks)
+            Wbig = (1 << 20) // world
+            big = scenes.collisions64(Wbig, world_offset=rank * Wbig, max_contacts=args.max_contacts)
+            rec = timed_window(big, local, args.preroll, 10, **shape)
+            t = torch.tensor([rec["ms_per_step"]], dtype=torch.float64, device="cuda")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            if rank == 0:
+                ms = float(t.item())
+                extras["configs4_1M_worlds"] = {"value": (1 << 20) * 1e3 / ms, "unit": UNIT, "ms_per_step": ms, "steps": 10,
+                                                "worlds_per_gpu": Wbig, "after_steps": args.preroll,
+                                                "workload": "BASELINE.json configs[4]: 1 048 576 worlds over %d GPUs" % world}
+        elif rank == 0:
+            import bench_ecs
+            ecs = {}
+            for name in ("taskgraph", "fanout", "fvs"):       # BASELINE.json configs[0], [1], [3]
+                try:
+                    ecs[name] = bench_ecs.run_record(name, steps=100, warmup=10, no_cpu=args.no_cpu)
+                except Exception as e:                          # a sub-record must never cost the headline
+                    ecs[name] = {"error": repr(e)}
+            extras["ecs_configs"] = ecs
+
     if rank == 0:
         peak, peak_src = measured_peak()
         A = algorithmic_bytes(P, C)
         achieved = A * W / (kms * 1e-3) / 1e9
-        traffic = None
+        # DRAM bytes per launch cannot be measured without a profiler: the figure is the STATIC one of the last
+        # `ncu --set full` capture of this kernel in this regime (profiles/traffic.json names capture and build)
+        traffic, traffic_src = None, None
         tpath = os.path.join(ROOT, "profiles", "traffic.json")
         if os.path.exists(tpath):
             try:
-                traffic = json.load(open(tpath)).get("dram_bytes_per_launch")
+                tj = json.load(open(tpath))
+                traffic, traffic_src = tj.get("dram_bytes_per_launch"), "static: " + tj.get("source", "profiles/traffic.json")
             except Exception:
                 traffic = None
-        base, _ = cpu_baseline(args.steps, args.warmup) if not args.no_cpu else ({}, 0)
+        base, _ = cpu_baseline(args.steps, args.warmup, preroll=args.preroll) if not args.no_cpu else ({}, 0)
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": dev_ms / args.steps, "higher_is_better": True,
@@ -293,23 +366,27 @@ def run_ours(args):
                                    "plane), 4 substeps, dt 1/60 (BASELINE.json configs[2])",
                        "worlds_per_gpu": W, "bodies_per_world": N_ROWS, "substeps": SUBSTEPS,
                        "mean_pairs_per_world": P, "mean_contacts_per_world": C,
+                       "regime": f"settled: {args.preroll} untimed pre-roll steps, then {args.warmup} warm-up, then the {args.steps} "
+                                 "timed steps (contacts per world have plateaued; every --steps / --warmup pair times this regime)",
                        "l2": "state tables (%.0f MB per GPU) exceed the 126 MB L2; no flush needed"
-                             % (W * ex.row_stride() * 290 / 1e6),
+                             % (W * 68 * 290 / 1e6),
                        "launch": info, "wall_ms_per_step": 1e3 * wall / args.steps,
                        "parallelism": f"worlds sharded over {world} GPU(s), no per-step communication",
                        "episode_stats_all_gather": episode},
             "gpu_launches": args.steps,
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d,
-                    "d2h_bytes_per_step": d2h, "steps": e2e_steps, "finite": finite},
+                    "d2h_bytes_per_step": d2h, "steps": e2e_steps, "finite": finite,
+                    "pcie_gb_per_s_per_rank": (h2d + d2h) * e2e_steps / e2e_s / 1e9,
+                    "columns": "in: ExternalForce, ExternalTorque; out: Position, Rotation, Velocity (whole column tiles)"},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
+                         "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
                          "algorithmic_bytes_per_world_step": A, "kernel": "physStepKernel",
                          "kernel_ms": kms},
             "cpu_baseline": base,
             "clocks": clocks,
         }
+        line.update(extras)
         print(json.dumps(line))
-    ex.close()
     if dist is not None:
         dist.barrier()
         dist.destroy_process_group()
@@ -329,6 +406,10 @@ def main():
     ap.add_argument("--io-chunks", type=int, default=4,
                     help="world ranges the end-to-end step is pipelined over (1: copy, step, copy in sequence)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--preroll", type=int, default=PREROLL,
+                    help="untimed steps before the warm-up, so that every --steps / --warmup pair times the settled regime")
+    ap.add_argument("--no-extra", action="store_true",
+                    help="skip the sub-records (regimes, FMA build, ECS configs, configs[4] size): the headline only")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

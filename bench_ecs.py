@@ -40,7 +40,9 @@ def algorithmic_bytes(app, rows):
     return 0
 
 
-def cpu_baseline(app, steps, warmup, worlds_per_thread):
+def cpu_baseline(app, warmup, worlds_per_thread, min_seconds=1.2):
+    """The reference's own state layer + task graph (oracle/_ref/libmadrona_ecs_ref.so) on this host's cores,
+    timed for at least `min_seconds` of wall clock (steps added in batches until then)."""
     from oracle import eorc
     from tests import ecs_util as U
     kind = "reference" if eorc.available("reference") else "port"
@@ -48,15 +50,23 @@ def cpu_baseline(app, steps, warmup, worlds_per_thread):
     worlds = worlds_per_thread * cores
     o = U.make_oracle(kind, app, worlds)
     o.step(warmup, cores)
+    steps, batch = 0, 20
     t0 = time.perf_counter()
-    o.step(steps, cores)
-    dt = time.perf_counter() - t0
+    while True:
+        o.step(batch, cores)
+        steps += batch
+        dt = time.perf_counter() - t0
+        if dt >= min_seconds:
+            break
+        batch = min(4 * batch, 2000)
     o.close()
     return {"value": worlds * steps / dt, "unit": "world-steps/s", "cores": cores, "kind": kind,
             "sample": f"{worlds} worlds x {steps} steps after {warmup} warm-up, {cores} threads ({dt:.2f} s wall)"}
 
 
-def run(name, worlds, steps, warmup, no_cpu):
+def run_record(name, worlds=0, steps=100, warmup=10, no_cpu=False):
+    """One ECS config on the CUDA executor: device-timed value, end-to-end value (every exported column read
+    back to host memory after every step), roofline on the graph-faithful bytes, CPU baseline. Returns a dict."""
     from gpu_ecs_madrona_b200.ecs import EcsExecutor
     app, dflt = APPS[name]
     W = worlds or dflt
@@ -73,17 +83,37 @@ def run(name, worlds, steps, warmup, no_cpu):
         peak = float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"])
     except Exception:
         pass
+    # end to end: a fresh executor over the same step range, one run() + host copies of the exports per step
+    ex.close()
+    ex = EcsExecutor(app, W)
+    slots = U_NUM_EXPORTS[app]
+    ex.run(warmup)
+    d2h = 0
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        ex.run(1)
+        d2h = sum(len(ex.export(s)) for s in range(slots))
+    e2e_s = time.perf_counter() - t0
     line = {"metric": f"world-steps/sec ({A.APP_NAMES[app]}, device-timed)", "value": W * n / (ms * n * 1e-3),
             "unit": "world-steps/s", "n_gpus": 1, "steps": n, "warmup": warmup, "ms_per_step": ms,
             "config": {"workload": f"{A.APP_NAMES[app]}: {W} worlds, params {ex.params}", "mean_rows": rows.tolist()},
             "gpu_launches": n * ex.launches_per_step(),
+            "e2e": {"value": W * steps / e2e_s, "unit": "world-steps/s", "h2d_bytes_per_step": 0,
+                    "d2h_bytes_per_step": int(d2h), "steps": steps},
             "roofline": {"bound": "hbm", "achieved": Abytes * W / (ms * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
                          "frac": Abytes * W / (ms * 1e-3) / 1e9 / peak, "algorithmic_bytes_per_world_step": Abytes,
-                         "kernel": "ecsStepKernel (+export kernels)"}}
+                         "kernel": "ecsStepKernel (+export kernels)", "traffic": None}}
     if not no_cpu:
-        line["cpu_baseline"] = cpu_baseline(app, min(steps, 40), min(warmup, 5), 8)
+        line["cpu_baseline"] = cpu_baseline(app, min(warmup, 5), 8)
     ex.close()
-    print(json.dumps(line))
+    return line
+
+
+U_NUM_EXPORTS = {A.APP_TASKGRAPH: 2, A.APP_FANOUT: 1, A.APP_FVS: 2}
+
+
+def run(name, worlds, steps, warmup, no_cpu):
+    print(json.dumps(run_record(name, worlds, steps, warmup, no_cpu)))
 
 
 def main():
