@@ -111,7 +111,8 @@ def dist_env():
     return rank, world, local
 
 
-PREROLL = 60     # untimed steps before warm-up: the cubes have landed, contacts per world have plateaued
+PREROLL = 120    # untimed steps before warm-up: every cube has landed and come to rest (contacts per world plateau at 64
+                 # from step 100 on, ms per step within 1 % afterwards: profiles/r02i_step_profile.txt)
 
 
 def cpu_baseline(steps, warmup, worlds_per_thread=256, kind=None, preroll=PREROLL, min_seconds=1.5):
@@ -189,7 +190,8 @@ def extra_records(args, sc, local, world, rank, shape):
     if rank == 0:
         # the two regimes of the scene: the headline is the settled one whatever --steps / --warmup say
         out["regimes"] = {"falling": dict(timed_window(sc, local, 5, 20, **shape), note="steps 5-25: a third of the cubes rest on the plane"),
-                          "settled": dict(timed_window(sc, local, args.preroll + 50, 20, **shape), note="steps 110-130")}
+                          "landing": dict(timed_window(sc, local, 80, 20, **shape), note="steps 80-100: the top layer lands, the heaviest steps of the episode"),
+                          "settled": dict(timed_window(sc, local, args.preroll, 20, **shape), note="after the pre-roll: the headline's regime")}
         fma = os.path.join(os.path.dirname(phys.LIB_PATH), "libmadrona_b200_fma.so")
         if os.path.exists(fma):
             rec = timed_window(sc, local, args.preroll + args.warmup, args.steps, lib=phys.bind(C.CDLL(fma)), **shape)
