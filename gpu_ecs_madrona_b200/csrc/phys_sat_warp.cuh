@@ -169,10 +169,11 @@ __device__ __forceinline__ void hullHullWarp(WorldView &v, const StepParams &p, 
     const V3 zero = mk3(0.f, 0.f, 0.f);
     Plane none;
     none.n = zero; none.d = 0.f;
-    const V3 va = lane < nva ? worldVert(xa, src_va, lane) : zero;
+    // The first face query needs A's planes and B's vertices only; most pairs that reach a warp in a resting
+    // scene (neighbours whose boxes overlap after a few degrees of yaw) end there, separated: the other
+    // half of the world-space hulls is built only for those that go on.
     const V3 vb = lane < nvb ? worldVert(xb, src_vb, lane) : zero;
     const Plane pa = lane < nfa ? worldPlane(xa, src_pa, lane) : none;
-    const Plane pb = lane < nfb ? worldPlane(xb, src_pb, lane) : none;
 
     Manifold m;
     int ref = -1, alt = -1;
@@ -182,6 +183,8 @@ __device__ __forceinline__ void hullHullWarp(WorldView &v, const StepParams &p, 
         int fa_face = lane;
         warpArgMax(fa_sep, fa_face);
         if (fa_sep > 0.0f) break;
+        const V3 va = lane < nva ? worldVert(xa, src_va, lane) : zero;
+        const Plane pb = lane < nfb ? worldPlane(xb, src_pb, lane) : none;
         float fb_sep = faceSeparationLane(pb, lane < nfb, va, nva);
         int fb_face = lane;
         warpArgMax(fb_sep, fb_face);
