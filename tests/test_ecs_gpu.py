@@ -229,3 +229,33 @@ def test_zero_copy_tensor_views():
     pos = pe.column_tensor(phys.COL_POSITION)
     pe.run(2)
     assert np.array_equal(pos.cpu().numpy()[:, :65], pe.state()[0])
+
+
+@pytest.mark.parametrize("app,worlds,steps,sample", [
+    (A.APP_TASKGRAPH, 1024, 1000, [0, 1, 77, 500, 1023]),          # BASELINE.json configs[0] at its own size
+    (A.APP_FANOUT, 4096, 25, [0, 9, 2048, 4095]),                  # configs[1]
+    (A.APP_FVS, 8192, 150, [0, 3, 1234, 4096, 8190, 8191]),        # configs[3]
+])
+def test_full_size_sampled_worlds_match_the_checker(app, worlds, steps, sample):
+    """The whole batch of a BASELINE config on the GPU; sampled worlds against the checker run on those worlds
+    alone (worlds are independent and seeded by their GLOBAL index, so a one-world checker with first_world = w
+    is world w of the batch): row counts, Entity columns, every component, the id map -- bit for bit."""
+    from gpu_ecs_madrona_b200.ecs import EcsExecutor
+    ex = EcsExecutor(app, worlds)
+    ex.run(steps)
+    rows = ex.row_counts()
+    cols = ex.read_world_columns()
+    temp = U.TEMP_ARCHETYPES[app]
+    for w in sample:
+        ck = U.make_oracle(_kind(), app, 1, None, first_world=w)
+        ck.step(steps)
+        assert np.array_equal(ck.row_counts()[0], rows[w]), w
+        for a in range(ex.num_archetypes):
+            for c in range(len(ex.col_bytes[a])):
+                if c == 0 and a in temp:
+                    continue
+                assert np.array_equal(cols[(a, c)][w, :rows[w, a]], ck.read_column(0, a, c)), (w, a, c)
+        for x, y in zip(ex.idmap(w), ck.idmap(0)):
+            assert np.array_equal(x, y), w
+        ck.close()
+    ex.close()
