@@ -780,6 +780,12 @@ int32_t mdr_ecs_script(mdr_ecs *e, const mdr_script_op *ops, const int32_t *offs
     const int W = e->host.num_worlds;
     const int32_t total = offsets[W];
     if (total <= 0) return MDR_OK;
+    for (int32_t i = 0; i < total; i++) {
+        // MDR_OP_TMP / MDR_OP_CLEAR_TMP address the script app's temporary archetype (3)
+        if ((ops[i].op == MDR_OP_TMP || ops[i].op == MDR_OP_CLEAR_TMP) && (e->cfg.app != MDR_APP_SCRIPT || e->host.num_arch <= 3))
+            return MDR_ESTATE;
+        if (ops[i].op < MDR_OP_CREATE || ops[i].op > MDR_OP_CLEAR_TMP) return MDR_EINVAL;
+    }
     mdr_script_op *d = nullptr;
     int32_t *doff = nullptr;
     REQ_CUDA(cudaMalloc(&d, sizeof(mdr_script_op) * (size_t)total));
@@ -886,7 +892,12 @@ int32_t mdr_ecs_step_async(mdr_ecs *e, int32_t num_steps)
     if (!e->built) return MDR_ESTATE;
     if (num_steps == 0) return MDR_OK;
     REQ_CUDA(cudaSetDevice(e->cfg.gpu_id));
-    closeTiming(e);
+    // never block the host here: a timed batch that is still running is extended, not waited for
+    bool extend = false;
+    if (e->timing_open) {
+        if (cudaEventQuery(e->ev1) == cudaSuccess) closeTiming(e);
+        else { cudaGetLastError(); extend = true; }
+    }
     if (e->exports_dirty) refreshExports(e);
     const bool staged = [&] {
         for (int s = 0; s < e->host.num_exports; s++)
@@ -930,11 +941,11 @@ int32_t mdr_ecs_step_async(mdr_ecs *e, int32_t num_steps)
         REQ_CUDA(cudaGraphInstantiate(&e->graph, g, 0));
         REQ_CUDA(cudaGraphDestroy(g));
     }
-    REQ_CUDA(cudaEventRecord(e->ev0, e->stream));
+    if (!extend) REQ_CUDA(cudaEventRecord(e->ev0, e->stream));
     for (int s = 0; s < num_steps; s++) REQ_CUDA(cudaGraphLaunch(e->graph, e->stream));
     REQ_CUDA(cudaEventRecord(e->ev1, e->stream));
     e->timing_open = true;
-    e->pending_steps = num_steps;
+    e->pending_steps = (extend ? e->pending_steps : 0) + num_steps;
     return MDR_OK;
 }
 

@@ -119,6 +119,17 @@ struct mdr_phys {
     }
 };
 
+// Called by the ASYNC entry points before they enqueue more work: the batch already timed is closed only
+// if it has finished (cudaEventQuery); otherwise it stays open and the new launches extend it, so that
+// back-to-back asynchronous calls never block the host (the executor's stream keeps them in order).
+static bool timingStillRunning(mdr_phys *p)
+{
+    if (!p->timing_open) return false;
+    if (cudaEventQuery(p->ev1) == cudaSuccess) return false;
+    cudaGetLastError();      // cudaErrorNotReady is not an error
+    return true;
+}
+
 static void closeTiming(mdr_phys *p)
 {
     if (!p->timing_open) return;
@@ -417,6 +428,15 @@ int32_t mdr_phys_set_joints(mdr_phys *p, int32_t max_joints, const int32_t *coun
     }
     REQ_CUDA(cudaSetDevice(p->cfg.gpu_id));
     REQ_CUDA(cudaStreamSynchronize(p->stream));
+    if (max_joints > 0) {       // joint rows must be live rows of their world
+        std::vector<int32_t> rows((size_t)W);
+        REQ_CUDA(cudaMemcpy(rows.data(), p->params.t.row_count, 4 * (size_t)W, cudaMemcpyDeviceToHost));
+        for (int w = 0; w < W; w++)
+            for (int k = 0; k < counts[w]; k++) {
+                const mdr_joint &j = joints[(size_t)w * max_joints + k];
+                if (j.row1 >= rows[w] || j.row2 >= rows[w]) return MDR_EINVAL;
+            }
+    }
     if (p->d_joints) { REQ_CUDA(cudaFree(p->d_joints)); p->d_joints = nullptr; }
     if (p->d_joint_count) { REQ_CUDA(cudaFree(p->d_joint_count)); p->d_joint_count = nullptr; }
     if (max_joints > 0) {
@@ -618,14 +638,15 @@ int32_t mdr_phys_step_async(mdr_phys *p, int32_t num_steps)
     if (!p || num_steps < 0) return MDR_EINVAL;
     if (num_steps == 0) return MDR_OK;
     REQ_CUDA(cudaSetDevice(p->cfg.gpu_id));
-    closeTiming(p);
+    const bool extend = timingStillRunning(p);
+    if (!extend) closeTiming(p);
     if (p->maybe_rebuild) {
         const int W = p->cfg.num_worlds;
         bvhRebuildKernel<<<(W + 63) / 64, 64, 0, p->stream>>>(p->params);
         REQ_CUDA(cudaGetLastError());
         p->maybe_rebuild = false;
     }
-    REQ_CUDA(cudaEventRecord(p->ev0, p->stream));
+    if (!extend) REQ_CUDA(cudaEventRecord(p->ev0, p->stream));
     for (int s = 0; s < num_steps; s++) {
         p->kernel<<<p->blocks, p->threads, p->smem_bytes, p->stream>>>(
             p->params, p->threads_per_world, (int)p->slot_bytes, p->overflow_per_slot, p->lockstep,
@@ -634,7 +655,7 @@ int32_t mdr_phys_step_async(mdr_phys *p, int32_t num_steps)
     REQ_CUDA(cudaGetLastError());
     REQ_CUDA(cudaEventRecord(p->ev1, p->stream));
     p->timing_open = true;
-    p->pending_launches = num_steps;
+    p->pending_launches = (extend ? p->pending_launches : 0) + num_steps;
     return MDR_OK;
 }
 
@@ -666,11 +687,6 @@ int32_t mdr_phys_step_io_async(mdr_phys *p, int32_t num_in, const int32_t *in_co
         REQ_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
         p->io_events.push_back(e);
     }
-    if (p->maybe_rebuild) {
-        bvhRebuildKernel<<<(W + 63) / 64, 64, 0, p->stream>>>(p->params);
-        REQ_CUDA(cudaGetLastError());
-        p->maybe_rebuild = false;
-    }
     // the side streams start after everything already queued on the executor's stream
     cudaEvent_t start = p->io_events[2 * ranges], done = p->io_events[2 * ranges + 1];
     REQ_CUDA(cudaEventRecord(start, p->stream));
@@ -678,9 +694,23 @@ int32_t mdr_phys_step_io_async(mdr_phys *p, int32_t num_in, const int32_t *in_co
     REQ_CUDA(cudaStreamWaitEvent(p->io_out, start, 0));
     REQ_CUDA(cudaEventRecord(p->ev0, p->stream));
     const size_t stride = p->params.t.stride;
+    // A flagged BVH rebuild reads poses of EVERY world: on such a step (a reset) all inputs go in first and
+    // the rebuild follows them; the per-range overlap of copy-in and step is given up for that one step.
+    const bool inputs_first = p->maybe_rebuild;
+    if (inputs_first) {
+        for (int i = 0; i < num_in; i++) {
+            const size_t bytes = (size_t)kColBytes[in_cols[i]] * stride * W;
+            REQ_CUDA(cudaMemcpyAsync(*colSlot(p->params.t, in_cols[i]), in_host[i], bytes, cudaMemcpyHostToDevice, p->io_in));
+        }
+        REQ_CUDA(cudaEventRecord(p->io_events[0], p->io_in));
+        REQ_CUDA(cudaStreamWaitEvent(p->stream, p->io_events[0], 0));
+        bvhRebuildKernel<<<(W + 63) / 64, 64, 0, p->stream>>>(p->params);
+        REQ_CUDA(cudaGetLastError());
+        p->maybe_rebuild = false;
+    }
     for (int r = 0; r < ranges; r++) {
         const int first = r * per, end = first + per < W ? first + per : W;
-        for (int i = 0; i < num_in; i++) {
+        for (int i = 0; i < num_in && !inputs_first; i++) {
             const size_t row = (size_t)kColBytes[in_cols[i]] * stride;
             REQ_CUDA(cudaMemcpyAsync((char *)*colSlot(p->params.t, in_cols[i]) + row * first,
                                      (const char *)in_host[i] + row * first, row * (end - first),

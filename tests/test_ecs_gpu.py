@@ -259,3 +259,36 @@ def test_full_size_sampled_worlds_match_the_checker(app, worlds, steps, sample):
             assert np.array_equal(x, y), w
         ck.close()
     ex.close()
+
+
+def test_forty_node_graph():
+    """The reference's own physics graph is 40 nodes at 4 substeps: a 40-node graph here --
+    20 x (drift, clamp) over the simple_taskgraph tables -- equals 20 steps of the 2-node world on the checker."""
+    from gpu_ecs_madrona_b200.ecs import EcsRegistry
+    from gpu_ecs_madrona_b200 import ecs_apps
+    W, n = 9, 100
+    r = EcsRegistry(W)
+    pos, rot = r.register_component(12), r.register_component(16)
+    sphere = r.register_archetype([pos, rot], n)
+    agent = r.register_archetype([pos, rot], 1)
+    r.export_column(agent, pos, 0)
+    r.export_column(agent, rot, 1)
+    prev = []
+    for k in range(20):
+        d = r.parallel_for(1, [pos], deps=prev)          # kTgDrift
+        prev = [r.parallel_for(2, [pos], deps=[d])]      # kTgClamp
+    r.build()
+    r.make_entities(sphere, n)
+    r.make_entities(agent, 1)
+    for (a, c), data in ecs_apps.initial_columns(A.APP_TASKGRAPH, W, [n]).items():
+        r.write_column_all(a, c, data)
+    r.run(1)
+    ck = U.make_oracle(_kind(), A.APP_TASKGRAPH, W, [n])
+    ck.step(20)
+    for a, rows in ((0, n), (1, 1)):
+        got = r.read_column_all(a, 1, rows)
+        for w in range(W):
+            assert np.array_equal(got[w], ck.read_column(w, a, 1)), (a, w)
+    assert np.array_equal(r.export(0), ck.export(0))
+    r.close()
+    ck.close()

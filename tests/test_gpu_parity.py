@@ -269,3 +269,33 @@ def test_partial_reset_rebuilds_only_the_named_worlds(cuda_lib, port_oracle):
     assert (slot_after[others][..., 3:] >= slot_before[others][..., 3:]).all()
     assert (slot_after[others][..., :3] <= slot_before[others][..., :3]).all()
     assert e.lib.mdr_phys_reset_worlds(e.h, np.array([40], np.int32).ctypes.data, 1) == phys.MDR_EINVAL
+
+
+def test_step_io_with_a_flagged_rebuild_reads_the_new_poses(cuda_lib, port_oracle):
+    """mdr_phys_step_io_async with Position / Rotation among the INPUT columns on a step whose BVH rebuild is
+    flagged (an episode reset through the pipelined host I/O call): the rebuild must see the poses that come
+    in with the same call."""
+    sc = scenes.collisions64(300)
+    o = port_oracle.Oracle(sc, "port")
+    e = phys.PhysExecutor(sc)
+    o.step(12, 8)
+    e.run(12)
+    rng = np.random.default_rng(3)
+    pos = o.read_f32(phys.COL_POSITION).copy()
+    pos[:, 1:, :2] += rng.uniform(-0.05, 0.05, pos[:, 1:, :2].shape).astype(np.float32)
+    pos[:, 1:, 2] += np.float32(0.75)
+    o.write(phys.COL_POSITION, pos)
+    o.flag_rebuild()
+    o.step(1, 8)
+    pin = e.pinned(phys.COL_POSITION)
+    pin[:] = 0
+    pin.view(np.float32).reshape(300, e.row_stride(), 3)[:, :sc.bodies_per_world] = pos
+    pout = e.pinned(phys.COL_VELOCITY)
+    e.flag_rebuild()
+    e.step_io_async([(phys.COL_POSITION, pin)], [(phys.COL_VELOCITY, pout)], 4)
+    e.sync()
+    assert_state_equal(e.state(), o.state(), None, "step with rebuild + pipelined inputs")
+    o.step(5, 8)
+    e.run(5)
+    assert_state_equal(e.state(), o.state(), None, "after")
+    e.close(); o.close()
