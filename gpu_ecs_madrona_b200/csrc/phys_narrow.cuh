@@ -521,6 +521,32 @@ MDR_HD void probeContact(const StepParams &p, int sub, int pi, const Manifold *m
     p.probe.contacts[(size_t)sub * p.probe.max_contacts + pi] = o;
 }
 
+// A hull-hull pair that a warp found separated by a FACE axis is, in a resting or slowly moving scene, separated
+// by the same face in the next substep and the next step. The pair slot remembers that face (WorldView::hint), and
+// the pair's own thread re-evaluates just that one axis -- the same world plane, the same vertex scan, operand
+// for operand what the full query computes for that face (queryFaceDirections, narrowphase.cpp:352-378;
+// faceSeparationLane in phys_sat_warp.cuh) -- before asking for a warp. A positive value is the value the
+// reference's scan would meet at that face (or it has stopped at an earlier face, positive as well): doSAT
+// reports no contact either way (:678-758), so returning "no contact" here is exact, not an approximation.
+// A stale hint (another pair now sits in the slot) is just an axis that may fail to separate: the warp runs.
+MDR_HD bool satHintSeparates(const WorldView &v, const StepParams &p, int a, int b, uint32_t hint)
+{
+    const uint32_t code = hint - 1u;
+    const int f = (int)(code & 31u);
+    const bool face_of_b = (code >> 5) != 0u;
+    const BodyXf xf = bodyXf(v, p, face_of_b ? b : a), xo = bodyXf(v, p, face_of_b ? a : b);
+    if (f >= MDR_LDG(&xf.o->num_faces)) return false;
+    const Plane pl = worldPlane(xf, p.a.planes + 4 * MDR_LDG(&xf.o->face_off), f);
+    const float *src_v = p.a.verts + 3 * MDR_LDG(&xo.o->vert_off);
+    const int nv = MDR_LDG(&xo.o->num_verts);
+    float m = FLT_MAX;
+    for (int k = 0; k < nv; k++) {
+        const float d = dot(pl.n, worldVert(xo, src_v, k));
+        if (d < m) m = d;
+    }
+    return m - pl.d > 0.0f;
+}
+
 // runNarrowphase (CPU branch) + narrowphaseDispatch + generateContacts
 // (narrowphase.cpp:1515-1728,1182-1364,1366-1513) for pair slot `pi`. A slot
 // without contact gets a zero header.
@@ -539,7 +565,9 @@ MDR_HD void narrowphasePair(WorldView &v, const StepParams &p, int pi, bool prob
     if (overlaps(ldBox(v.box, a), ldBox(v.box, b))) {
         if (a_hull && b_hull) {
 #if defined(__CUDA_ARCH__)
-            // a whole warp takes the pair after this pass (phys_sat_warp.cuh)
+            // the face that separated this slot's hulls last time, if any, then a whole warp (phys_sat_warp.cuh)
+            const uint32_t hint = v.hint[pi];
+            if (hint && !probing && satHintSeparates(v, p, a, b, hint)) return;
             v.pairs[pi] = pr | PAIR_SAT;
             return;
 #else

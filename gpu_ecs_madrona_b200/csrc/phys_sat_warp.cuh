@@ -178,17 +178,18 @@ __device__ __forceinline__ void hullHullWarp(WorldView &v, const StepParams &p, 
     Manifold m;
     int ref = -1, alt = -1;
     bool hit = false;
+    uint32_t hint = 0u;         // what the pair's thread tries first next time (satHintSeparates)
     do {
         float fa_sep = faceSeparationLane(pa, lane < nfa, vb, nvb);
         int fa_face = lane;
         warpArgMax(fa_sep, fa_face);
-        if (fa_sep > 0.0f) break;
+        if (fa_sep > 0.0f) { hint = 1u + (uint32_t)fa_face; break; }
         const V3 va = lane < nva ? worldVert(xa, src_va, lane) : zero;
         const Plane pb = lane < nfb ? worldPlane(xb, src_pb, lane) : none;
         float fb_sep = faceSeparationLane(pb, lane < nfb, va, nva);
         int fb_face = lane;
         warpArgMax(fb_sep, fb_face);
-        if (fb_sep > 0.0f) break;
+        if (fb_sep > 0.0f) { hint = 1u + 32u + (uint32_t)fb_face; break; }
         const EdgeWin eq = edgeQueryWarp(lane, va, pa, ta.he, edges_a, nea, xa.t, vb, pb, tb.he, edges_b, neb);
         if (eq.sep > 0.0f) break;
         const bool face_a = fa_sep > eq.sep, face_b = fb_sep > eq.sep;
@@ -218,6 +219,7 @@ __device__ __forceinline__ void hullHullWarp(WorldView &v, const StepParams &p, 
         }
         hit = true;
     } while (false);
+    if (lane == 0) v.hint[pi] = (uint8_t)hint;
     const bool emit = hit && m.n > 0;
     if (emit) emitContactLanes(v, p, contactSlot(v, pi), m, ref, alt, lane);
     if (lane == 0 && probing) probeContact(p, sub, pi, emit ? &m : nullptr, ref, alt);

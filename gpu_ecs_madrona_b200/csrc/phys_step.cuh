@@ -171,7 +171,7 @@ MDR_HD void stepWorld(const BlockCtx &c, WorldView &v, const StepParams &p, int 
     updateLeavesAndRefitGlobal(c, v, p, w);
     c.sync();
     MDR_PHASE(11);
-    storeWorld(c, v, p.t, w);
+    storeWorld(c, v, p, w);
     c.sync();
     MDR_PHASE(12);
 }

@@ -116,6 +116,8 @@ struct StepParams {
     int32_t max_pairs;            // SMEM pair-list capacity per world
     int32_t smem_contacts;        // contact slots held in SMEM; the rest go to `overflow`
     SolverContact *overflow;      // [resident world slots][max_pairs - smem_contacts]
+    uint8_t *sat_hint;            // [W][max_pairs rounded up to 4] separating face seen last per pair slot (0: none);
+                                  // null: no hints (host emulation)
     int32_t *world_pairs;         // [W] pairs found in the last step
     int32_t *world_contacts;      // [W] contacts of the last substep
     int32_t *error_flags;         // [1] bit 0: pair list overflow

@@ -80,6 +80,8 @@ struct WorldView {
     uint32_t *meta;        // object id | META_*
     float *box;            // [np][6] leaf AABBs (broadphase) / world AABBs (narrowphase)
     uint32_t *pairs;       // [max_pairs] row a | row b << 10 | level << 20 (11 bits) | PAIR_SAT
+    uint8_t *hint;         // [max_pairs] per pair slot: 1 + face + 32 * (face of b), the face that separated the
+                           // pair's hulls when a warp last ran the SAT on this slot (see satHintSeparates)
     int32_t *misc;         // [0] num pairs  [1] max level  [2] queued hull-hull pairs
     // --- broadphase scratch, aliased with the contact slots ---
     float *slot;           // [np][6] grow-only slot boxes
@@ -144,6 +146,7 @@ MDR_HD size_t carveWorld(WorldView &v, char *base, int np, int max_pairs, int sm
     MDR_CARVE(meta, uint32_t, np)
     MDR_CARVE(box, float, 6 * np)
     MDR_CARVE(pairs, uint32_t, max_pairs)
+    MDR_CARVE(hint, uint8_t, (max_pairs + 3) / 4 * 4)
     MDR_CARVE(misc, int32_t, 4)
     MDR_CARVE(row_perm, uint16_t, np)
     off = alignUp(off, 16);
@@ -263,6 +266,10 @@ MDR_HD void loadWorld(const BlockCtx &c, WorldView &v, const StepParams &p, int 
     fetchWords(c, v.vel, t.vel + 6 * r0, 6 * n);
     fetchWords(c, v.scale, t.scale + 3 * r0, 3 * n);
     fetchWords(c, v.slot, t.slot_box + 6 * r0, 6 * n);
+    if (p.sat_hint) {
+        const int hw = (p.max_pairs + 3) / 4;
+        fetchWords(c, reinterpret_cast<float *>(v.hint), reinterpret_cast<const float *>(p.sat_hint + (size_t)w * hw * 4), hw);
+    }
     for (int i = c.tid(); i < n; i += c.nthreads()) {
         // four independent loads, then the object table (cached)
         const int32_t ent = t.entity[2 * (r0 + i) + 1];
@@ -281,10 +288,16 @@ MDR_HD void loadWorld(const BlockCtx &c, WorldView &v, const StepParams &p, int 
     fetchWait();
 }
 
-MDR_HD void storeWorld(const BlockCtx &c, const WorldView &v, const PhysTables &t, int w)
+MDR_HD void storeWorld(const BlockCtx &c, const WorldView &v, const StepParams &p, int w)
 {
+    const PhysTables &t = p.t;
     const size_t r0 = (size_t)w * t.stride;
     const int n = v.n;
+    if (p.sat_hint && v.active) {     // only the slots of this step's pairs can have changed
+        const int hw = (v.misc[0] + 3) / 4;
+        copyWords(c, reinterpret_cast<uint32_t *>(p.sat_hint + (size_t)w * ((p.max_pairs + 3) / 4) * 4),
+                  reinterpret_cast<const uint32_t *>(v.hint), hw);
+    }
     copyWords(c, t.pos + 3 * r0, v.pos, 3 * n);
     copyWords(c, t.rot + 4 * r0, v.rot, 4 * n);
     copyWords(c, t.vel + 6 * r0, v.vel, 6 * n);

@@ -235,6 +235,7 @@ static int32_t createImpl(const mdr_phys_config *cfg, const mdr_object *objs, in
     sp.max_pairs = cfg->max_contacts;
     sp.smem_contacts = cfg->smem_contacts > 0 ? cfg->smem_contacts : 72;
     if (sp.smem_contacts > sp.max_pairs) sp.smem_contacts = sp.max_pairs;
+    sp.sat_hint = p->dalloc<uint8_t>((size_t)W * ((sp.max_pairs + 3) / 4 * 4));
     sp.world_pairs = p->dalloc<int32_t>(W);
     sp.world_contacts = p->dalloc<int32_t>(W);
     p->d_err = p->dalloc<int32_t>(1);
