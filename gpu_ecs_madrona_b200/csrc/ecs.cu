@@ -49,12 +49,14 @@ __global__ void __launch_bounds__(32 * kWarpsPerBlock, kMinBlocks)
 ecsStepKernel(const EcsDev *__restrict__ E, int first, int last)
 {
     __shared__ WarpShared shared[kWarpsPerBlock];
+    __shared__ BlockDescriptors descriptors;
     WarpShared *ws = &shared[threadIdx.x >> 5];
     const int warps = gridDim.x * kWarpsPerBlock;
     Context ctx;
+    const NodeDev *nodes = loadDescriptors(&descriptors, ctx, E, first, last);
     for (int w = blockIdx.x * kWarpsPerBlock + (threadIdx.x >> 5); w < E->num_worlds; w += warps) {
         loadWorld(ctx, E, ws, w);
-        runNodes(ctx, E, first, last, AppsBuiltin());
+        runNodes(ctx, nodes, last - first, AppsBuiltin());
         storeWorld(ctx);
     }
 }

@@ -237,6 +237,7 @@ __device__ inline void idBulkRelease(IdNode *nodes, IdState &st, IdCache &c, con
 // in that case as well).
 struct Context {
     const EcsDev *E;
+    const ArchDev *archs = nullptr;   // E->arch, or the block's shared-memory copy of it (BlockDescriptors)
     WarpShared *ws;
     int32_t world;          // index on this GPU
     uint32_t world_id;      // global index (seeds)
@@ -250,7 +251,7 @@ struct Context {
 
     __device__ __forceinline__ char *colPtr(int arch, int col) const
     {
-        const ArchDev &A = E->arch[arch];
+        const ArchDev &A = archs[arch];
         return A.col[col] + (size_t)world * A.stride * A.col_bytes[col];
     }
     template <typename T> __device__ __forceinline__ T *column(int arch, int col) const { return (T *)colPtr(arch, col); }
@@ -284,7 +285,7 @@ struct Context {
     __device__ __forceinline__ Loc makeTemporary(int arch) const
     {
         const int32_t row = atomicAdd(&ws->count[arch], 1);
-        if (row >= E->arch[arch].max_rows) {
+        if (row >= archs[arch].max_rows) {
             atomicSub(&ws->count[arch], 1);
             atomicOr(E->error, kErrRowOverflow);
             return Loc { kNoArch, 0 };
@@ -313,7 +314,7 @@ struct Context {
     __device__ inline Entity makeEntityNowImmediate(int arch, const uint32_t *words, int num_words)
     {
         waitTurn();
-        const ArchDev &A = E->arch[arch];
+        const ArchDev &A = archs[arch];
         volatile int32_t *cnt = ws->count;
         const int32_t r = cnt[arch];
         if (r >= A.max_rows) { atomicOr(E->error, kErrRowOverflow); return Entity { 0u, -1 }; }
@@ -340,7 +341,7 @@ struct Context {
         const Loc l = getLoc(e);
         if (l.archetype == kNoArch) return;         // stale handle: the reference's lookup fails the same way
         const int arch = (int)l.archetype;
-        const ArchDev &A = E->arch[arch];
+        const ArchDev &A = archs[arch];
         volatile int32_t *cnt = ws->count;
         const int32_t from = cnt[arch] - 1, to = l.row;
         IdNode *nodes = idNodes();
@@ -469,7 +470,7 @@ __device__ inline void destroyBatch(Context &ctx, unsigned run)
         mover = (peers >> lane) == 1u && ent_to < ws->count[ent_arch];
     }
     if (mover) {
-        const ArchDev &A = E->arch[ent_arch];
+        const ArchDev &A = ctx.archs[ent_arch];
         for (int c = 0; c < A.num_cols; c++) {
             const int words = A.col_bytes[c] >> 2;
             uint32_t *base = (uint32_t *)ctx.colPtr(ent_arch, c);
@@ -502,7 +503,7 @@ __device__ inline void createBatch(Context &ctx, unsigned run)
         int32_t r = -1;
         if (lane == 0) {
             r = ws->count[a_i];
-            if (r >= E->arch[a_i].max_rows) {
+            if (r >= ctx.archs[a_i].max_rows) {
                 atomicOr(E->error, kErrRowOverflow);
                 r = -1;
             } else {
@@ -518,7 +519,7 @@ __device__ inline void createBatch(Context &ctx, unsigned run)
     }
     if (((run >> lane) & 1u) && my_row >= 0) {
         const int a = ctx.create_arch;
-        const ArchDev &A = E->arch[a];
+        const ArchDev &A = ctx.archs[a];
         ctx.column<Entity>(a, 0)[my_row] = my_e;
         int w = 0;
         for (int c = 1; c < A.num_cols; c++) {
@@ -589,7 +590,7 @@ __device__ inline void sortArchetype(Context &ctx, int arch, int key_col, bool r
     const int lane = laneId();
     const EcsDev *E = ctx.E;
     WarpShared *ws = ctx.ws;
-    const ArchDev &A = E->arch[arch];
+    const ArchDev &A = ctx.archs[arch];
     const SortScratch &S = E->sort[arch];
     __syncwarp();
     const int32_t n = ws->count[arch];
@@ -686,13 +687,14 @@ __device__ inline void loadWorld(Context &ctx, const EcsDev *E, WarpShared *ws, 
 {
     const int lane = laneId();
     ctx.E = E; ctx.ws = ws; ctx.world = world; ctx.world_id = (uint32_t)(E->first_world + world);
+    if (!ctx.archs) ctx.archs = E->arch;
     ctx.pend = 0u;
     ctx.serial = 0u;
     ctx.created = Entity { 0u, -1 };
     ctx.created_row = -1;
     __syncwarp();
     if (lane == 0) { ws->tmp_used = E->tmp_used ? E->tmp_used[world] : 0; ws->done = 0u; }
-    if (lane < E->num_arch) ws->count[lane] = E->arch[lane].row_count[world];
+    if (lane < E->num_arch) ws->count[lane] = ctx.archs[lane].row_count[world];
     if (lane < (int)(sizeof(IdState) / 4)) ((int32_t *)&ws->ids)[lane] = ((const int32_t *)(E->id_state + world))[lane];
     __syncwarp();
 }
@@ -704,7 +706,7 @@ __device__ inline void storeWorld(Context &ctx)
     WarpShared *ws = ctx.ws;
     __syncwarp();
     if (lane == 0 && E->tmp_used) E->tmp_used[ctx.world] = ws->tmp_used;
-    if (lane < E->num_arch) E->arch[lane].row_count[ctx.world] = ws->count[lane];
+    if (lane < E->num_arch) ctx.archs[lane].row_count[ctx.world] = ws->count[lane];
     if (lane < (int)(sizeof(IdState) / 4)) ((int32_t *)(E->id_state + ctx.world))[lane] = ((const int32_t *)&ws->ids)[lane];
     __syncwarp();
 }
@@ -806,11 +808,37 @@ __device__ __forceinline__ void parallelForImmediate(Context &ctx, const NodeDev
 // TaskGraph::run (src/core/taskgraph.cpp:117-122) for nodes [first, last) of one world, one warp.
 // `builtin(ctx, nd)` dispatches a library-compiled func id (the generated switch of the reference,
 // src/mw/cuda_exec.cpp:553-564); nodes compiled in the user's translation unit arrive as pointers.
-template <typename Builtin>
-__device__ __forceinline__ void runNodes(Context &ctx, const EcsDev *E, int first, int last, Builtin builtin)
+// The descriptors every warp of a block reads for every world -- archetype tables (column addresses, sizes)
+// and the nodes of the launch -- copied to shared memory once per block: the walk of one world is a chain of
+// dependent loads descriptor -> column -> row, and its first link then costs a shared-memory access
+// instead of a trip to L2 (profiles/r01e_summary.md: long scoreboard on exactly these loads).
+constexpr int kSharedArch = 8, kSharedNodes = 16;
+struct BlockDescriptors {
+    ArchDev arch[kSharedArch];
+    NodeDev node[kSharedNodes];
+};
+// All threads of the block. Returns the node array to walk (indexed from `first`).
+__device__ __forceinline__ const NodeDev *loadDescriptors(BlockDescriptors *bd, Context &ctx, const EcsDev *E, int first, int last)
 {
-    for (int ni = first; ni < last; ni++) {
-        const NodeDev &nd = E->node[ni];
+    const bool arch_fits = E->num_arch <= kSharedArch, nodes_fit = last - first <= kSharedNodes;
+    if (arch_fits) {
+        const int words = E->num_arch * (int)(sizeof(ArchDev) / 4);
+        for (int i = threadIdx.x; i < words; i += blockDim.x) ((uint32_t *)bd->arch)[i] = ((const uint32_t *)E->arch)[i];
+    }
+    if (nodes_fit) {
+        const int words = (last - first) * (int)(sizeof(NodeDev) / 4);
+        for (int i = threadIdx.x; i < words; i += blockDim.x) ((uint32_t *)bd->node)[i] = ((const uint32_t *)(E->node + first))[i];
+    }
+    __syncthreads();
+    ctx.archs = arch_fits ? bd->arch : E->arch;
+    return nodes_fit ? bd->node : E->node + first;
+}
+
+template <typename Builtin>
+__device__ __forceinline__ void runNodes(Context &ctx, const NodeDev *nodes, int count, Builtin builtin)
+{
+    for (int ni = 0; ni < count; ni++) {
+        const NodeDev &nd = nodes[ni];
         switch (nd.kind) {
         case kNodeParallelFor:
             if (nd.func == 0) nd.fn(ctx, nd);
@@ -840,12 +868,14 @@ __global__ void __launch_bounds__(32 * kWarpsPerBlock, kMinBlocks)
 ecsGraphKernel(const EcsDev *__restrict__ E, int first, int last)
 {
     __shared__ WarpShared shared[kWarpsPerBlock];
+    __shared__ BlockDescriptors descriptors;
     WarpShared *ws = &shared[threadIdx.x >> 5];
     const int warps = gridDim.x * kWarpsPerBlock;
     Context ctx;
+    const NodeDev *nodes = loadDescriptors(&descriptors, ctx, E, first, last);
     for (int w = blockIdx.x * kWarpsPerBlock + (threadIdx.x >> 5); w < E->num_worlds; w += warps) {
         loadWorld(ctx, E, ws, w);
-        runNodes(ctx, E, first, last, Builtin());
+        runNodes(ctx, nodes, last - first, Builtin());
         storeWorld(ctx);
     }
 }
