@@ -28,6 +28,7 @@ physStepKernel(const __grid_constant__ StepParams p, int threads_per_world, int 
     v.overflow = p.overflow + ((size_t)blockIdx.x * slots + slot) * overflow_per_slot;
     // dense solver lanes need block-wide barriers, pair slots in 10 bits and a view per slot
     BlockSolve *bs = lockstep && slots <= kDenseSlots && p.max_pairs <= 1024 ? &block_solve : nullptr;
+    v.level_any = bs ? block_solve.level_any : nullptr;
     if (bs && ctx.tid_ == 0) { v.n = 0; v.active = false; bs->views[slot] = v; }
     __syncthreads();
     // Every slot of the block walks the same barriers: the trip count depends on

@@ -221,7 +221,13 @@ __device__ __forceinline__ void hullHullWarp(WorldView &v, const StepParams &p, 
     } while (false);
     if (lane == 0) v.hint[pi] = (uint8_t)hint;
     const bool emit = hit && m.n > 0;
-    if (emit) emitContactLanes(v, p, contactSlot(v, pi), m, ref, alt, lane);
+    if (emit) {
+        emitContactLanes(v, p, contactSlot(v, pi), m, ref, alt, lane);
+        if (lane == 0 && v.level_any) {
+            const int lv = pairLevel(pr);
+            atomicOr(&v.level_any[sub & 1], 1u << (lv < 31 ? lv : 31));
+        }
+    }
     if (lane == 0 && probing) probeContact(p, sub, pi, emit ? &m : nullptr, ref, alt);
 }
 

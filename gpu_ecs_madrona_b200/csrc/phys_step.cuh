@@ -23,22 +23,25 @@ struct BlockSolve {
     int32_t cnt[32];                  // per level (index 31: deeper than kDenseLevels)
     int32_t off[33];
     int32_t dense;
+    uint32_t level_any[2];            // per substep parity: bit lv set when a contact of level lv was emitted
     uint16_t items[kDenseItems];      // world slot << 10 | pair slot
     WorldView views[kDenseSlots];
 };
 
 #if defined(__CUDA_ARCH__)
-// All threads of the block; the contacts of this substep are final and a block
-// barrier has passed since they were written. Returns the block-uniform verdict.
+// All threads of the block, once per step, after every world slot has its pair list and levels (block
+// barrier passed): the PAIRS of all slots bucketed by level. Which of them carry a contact changes from
+// substep to substep; the solver skips empty slots and, through `level_any`, whole levels nobody has.
+// Returns the block-uniform verdict.
 __device__ __forceinline__ bool buildLevelLists(const BlockCtx &c, const WorldView &v, BlockSolve *bs, int slot,
                                                 int max_level)
 {
     const int t = threadIdx.x;
     if (t < 32) bs->cnt[t] = 0;
+    if (t == 32) { bs->level_any[0] = 0u; bs->level_any[1] = 0u; }
     __syncthreads();
     const int np = v.misc[0];
     for (int i = c.tid(); i < np; i += c.nthreads()) {
-        if (contactSlot(v, i)->hdr == 0) continue;
         const int lv = pairLevel(v.pairs[i]);
         atomicAdd(&bs->cnt[lv <= kDenseLevels ? lv : 31], 1);
     }
@@ -61,7 +64,6 @@ __device__ __forceinline__ bool buildLevelLists(const BlockCtx &c, const WorldVi
     __syncthreads();
     if (!bs->dense) return false;
     for (int i = c.tid(); i < np; i += c.nthreads()) {
-        if (contactSlot(v, i)->hdr == 0) continue;
         const int lv = pairLevel(v.pairs[i]);
         const int at = bs->off[lv] + atomicAdd(&bs->cnt[lv], 1);
         bs->items[at] = (uint16_t)((slot << 10) | i);
@@ -70,16 +72,18 @@ __device__ __forceinline__ bool buildLevelLists(const BlockCtx &c, const WorldVi
     return true;
 }
 
+// `any`: the levels that hold a contact in this substep (bit lv), read by every thread after a block barrier.
 template <bool kVelocity>
-__device__ __forceinline__ void solveDense(BlockSolve *bs, const StepParams &p, int max_level)
+__device__ __forceinline__ void solveDense(BlockSolve *bs, const StepParams &p, int max_level, uint32_t any)
 {
     for (int lv = 1; lv <= max_level; lv++) {
+        if (!((any >> lv) & 1u)) continue;             // block-uniform
         const int begin = bs->off[lv], end = bs->off[lv + 1];
-        if (begin == end) continue;                    // block-uniform
         for (int k = begin + (int)threadIdx.x; k < end; k += (int)blockDim.x) {
             const uint32_t code = bs->items[k];
             WorldView &vv = bs->views[code >> 10];
             SolverContact *ct = contactSlot(vv, (int)(code & 1023u));
+            if (ct->hdr == 0) continue;
             if (kVelocity) solveContactVelocities(vv, p, ct);
             else solveContactPositions(vv, p, ct);
         }
@@ -119,12 +123,20 @@ MDR_HD void stepWorld(const BlockCtx &c, WorldView &v, const StepParams &p, int 
     MDR_PHASE(2);
     const int max_level = c.lockstep() ? *group_level : v.misc[1];
     const bool probing = v.active && p.probe.world == w;
+#if defined(__CUDA_ARCH__)
+    const bool dense = bs && buildLevelLists(c, v, bs, slot, max_level);
+    MDR_PHASE(6);
+#endif
     for (int sub = 0; sub < p.substeps; sub++) {
         substepBodies(c, v, p, w, sub);
         worldBoxes(c, v, p, sub);
         c.sync();
         MDR_PHASE(3);
         const int np = v.misc[0];
+#if defined(__CUDA_ARCH__)
+        // nobody reads the other parity's flags any more (its solves ended before this substep's first barrier)
+        if (bs && threadIdx.x == 0) bs->level_any[(sub + 1) & 1] = 0u;
+#endif
         for (int i = c.tid(); i < np; i += c.nthreads()) narrowphasePair(v, p, i, probing, sub);
         c.sync();
         MDR_PHASE(4);
@@ -134,15 +146,15 @@ MDR_HD void stepWorld(const BlockCtx &c, WorldView &v, const StepParams &p, int 
         MDR_PHASE(5);
 #endif
 #if defined(__CUDA_ARCH__)
-        if (bs && buildLevelLists(c, v, bs, slot, max_level)) {
-            MDR_PHASE(6);
-            solveDense<false>(bs, p, max_level);
+        if (dense) {
+            const uint32_t any = bs->level_any[sub & 1];      // final: a block barrier has passed since the last emit
+            solveDense<false>(bs, p, max_level, any);
             MDR_PHASE(7);
             if (kJoints) solveJoints(c, v, p, w);
             setVelocities(c, v, p, sub);
             c.sync();
             MDR_PHASE(8);
-            solveDense<true>(bs, p, max_level);
+            solveDense<true>(bs, p, max_level, any);
             MDR_PHASE(9);
             continue;
         }

@@ -80,6 +80,7 @@ struct WorldView {
     uint32_t *meta;        // object id | META_*
     float *box;            // [np][6] leaf AABBs (broadphase) / world AABBs (narrowphase)
     uint32_t *pairs;       // [max_pairs] row a | row b << 10 | level << 20 (11 bits) | PAIR_SAT
+    uint32_t *level_any;   // block-shared [2] (substep parity): levels that hold a contact; null without dense lists
     uint8_t *hint;         // [max_pairs] per pair slot: 1 + face + 32 * (face of b), the face that separated the
                            // pair's hulls when a warp last ran the SAT on this slot (see satHintSeparates)
     int32_t *misc;         // [0] num pairs  [1] max level  [2] queued hull-hull pairs
@@ -135,6 +136,7 @@ MDR_HD size_t carveWorld(WorldView &v, char *base, int np, int max_pairs, int sm
 #define MDR_CARVE(field, type, count) \
     off = alignUp(off, 16); v.field = (type *)(base + off); off += sizeof(type) * (size_t)(count);
     v.np = np;
+    v.level_any = nullptr;
     v.mask_words = (np + 31) / 32;
     v.smem_contacts = smem_contacts;
     MDR_CARVE(rot, float, 4 * np)
