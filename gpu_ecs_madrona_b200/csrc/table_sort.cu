@@ -466,6 +466,93 @@ int32_t mdr_sort_run(mdr_sort *s, const void *const *columns_in, void *const *co
     return MDR_OK;
 }
 
+// ---- allocation-free variant (no counterpart in the reference) ----
+// For callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that
+// forbid it): the key sort of mdr_sort_run -- histogram, scan, one Onesweep pass per digit -- with ALL its scratch
+// (one key / permutation ping-pong pair, digit bins, tile counters, look-back words) in the file-scope device array
+// below instead of buffers from mdr_sort_create. The array costs kStaticScratchBytes on every GPU that loads the
+// library, until exit; every call shares it, so calls that overlap on the GPU race (one call at a time per device,
+// or calls ordered on one stream). It keeps the last call's contents: the words that must start at zero (bins,
+// counters, look-back) are cleared by every call; the ping-pong pair is fully overwritten before it is read.
+constexpr int kStaticMaxRows = MDR_SORT_STATIC_MAX_ROWS;
+constexpr int kStaticMaxTiles = (kStaticMaxRows + kTile - 1) / kTile;
+constexpr size_t kStaticBinWords = (size_t)kMaxPasses * kDigits + kDigits + (size_t)kStaticMaxTiles * kDigits * kMaxPasses;
+constexpr size_t kStaticScratchWords = 2 * (size_t)kStaticMaxRows + kStaticBinWords;
+static __device__ __align__(256) uint32_t g_sort_static_scratch[kStaticScratchWords];
+
+// In host code `g_sort_static_scratch` is a host-side stand-in for the symbol, not a device address: the address a
+// kernel can use comes from cudaGetSymbolAddress, once per device, with that device current.
+static uint32_t *staticScratchOn(int gpu_id)
+{
+    static uint32_t *ptrs[64] = {};
+    static bool ready[64] = {};
+    if (gpu_id < 0 || gpu_id >= 64) return nullptr;
+    if (!ready[gpu_id]) {
+        void *ptr = nullptr;
+        if (cudaGetSymbolAddress(&ptr, g_sort_static_scratch) != cudaSuccess || !ptr) { cudaGetLastError(); return nullptr; }
+        if (cudaFuncSetAttribute(sortOnesweepKernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 (int)sizeof(OnesweepSmem)) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+        ptrs[gpu_id] = (uint32_t *)ptr;
+        ready[gpu_id] = true;
+    }
+    return ptrs[gpu_id];
+}
+
+int32_t mdr_sort_static_max_rows(void) { return kStaticMaxRows; }
+int64_t mdr_sort_static_scratch_bytes(void) { return (int64_t)(kStaticScratchWords * 4); }
+
+int32_t mdr_sort_pairs_static(int32_t gpu_id, const uint32_t *keys_in, uint32_t *keys_out, int32_t *perm_out,
+                              int32_t num_rows, int32_t num_key_bits, void *stream)
+{
+    if (!keys_in || !keys_out || !perm_out || num_rows < 0 || num_key_bits < 1 || num_key_bits > 32 ||
+        (const void *)keys_in == (const void *)keys_out || ((uintptr_t)keys_in & 15u) || ((uintptr_t)keys_out & 3u) ||
+        ((uintptr_t)perm_out & 3u))
+        return MDR_EINVAL;
+    if (num_rows > kStaticMaxRows) {
+        fprintf(stderr, "madrona_b200: mdr_sort_pairs_static sorts at most %d rows (asked for %d): its scratch is a fixed "
+                        "device array; use mdr_sort_create / mdr_sort_run for larger tables\n", kStaticMaxRows, num_rows);
+        return MDR_ECAPACITY;
+    }
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || gpu_id < 0 || gpu_id >= ndev) { cudaGetLastError(); return MDR_ENODEVICE; }
+    if (cudaSetDevice(gpu_id) != cudaSuccess) { cudaGetLastError(); return MDR_ENODEVICE; }
+    uint32_t *scratch = staticScratchOn(gpu_id);
+    if (!scratch) return MDR_ESTATE;
+    if (num_rows == 0) return MDR_OK;
+    cudaStream_t st = (cudaStream_t)stream;
+    const int passes = (num_key_bits + 7) / 8;
+    const int tiles = (num_rows + kTile - 1) / kTile;
+    uint32_t *keys_s = scratch;
+    int32_t *vals_s = (int32_t *)(scratch + kStaticMaxRows);
+    uint32_t *bins = scratch + 2 * (size_t)kStaticMaxRows;
+    uint32_t *counters = bins + kMaxPasses * kDigits;
+    uint32_t *lookback = counters + kDigits;
+    if (cudaMemsetAsync(bins, 0, 4 * ((size_t)kMaxPasses * kDigits + kDigits + (size_t)tiles * kDigits * passes), st) != cudaSuccess) {
+        cudaGetLastError();
+        return MDR_ESTATE;
+    }
+    int sms = 0;
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, gpu_id);
+    int hgrid = (num_rows / 4 + kThreads - 1) / kThreads;
+    if (hgrid > 8 * sms) hgrid = 8 * sms;
+    if (hgrid < 1) hgrid = 1;
+    sortHistogramKernel<<<hgrid, kThreads, 0, st>>>(keys_in, num_rows, passes, bins);
+    sortScanKernel<<<passes, kThreads, 0, st>>>(bins);
+    const uint32_t *src_k = keys_in;
+    const int32_t *src_v = nullptr;                      // pass 0 reads the identity permutation
+    for (int p = 0; p < passes; p++) {
+        const bool to_out = (passes - 1 - p) % 2 == 0;   // the last pass lands in the caller's buffers
+        uint32_t *dst_k = to_out ? keys_out : keys_s;
+        int32_t *dst_v = to_out ? perm_out : vals_s;
+        sortOnesweepKernel<<<tiles, kThreads, sizeof(OnesweepSmem), st>>>(
+            src_k, src_v, dst_k, dst_v, bins + p * kDigits, lookback + (size_t)p * tiles * kDigits, counters + p,
+            num_rows, 8 * p);
+        src_k = dst_k;
+        src_v = dst_v;
+    }
+    return cudaGetLastError() == cudaSuccess ? MDR_OK : MDR_ESTATE;
+}
+
 float mdr_sort_last_ms(mdr_sort *s, int32_t *launches)
 {
     if (!s) return 0.f;

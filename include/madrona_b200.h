@@ -426,6 +426,22 @@ int32_t mdr_sort_create(int32_t gpu_id, int32_t max_rows, int32_t num_columns, c
 void mdr_sort_destroy(mdr_sort *s);
 int32_t mdr_sort_run(mdr_sort *s, const void *const *columns_in, void *const *columns_out, int32_t num_rows,
                      int32_t *entity_row, int32_t max_entity_ids, int32_t *out_num_rows);
+/* Allocation-free key sort. NO COUNTERPART IN THE REFERENCE: added for
+ * callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid
+ * it). The key sort of mdr_sort_run (histogram, scan, one Onesweep pass per 8-bit digit) with all of its scratch in
+ * a fixed device array inside the library instead of buffers from mdr_sort_create: keys_in [num_rows] u32 (device,
+ * 16-byte aligned) -> keys_out [num_rows] (stably sorted by the low 8 * ceil(num_key_bits / 8) bits) and perm_out
+ * [num_rows] i32 (source row of every output row); keys_out must not alias keys_in. Work is ENQUEUED on `stream`
+ * (a cudaStream_t, NULL = the default stream) and not waited for. Calls no cudaMalloc / cudaFree or any allocating
+ * routine. LIMITS: num_rows <= MDR_SORT_STATIC_MAX_ROWS (more: MDR_ECAPACITY and a message); the array
+ * (mdr_sort_static_scratch_bytes(), ~0.6 MB) is held by every GPU that loads the library until exit; every call on
+ * a device shares it, so calls that overlap on the GPU race -- order them on one stream or wait in between. The
+ * array keeps the last call's contents; each call clears the words that must start at zero. */
+#define MDR_SORT_STATIC_MAX_ROWS 65536
+int32_t mdr_sort_pairs_static(int32_t gpu_id, const uint32_t *keys_in, uint32_t *keys_out, int32_t *perm_out,
+                              int32_t num_rows, int32_t num_key_bits, void *stream);
+int32_t mdr_sort_static_max_rows(void);
+int64_t mdr_sort_static_scratch_bytes(void);
 /* Device time of the last mdr_sort_run (CUDA events on its stream) and its kernel launches. */
 float mdr_sort_last_ms(mdr_sort *s, int32_t *launches);
 
