@@ -44,11 +44,10 @@ def cpu_baseline(app, warmup, worlds_per_thread, min_seconds=1.2):
     """The reference's own state layer + task graph (oracle/_ref/libmadrona_ecs_ref.so) on this host's cores,
     timed for at least `min_seconds` of wall clock (steps added in batches until then)."""
     from oracle import eorc
-    from tests import ecs_util as U
     kind = "reference" if eorc.available("reference") else "port"
     cores = len(os.sched_getaffinity(0))
     worlds = worlds_per_thread * cores
-    o = U.make_oracle(kind, app, worlds)
+    o = eorc.make_app_oracle(kind, app, worlds)
     o.step(warmup, cores)
     steps, batch = 0, 20
     t0 = time.perf_counter()

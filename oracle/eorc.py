@@ -111,3 +111,15 @@ class EcsOracle:
         if n < 0:
             raise RuntimeError("eorc_export failed")
         return out[:n].copy()
+
+
+def make_app_oracle(kind, app, num_worlds, params=None, first_world=0):
+    """A checker for one of the task-graph worlds with the SAME initial columns the CUDA executor gets
+    (gpu_ecs_madrona_b200.ecs_apps.initial_columns: host-side input data only)."""
+    from gpu_ecs_madrona_b200 import ecs_apps
+    params = list(params if params is not None else ecs_apps.DEFAULT_PARAMS[app])
+    o = EcsOracle(kind, app, num_worlds, params, first_world)
+    for (arch, col), data in ecs_apps.initial_columns(app, num_worlds, params, first_world).items():
+        for w in range(num_worlds):
+            o.write_column(w, arch, col, data[w])
+    return o

@@ -5,13 +5,7 @@ from gpu_ecs_madrona_b200 import ecs_apps
 from oracle import eorc
 
 
-def make_oracle(kind, app, num_worlds, params=None, first_world=0):
-    params = list(params if params is not None else ecs_apps.DEFAULT_PARAMS[app])
-    o = eorc.EcsOracle(kind, app, num_worlds, params, first_world)
-    for (arch, col), data in ecs_apps.initial_columns(app, num_worlds, params, first_world).items():
-        for w in range(num_worlds):
-            o.write_column(w, arch, col, data[w])
-    return o
+make_oracle = eorc.make_app_oracle
 
 
 def snapshot(o, num_exports=0):
