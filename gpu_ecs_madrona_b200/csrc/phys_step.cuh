@@ -234,12 +234,20 @@ MDR_HD int midpointSplit(const float *leaf, uint16_t *sorted, int base, int num)
 }
 
 // leaf: this world's current leaf boxes [n][6]; slot/order/sorted: outputs.
+// The traversal order alone; `sorted` holds 0..n-1 on entry.
+MDR_HD void bvhRankOrder(const float *leaf, uint16_t *order, uint16_t *sorted, int n);
+
 MDR_HD void bvhRebuildWorld(const float *leaf, float *slot, uint16_t *order, uint16_t *sorted, int n)
 {
     for (int i = 0; i < n; i++) {
         sorted[i] = (uint16_t)i;
         for (int k = 0; k < 6; k++) slot[6 * i + k] = leaf[6 * i + k];
     }
+    bvhRankOrder(leaf, order, sorted, n);
+}
+
+MDR_HD void bvhRankOrder(const float *leaf, uint16_t *order, uint16_t *sorted, int n)
+{
     struct Range { int32_t off, num; };
     Range stack[128];
     int sz = 0, rank = 0;

@@ -31,23 +31,36 @@ using namespace mdr;
 
 // ------------------------------------------------------------------ kernels --
 // physStepKernel lives in phys_kernel.cuh and is instantiated by phys_inst*.cu (parallel builds).
-// One thread per flagged world: current leaf boxes, then the reference's
-// top-down build reduced to traversal order + slot-box reset.
-__global__ void bvhRebuildKernel(const __grid_constant__ StepParams p)
+// The reference's top-down build reduced to traversal order + slot-box reset (phys_step.cuh).
+// One WARP per flagged world (an episode reset names few worlds, the others return at once): the lanes compute the
+// current leaf boxes and reset the slot boxes row-parallel; the first lane then runs the top-down splits, which are
+// sequential by nature (each split partitions what the previous one left).
+constexpr int kRebuildWarps = 8;
+__global__ void __launch_bounds__(32 * kRebuildWarps) bvhRebuildKernel(const __grid_constant__ StepParams p)
 {
-    const int w = blockIdx.x * blockDim.x + threadIdx.x;
+    const int w = blockIdx.x * kRebuildWarps + (threadIdx.x >> 5), lane = threadIdx.x & 31;
     if (w >= p.t.num_worlds || !p.t.rebuild_flag[w]) return;
-    p.t.rebuild_flag[w] = 0;
     const PhysTables &t = p.t;
     const size_t r0 = (size_t)w * t.stride;
     const int n = t.row_count[w];
-    for (int i = 0; i < n; i++) {
+    for (int i = lane; i < n; i += 32) {
         const ObjDev *o = p.a.objs + t.obj[r0 + i];
         Box wb = applyTRS(objAABB(o), ld3(t.pos + 3 * r0, i), ld4(t.rot + 4 * r0, i), ld3(t.scale + 3 * r0, i));
-        stBox(t.leaf_aabb + 6 * r0, i,
-              expandWithMotion(wb, ldVelLin(t.vel + 6 * r0, i), p.vel_expand, p.accel_expand));
+        const Box leaf = expandWithMotion(wb, ldVelLin(t.vel + 6 * r0, i), p.vel_expand, p.accel_expand);
+        stBox(t.leaf_aabb + 6 * r0, i, leaf);
+        stBox(t.slot_box + 6 * r0, i, leaf);
+        t.sorted[r0 + i] = (uint16_t)i;
     }
-    bvhRebuildWorld(t.leaf_aabb + 6 * r0, t.slot_box + 6 * r0, t.order + r0, t.sorted + r0, n);
+    __syncwarp();
+    if (lane == 0) {
+        p.t.rebuild_flag[w] = 0;
+        bvhRankOrder(t.leaf_aabb + 6 * r0, t.order + r0, t.sorted + r0, n);
+    }
+}
+
+static void launchRebuild(const StepParams &params, int num_worlds, cudaStream_t stream)
+{
+    bvhRebuildKernel<<<(num_worlds + kRebuildWarps - 1) / kRebuildWarps, 32 * kRebuildWarps, 0, stream>>>(params);
 }
 
 // -------------------------------------------------------------- host state --
@@ -326,7 +339,7 @@ int32_t mdrPhysEnqueueStep(mdr_phys *p, cudaStream_t stream)
 {
     if (!p) return MDR_EINVAL;
     const int W = p->cfg.num_worlds;
-    bvhRebuildKernel<<<(W + 63) / 64, 64, 0, stream>>>(p->params);
+    launchRebuild(p->params, W, stream);
     p->kernel<<<p->blocks, p->threads, p->smem_bytes, stream>>>(
         p->params, p->threads_per_world, (int)p->slot_bytes, p->overflow_per_slot, p->lockstep, 0, W);
     return cudaGetLastError() == cudaSuccess ? MDR_OK : MDR_ESTATE;
@@ -643,7 +656,7 @@ int32_t mdr_phys_step_async(mdr_phys *p, int32_t num_steps)
     if (!extend) closeTiming(p);
     if (p->maybe_rebuild) {
         const int W = p->cfg.num_worlds;
-        bvhRebuildKernel<<<(W + 63) / 64, 64, 0, p->stream>>>(p->params);
+        launchRebuild(p->params, W, p->stream);
         REQ_CUDA(cudaGetLastError());
         p->maybe_rebuild = false;
     }
@@ -705,7 +718,7 @@ int32_t mdr_phys_step_io_async(mdr_phys *p, int32_t num_in, const int32_t *in_co
         }
         REQ_CUDA(cudaEventRecord(p->io_events[0], p->io_in));
         REQ_CUDA(cudaStreamWaitEvent(p->stream, p->io_events[0], 0));
-        bvhRebuildKernel<<<(W + 63) / 64, 64, 0, p->stream>>>(p->params);
+        launchRebuild(p->params, W, p->stream);
         REQ_CUDA(cudaGetLastError());
         p->maybe_rebuild = false;
     }
