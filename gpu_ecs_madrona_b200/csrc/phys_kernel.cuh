@@ -10,7 +10,9 @@ namespace mdr {
 
 extern __shared__ __align__(16) char mdr_smem[];
 
-template <int kMaxThreads, int kMinBlocks, bool kJoints>
+// kHullSlots: 1 = hulls of up to 32 vertices / faces, 2 = up to 64 (phys_sat_warp.cuh); the big-hull variant carries
+// the joint solve as well (one extra instantiation per register budget instead of two).
+template <int kMaxThreads, int kMinBlocks, bool kJoints, int kHullSlots = 1>
 __global__ void __launch_bounds__(kMaxThreads, kMinBlocks)
 physStepKernel(const __grid_constant__ StepParams p, int threads_per_world, int slot_bytes,
                int overflow_per_slot, int lockstep, int first_world, int end_world)
@@ -36,7 +38,7 @@ physStepKernel(const __grid_constant__ StepParams p, int threads_per_world, int 
     for (int base = first_world + blockIdx.x * slots; base < end_world; base += gridDim.x * slots) {
         const int w = base + slot;
         v.active = w < end_world;
-        stepWorld<kJoints>(ctx, v, p, v.active ? w : first_world, &group_level, bs, slot);
+        stepWorld<kJoints, kHullSlots>(ctx, v, p, v.active ? w : first_world, &group_level, bs, slot);
     }
 }
 
@@ -44,8 +46,9 @@ physStepKernel(const __grid_constant__ StepParams p, int threads_per_world, int 
 typedef void (*StepKernel)(const StepParams, int, int, int, int, int, int);
 // {max block threads, min resident blocks}; fn_joints is the same kernel with the joint
 // solve compiled in (mdr_phys_set_joints), so that batches without joints do not carry it.
-struct KernelVariant { int threads, min_blocks; StepKernel fn, fn_joints; };
-#define MDR_STEP_VARIANT(T, B) { T, B, mdr::physStepKernel<T, B, false>, mdr::physStepKernel<T, B, true> }
+struct KernelVariant { int threads, min_blocks; StepKernel fn, fn_joints, fn_big; };
+#define MDR_STEP_VARIANT(T, B) { T, B, mdr::physStepKernel<T, B, false>, mdr::physStepKernel<T, B, true>, \
+                                 mdr::physStepKernel<T, B, true, 2> }
 
 }  // namespace mdr
 

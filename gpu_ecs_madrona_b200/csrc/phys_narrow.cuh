@@ -538,11 +538,12 @@ MDR_HD void probeContact(const StepParams &p, int sub, int pi, const Manifold *m
 // reference's scan would meet at that face (or it has stopped at an earlier face, positive as well): doSAT
 // reports no contact either way (:678-758), so returning "no contact" here is exact, not an approximation.
 // A stale hint (another pair now sits in the slot) is just an axis that may fail to separate: the warp runs.
+constexpr uint32_t kHintFaceB = 64u;     // hint byte = 1 + face (< 64) + kHintFaceB * (a face of the pair's second hull)
 MDR_HD bool satHintSeparates(const WorldView &v, const StepParams &p, int a, int b, uint32_t hint)
 {
     const uint32_t code = hint - 1u;
-    const int f = (int)(code & 31u);
-    const bool face_of_b = (code >> 5) != 0u;
+    const int f = (int)(code & (kHintFaceB - 1u));
+    const bool face_of_b = (code & kHintFaceB) != 0u;
     const BodyXf xf = bodyXf(v, p, face_of_b ? b : a), xo = bodyXf(v, p, face_of_b ? a : b);
     if (f >= MDR_LDG(&xf.o->num_faces)) return false;
     const Plane pl = worldPlane(xf, p.a.planes + 4 * MDR_LDG(&xf.o->face_off), f);

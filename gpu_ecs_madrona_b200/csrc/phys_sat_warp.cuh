@@ -1,7 +1,7 @@
 // Warp-cooperative hull-hull SAT (device only). The thread-per-pair narrowphase
 // marks the hull-hull pairs that pass the AABB reject; here one warp takes one
 // marked pair: lane k holds world vertex k and world face plane k of both hulls
-// (MDR_MAX_HULL_VERTS / FACES = 32), face queries run one face per lane, the
+// (32 per slot, up to MDR_MAX_HULL_VERTS / FACES = 64 in the two-slot variant), face queries run one face per lane, the
 // edge-edge query one edge pair per lane, and warp arg-max reductions pick the
 // same winner as the reference's sequential scans (first strict maximum =
 // largest value, lowest index; src/physics/narrowphase.cpp:352-378,474-576).
@@ -22,12 +22,51 @@ __device__ __forceinline__ V3 shfl3(V3 v, int src)
                __shfl_sync(MDR_FULL, v.z, src));
 }
 
-// Vertex k of a hull whose world vertices sit one per lane. Every lane of the
+// Hulls of up to 32 * kSlots vertices / faces: lane l holds vertex (and face plane) l of every slot, element k
+// lives in slot k >> 5 of lane k & 31. kSlots = 1 is the common case (cubes, the 4-32 vertex hulls of the asset
+// tests); kSlots = 2 (64 vertices / faces) is its own kernel variant, chosen at creation when an object needs it,
+// so that the common case does not carry the second set of registers.
+template <int kSlots> struct LaneV3 { V3 v[kSlots]; };
+template <int kSlots> struct LanePlane { Plane p[kSlots]; };
+
+// Element k; every lane of the warp takes part, k may differ from lane to lane.
+template <int kSlots> __device__ __forceinline__ V3 laneGet(const LaneV3<kSlots> &a, int k)
+{
+    V3 r = shfl3(a.v[0], k & 31);
+#pragma unroll
+    for (int s = 1; s < kSlots; s++) {
+        const V3 o = shfl3(a.v[s], k & 31);
+        if ((k >> 5) == s) r = o;
+    }
+    return r;
+}
+template <int kSlots> __device__ __forceinline__ V3 laneGetNormal(const LanePlane<kSlots> &a, int k)
+{
+    V3 r = shfl3(a.p[0].n, k & 31);
+#pragma unroll
+    for (int s = 1; s < kSlots; s++) {
+        const V3 o = shfl3(a.p[s].n, k & 31);
+        if ((k >> 5) == s) r = o;
+    }
+    return r;
+}
+template <int kSlots> __device__ __forceinline__ float laneGetD(const LanePlane<kSlots> &a, int k)
+{
+    float r = __shfl_sync(MDR_FULL, a.p[0].d, k & 31);
+#pragma unroll
+    for (int s = 1; s < kSlots; s++) {
+        const float o = __shfl_sync(MDR_FULL, a.p[s].d, k & 31);
+        if ((k >> 5) == s) r = o;
+    }
+    return r;
+}
+
+// Vertex k of a hull whose world vertices sit in the lanes. Every lane of the
 // warp must call at() together (contact generation below runs on all lanes
 // with identical inputs, so its control flow is uniform).
-struct LaneVerts {
-    V3 mine;
-    __device__ __forceinline__ V3 at(int k) const { return shfl3(mine, k); }
+template <int kSlots> struct LaneVerts {
+    LaneV3<kSlots> mine;
+    __device__ __forceinline__ V3 at(int k) const { return laneGet<kSlots>(mine, k); }
 };
 
 // emitContact with one contact point per lane (lanes 0..3); every lane holds
@@ -74,16 +113,31 @@ __device__ __forceinline__ void warpArgMax(float &val, int &idx)
     }
 }
 
-// One lane per face of `a`: distance of the other hull (vertices in `vb`, one
-// per lane, nvb of them) from the face plane held by this lane.
-__device__ __forceinline__ float faceSeparationLane(Plane pl, bool lane_has_face, V3 vb, int nvb)
+// The faces of `a` held by this lane (one per slot): distance of the other hull (vertices in `vb`, nvb of them)
+// from each, reduced to this lane's first strict maximum (value, face index).
+template <int kSlots>
+__device__ __forceinline__ void faceSeparationLane(const LanePlane<kSlots> &pa, int nfa, const LaneV3<kSlots> &vb, int nvb,
+                                                   int lane, float &best, int &best_face)
 {
-    float m = FLT_MAX;
-    for (int k = 0; k < nvb; k++) {
-        float d = dot(pl.n, shfl3(vb, k));
-        if (d < m) m = d;
+    float m[kSlots];
+#pragma unroll
+    for (int s = 0; s < kSlots; s++) m[s] = FLT_MAX;
+    for (int k = 0; k < nvb; k++) {                      // k is warp-uniform
+        const V3 v = laneGet<kSlots>(vb, k);
+#pragma unroll
+        for (int s = 0; s < kSlots; s++) {
+            const float d = dot(pa.p[s].n, v);
+            if (d < m[s]) m[s] = d;
+        }
     }
-    return lane_has_face ? m - pl.d : -FLT_MAX;
+    best = -FLT_MAX;
+    best_face = lane;
+#pragma unroll
+    for (int s = 0; s < kSlots; s++) {
+        const int f = lane + 32 * s;
+        const float sep = f < nfa ? m[s] - pa.p[s].d : -FLT_MAX;
+        if (s == 0 || sep > best) { best = sep; best_face = f; }
+    }
 }
 
 // Edge-edge query, one (edge of a, edge of b) pair per lane and round
@@ -91,10 +145,11 @@ __device__ __forceinline__ float faceSeparationLane(Plane pl, bool lane_has_face
 // :418-426; edgeDistance :433-472). Returns the warp-wide winner.
 struct EdgeWin { float sep; V3 normal; int ea, eb; };
 
-__device__ __forceinline__ EdgeWin edgeQueryWarp(int lane, V3 va, Plane pa, const HEdgeDev *hea_tab,
-                                                 const uint32_t *edges_a, int nea, V3 centre_a,
-                                                 V3 vb, Plane pb, const HEdgeDev *heb_tab,
-                                                 const uint32_t *edges_b, int neb)
+template <int kSlots>
+__device__ __forceinline__ EdgeWin edgeQueryWarp(int lane, const LaneV3<kSlots> &va, const LanePlane<kSlots> &pa,
+                                                 const HEdgeDev *hea_tab, const uint32_t *edges_a, int nea, V3 centre_a,
+                                                 const LaneV3<kSlots> &vb, const LanePlane<kSlots> &pb,
+                                                 const HEdgeDev *heb_tab, const uint32_t *edges_b, int neb)
 {
     const int total = nea * neb;
     float best = -FLT_MAX;
@@ -111,10 +166,10 @@ __device__ __forceinline__ EdgeWin edgeQueryWarp(int lane, V3 va, Plane pa, cons
         const int ea_next_root = (int)MDR_LDG(&hea_tab[ea.next].root);
         const int eb_next_root = (int)MDR_LDG(&heb_tab[eb.next].root);
         // every lane takes part in every shuffle
-        const V3 an1 = shfl3(pa.n, (int)ea.poly), an2 = shfl3(pa.n, ea_twin_poly);
-        const V3 bn1 = shfl3(pb.n, (int)eb.poly), bn2 = shfl3(pb.n, eb_twin_poly);
-        const V3 a1 = shfl3(va, (int)ea.root), a2 = shfl3(va, ea_next_root);
-        const V3 b1 = shfl3(vb, (int)eb.root), b2 = shfl3(vb, eb_next_root);
+        const V3 an1 = laneGetNormal<kSlots>(pa, (int)ea.poly), an2 = laneGetNormal<kSlots>(pa, ea_twin_poly);
+        const V3 bn1 = laneGetNormal<kSlots>(pb, (int)eb.poly), bn2 = laneGetNormal<kSlots>(pb, eb_twin_poly);
+        const V3 a1 = laneGet<kSlots>(va, (int)ea.root), a2 = laneGet<kSlots>(va, ea_next_root);
+        const V3 b1 = laneGet<kSlots>(vb, (int)eb.root), b2 = laneGet<kSlots>(vb, eb_next_root);
         float sep = -FLT_MAX;
         V3 normal = mk3(0.f, 0.f, 0.f);
         if (valid && minkowskiFace(an1, an2, -bn1, -bn2)) {
@@ -149,6 +204,7 @@ __device__ __forceinline__ EdgeWin edgeQueryWarp(int lane, V3 va, Plane pa, cons
 
 // One queued hull-hull pair, one warp. doSAT + generateContacts for two hulls
 // (narrowphase.cpp:678-758,1366-1513).
+template <int kSlots>
 __device__ __forceinline__ void hullHullWarp(WorldView &v, const StepParams &p, int pi, int lane,
                                              bool probing, int sub)
 {
@@ -172,41 +228,59 @@ __device__ __forceinline__ void hullHullWarp(WorldView &v, const StepParams &p, 
     // The first face query needs A's planes and B's vertices only; most pairs that reach a warp in a resting
     // scene (neighbours whose boxes overlap after a few degrees of yaw) end there, separated: the other
     // half of the world-space hulls is built only for those that go on.
-    const V3 vb = lane < nvb ? worldVert(xb, src_vb, lane) : zero;
-    const Plane pa = lane < nfa ? worldPlane(xa, src_pa, lane) : none;
+    LaneV3<kSlots> va, vb;
+    LanePlane<kSlots> pa, pb;
+#pragma unroll
+    for (int s = 0; s < kSlots; s++) {
+        const int k = lane + 32 * s;
+        vb.v[s] = k < nvb ? worldVert(xb, src_vb, k) : zero;
+        pa.p[s] = k < nfa ? worldPlane(xa, src_pa, k) : none;
+    }
 
     Manifold m;
     int ref = -1, alt = -1;
     bool hit = false;
     uint32_t hint = 0u;         // what the pair's thread tries first next time (satHintSeparates)
     do {
-        float fa_sep = faceSeparationLane(pa, lane < nfa, vb, nvb);
-        int fa_face = lane;
+        float fa_sep;
+        int fa_face;
+        faceSeparationLane<kSlots>(pa, nfa, vb, nvb, lane, fa_sep, fa_face);
         warpArgMax(fa_sep, fa_face);
         if (fa_sep > 0.0f) { hint = 1u + (uint32_t)fa_face; break; }
-        const V3 va = lane < nva ? worldVert(xa, src_va, lane) : zero;
-        const Plane pb = lane < nfb ? worldPlane(xb, src_pb, lane) : none;
-        float fb_sep = faceSeparationLane(pb, lane < nfb, va, nva);
-        int fb_face = lane;
+#pragma unroll
+        for (int s = 0; s < kSlots; s++) {
+            const int k = lane + 32 * s;
+            va.v[s] = k < nva ? worldVert(xa, src_va, k) : zero;
+            pb.p[s] = k < nfb ? worldPlane(xb, src_pb, k) : none;
+        }
+        float fb_sep;
+        int fb_face;
+        faceSeparationLane<kSlots>(pb, nfb, va, nva, lane, fb_sep, fb_face);
         warpArgMax(fb_sep, fb_face);
-        if (fb_sep > 0.0f) { hint = 1u + 32u + (uint32_t)fb_face; break; }
-        const EdgeWin eq = edgeQueryWarp(lane, va, pa, ta.he, edges_a, nea, xa.t, vb, pb, tb.he, edges_b, neb);
+        if (fb_sep > 0.0f) { hint = 1u + (uint32_t)kHintFaceB + (uint32_t)fb_face; break; }
+        const EdgeWin eq = edgeQueryWarp<kSlots>(lane, va, pa, ta.he, edges_a, nea, xa.t, vb, pb, tb.he, edges_b, neb);
         if (eq.sep > 0.0f) break;
         const bool face_a = fa_sep > eq.sep, face_b = fb_sep > eq.sep;
-        LaneVerts xva, xvb;
+        LaneVerts<kSlots> xva, xvb;
         xva.mine = va; xvb.mine = vb;
         if (face_a || face_b) {
             const bool a_ref = fa_sep >= fb_sep;
             const int rf = a_ref ? fa_face : fb_face;
             Plane rp;
-            rp.n = a_ref ? shfl3(pa.n, rf) : shfl3(pb.n, rf);
-            rp.d = a_ref ? __shfl_sync(MDR_FULL, pa.d, rf) : __shfl_sync(MDR_FULL, pb.d, rf);
+            rp.n = a_ref ? laneGetNormal<kSlots>(pa, rf) : laneGetNormal<kSlots>(pb, rf);
+            rp.d = a_ref ? laneGetD<kSlots>(pa, rf) : laneGetD<kSlots>(pb, rf);
             // incident face: most anti-parallel normal of the other hull, first
             // strict minimum (narrowphase.cpp:578-624) = arg-max of the negation
-            const Plane po = a_ref ? pb : pa;
             const int nfo = a_ref ? nfb : nfa;
-            float neg = lane < nfo ? -dot(po.n, rp.n) : -FLT_MAX;
+            float neg = -FLT_MAX;
             int inc = lane;
+#pragma unroll
+            for (int s = 0; s < kSlots; s++) {
+                const int f = lane + 32 * s;
+                const V3 on = a_ref ? pb.p[s].n : pa.p[s].n;
+                const float val = f < nfo ? -dot(on, rp.n) : -FLT_MAX;
+                if (s == 0 || val > neg) { neg = val; inc = f; }
+            }
             warpArgMax(neg, inc);
             // all lanes, same inputs: vertices come by shuffle instead of being recomputed
             if (a_ref) faceContact(m, rp, rf, inc, ta, xva, tb, xvb);
@@ -234,6 +308,7 @@ __device__ __forceinline__ void hullHullWarp(WorldView &v, const StepParams &p, 
 // The marked pairs of the world, in turn over the warps of its thread group.
 // Every warp walks the same marks (nobody writes the pair words in this phase)
 // and takes every nwarps-th one.
+template <int kSlots>
 __device__ __forceinline__ void satQueueWarp(const BlockCtx &c, WorldView &v, const StepParams &p,
                                              bool probing, int sub)
 {
@@ -246,7 +321,7 @@ __device__ __forceinline__ void satQueueWarp(const BlockCtx &c, WorldView &v, co
         while (marks) {
             const int bit = __ffs(marks) - 1;
             marks &= marks - 1;
-            if (turn == warp) hullHullWarp(v, p, base + bit, lane, probing, sub);
+            if (turn == warp) hullHullWarp<kSlots>(v, p, base + bit, lane, probing, sub);
             if (++turn == nwarps) turn = 0;
         }
     }

@@ -96,7 +96,7 @@ __device__ __forceinline__ void solveDense(BlockSolve *bs, const StepParams &p, 
 // whole block: the level loops must run the same number of barriers in every
 // world slot, so they run to the block-wide maximum. A slot without a world
 // this round (`!v.active`) walks the same barriers with zero rows.
-template <bool kJoints = true>
+template <bool kJoints = true, int kHullSlots = 1>
 MDR_HD void stepWorld(const BlockCtx &c, WorldView &v, const StepParams &p, int w, int *group_level,
                       BlockSolve *bs = nullptr, int slot = 0)
 {
@@ -141,7 +141,7 @@ MDR_HD void stepWorld(const BlockCtx &c, WorldView &v, const StepParams &p, int 
         c.sync();
         MDR_PHASE(4);
 #if defined(__CUDA_ARCH__)
-        satQueueWarp(c, v, p, probing, sub);
+        satQueueWarp<kHullSlots>(c, v, p, probing, sub);
         c.sync();
         MDR_PHASE(5);
 #endif

@@ -133,12 +133,13 @@ struct StepParams {
 
 enum { MDR_ERR_PAIR_OVERFLOW = 1 };
 
-// Compile-time caps of the hull-hull path (per-thread local arrays).
+// Caps of the hull-hull path: 32 vertices / faces per slot of the warp SAT (phys_sat_warp.cuh), two slots in the
+// big-hull kernel variant; also the per-thread arrays of the host emulation.
 #ifndef MDR_MAX_HULL_VERTS
-#define MDR_MAX_HULL_VERTS 32
+#define MDR_MAX_HULL_VERTS 64
 #endif
 #ifndef MDR_MAX_HULL_FACES
-#define MDR_MAX_HULL_FACES 32
+#define MDR_MAX_HULL_FACES 64
 #endif
 #define MDR_MAX_BODIES 1024      // rows are packed in 10 bits
 #define MDR_MAX_LEVEL 2047        // 11 bits of the pair word

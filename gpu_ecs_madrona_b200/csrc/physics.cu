@@ -99,6 +99,7 @@ struct mdr_phys {
     bool external_tables = false;            // columns and row counts belong to an ECS archetype
     StepKernel kernel = nullptr;             // the variant in use: kernel_plain, or kernel_joints once joints are set
     StepKernel kernel_plain = nullptr, kernel_joints = nullptr;
+    bool big_hulls = false;                  // an object has more than 32 vertices / faces: the two-slot SAT variant
     int threads = 0, blocks = 0, blocks_per_sm = 0, overflow_per_slot = 0;
     int threads_per_world = 0, worlds_per_block = 0, lockstep = 1;
     size_t smem_bytes = 0, slot_bytes = 0;
@@ -302,8 +303,9 @@ static int32_t createImpl(const mdr_phys_config *cfg, const mdr_object *objs, in
         if (want_min_blocks ? kv.min_blocks == want_min_blocks : kv.min_blocks <= fit) var = &kv;
     }
     if (!var) { mdr_phys_destroy(p); return MDR_EINVAL; }
-    p->kernel = p->kernel_plain = var->fn;
-    p->kernel_joints = var->fn_joints;
+    p->big_hulls = p->assets.max_verts > 32 || p->assets.max_faces > 32;
+    p->kernel = p->kernel_plain = p->big_hulls ? var->fn_big : var->fn;
+    p->kernel_joints = p->big_hulls ? var->fn_big : var->fn_joints;
     for (StepKernel k : { p->kernel_plain, p->kernel_joints }) {
         REQ_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p->smem_bytes));
         REQ_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributePreferredSharedMemoryCarveout, 100));

@@ -5,7 +5,8 @@
 #include "exp_list.h"      // written by build_exp.sh from $VARIANTS: #define MDR_EXP_LIST MDR_STEP_VARIANT(T, B), ...
 #undef MDR_STEP_VARIANT
 // joints variant aliased to the plain one: halves the build
-#define MDR_STEP_VARIANT(T, B) { T, B, mdr::physStepKernel<T, B, false>, mdr::physStepKernel<T, B, false> }
+#define MDR_STEP_VARIANT(T, B) { T, B, mdr::physStepKernel<T, B, false>, mdr::physStepKernel<T, B, false>, \
+                                 mdr::physStepKernel<T, B, false> }
 static const mdr::KernelVariant kPart[] = { MDR_EXP_LIST };
 const mdr::KernelVariant *mdrStepVariants0(int *n) { *n = (int)(sizeof(kPart) / sizeof(kPart[0])); return kPart; }
 const mdr::KernelVariant *mdrStepVariants1(int *n) { *n = 0; return kPart; }

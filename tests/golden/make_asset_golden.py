@@ -40,6 +40,18 @@ def prism(n, r=0.5, h=0.5, top=1.0, phase=0.0):
     return v, f
 
 
+def barrel(n, rings, r=0.55, h=0.45):
+    """`rings` rings of n vertices on an ellipsoidal profile (strictly convex): n * rings vertices,
+    n * (rings - 1) quads + two n-gon caps."""
+    zs = np.linspace(-h, h, rings)
+    rad = r * np.sqrt(1.0 - 0.6 * (zs / h) ** 2)
+    v = np.concatenate([ring(n, rad[k], zs[k]) for k in range(rings)])
+    f = [list(range(n - 1, -1, -1)), list(range(n * (rings - 1), n * rings))]
+    for k in range(rings - 1):
+        f += [[k * n + i, k * n + (i + 1) % n, (k + 1) * n + (i + 1) % n, (k + 1) * n + i] for i in range(n)]
+    return v, f
+
+
 def pyramid(n, r=0.6, h=0.5, phase=0.0):
     v = np.concatenate([ring(n, r, -h * 0.5, phase), [[0.0, 0.0, h]]])
     f = [list(range(n - 1, -1, -1))] + [[k, (k + 1) % n, n] for k in range(n)]

@@ -214,9 +214,21 @@ def _capacity_scene(n_sides, num_worlds):
     return sc
 
 
+def _barrel_scene(num_worlds, n=16, rings=4):
+    """A pile of 64-vertex / 50-face barrels (two slots of the warp SAT) and rocks over a plane."""
+    v, f = mag.barrel(n, rings)
+    text = mag.obj_text(f"barrel{n}x{rings}", v, f, 9, extras=False)
+    sc = scenes.hull_pile(num_worlds, num_bodies=8, seed=29, spread=1.0)
+    big = assets.hull_object(text, inv_mass=0.7, mu=0.45)
+    sc.objects = [big, sc.objects[7]] + [sc.objects[-1]]
+    sc.obj_ids[:, 1:] = (np.arange(8)[None] + np.arange(num_worlds)[:, None]) % 2
+    sc.obj_ids[:, 0] = 2
+    return sc
+
+
 def test_hull_at_capacity_and_beyond(port_oracle, emu_lib):
-    """MDR_MAX_HULL_VERTS / FACES = 32 (one vertex / face per lane of the warp-per-pair SAT): a 32-vertex hull
-    steps bit for bit, a 34-vertex one is refused at creation (no silent truncation)."""
+    """One slot of the warp SAT holds 32 vertices / faces, the big-hull variant two (MDR_MAX_HULL_VERTS / FACES = 64):
+    32- and 64-vertex hulls step bit for bit, a 66-vertex one is refused at creation (no silent truncation)."""
     sc = _capacity_scene(16, 3)
     assert len(sc.objects[0].verts) == 32 and len(sc.objects[0].polys) == 18
     o = port_oracle.Oracle(sc, "port")
@@ -225,20 +237,28 @@ def test_hull_at_capacity_and_beyond(port_oracle, emu_lib):
         o.step()
         e.run()
         assert_state_equal(e.state(), o.state(), None, f"32-vertex hulls step {st}")
+    sc = _barrel_scene(2)
+    assert len(sc.objects[0].verts) == 64 and len(sc.objects[0].polys) == 50
+    o = port_oracle.Oracle(sc, "port")
+    e = phys.PhysExecutor(sc, lib=emu_lib)
+    for st in range(15):
+        o.step()
+        e.run()
+        assert_state_equal(e.state(), o.state(), None, f"64-vertex hulls step {st}")
     with pytest.raises(phys.MadronaError):
-        phys.PhysExecutor(_capacity_scene(17, 1), lib=emu_lib)
+        phys.PhysExecutor(_capacity_scene(33, 1), lib=emu_lib)
 
 
 def test_port_matches_compiled_reference_at_hull_capacity(port_oracle, ref_oracle):
-    sc = _capacity_scene(16, 6)
-    r = ref_oracle.Oracle(sc, "reference")
-    p = port_oracle.Oracle(sc, "port")
-    for st in range(30):
-        r.step()
-        p.step()
-        det = p.indeterminate() == 0
-        assert_state_equal(p.state(), r.state(), det, f"32-vertex hulls step {st}")
-    assert det.sum() >= 3
+    for name, sc in (("32", _capacity_scene(16, 6)), ("64", _barrel_scene(6))):
+        r = ref_oracle.Oracle(sc, "reference")
+        p = port_oracle.Oracle(sc, "port")
+        for st in range(30):
+            r.step()
+            p.step()
+            det = p.indeterminate() == 0
+            assert_state_equal(p.state(), r.state(), det, f"{name}-vertex hulls step {st}")
+        assert det.sum() >= 3, name
 
 
 @pytest.mark.gpu
@@ -251,7 +271,24 @@ def test_cuda_hull_at_capacity_and_beyond(cuda_lib, port_oracle):
         e.run()
         assert_state_equal(e.state(), o.state(), None, f"32-vertex hulls step {st}")
     with pytest.raises(phys.MadronaError):
-        phys.PhysExecutor(_capacity_scene(17, 1))
+        phys.PhysExecutor(_capacity_scene(33, 1))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("threads", [32, 64])
+def test_cuda_64_vertex_hulls(cuda_lib, port_oracle, threads):
+    """hulls beyond 32 vertices / faces. 64-vertex, 50-face barrels through the two-slot warp SAT
+    (its own kernel variant), bit for bit against the port (itself pinned on the compiled reference for this scene in
+    test_port_matches_compiled_reference_at_hull_capacity), incl. the probed contact manifolds of one world."""
+    sc = _barrel_scene(20)
+    o = port_oracle.Oracle(sc, "port")
+    e = phys.PhysExecutor(sc, block_threads=threads)
+    for st in range(40):
+        o.step(1, 8)
+        e.run()
+        assert_state_equal(e.state(), o.state(), None, f"64-vertex hulls step {st}")
+    assert e.stats()[1].sum() > 0
+    e.close(); o.close()
 
 
 def test_obj_loader_dialect_matches_compiled_reference(host_lib, tmp_path):
