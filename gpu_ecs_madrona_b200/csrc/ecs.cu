@@ -983,6 +983,19 @@ float mdr_ecs_step_ms(mdr_ecs *e, int32_t *steps)
     return n > 0 ? (float)(ms / n) : -1.f;
 }
 
+#ifdef MDR_ECS_NODE_CLOCKS
+// profiling builds only: reads and clears the per-node clock sums
+int32_t mdr_ecs_node_clocks(mdr_ecs *e, unsigned long long *out, int32_t n)
+{
+    REQ_CUDA(cudaSetDevice(e->cfg.gpu_id));
+    REQ_CUDA(cudaStreamSynchronize(e->stream));
+    REQ_CUDA(cudaMemcpyFromSymbol(out, g_node_clocks, sizeof(unsigned long long) * (size_t)n));
+    static unsigned long long zeros[kMaxNodes + 2] = {};
+    REQ_CUDA(cudaMemcpyToSymbol(g_node_clocks, zeros, sizeof(zeros)));
+    return MDR_OK;
+}
+#endif
+
 int32_t mdr_ecs_launches_per_step(mdr_ecs *e)
 {
     if (!e || !e->built) return MDR_EINVAL;

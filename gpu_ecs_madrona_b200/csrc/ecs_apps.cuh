@@ -96,9 +96,16 @@ __device__ __forceinline__ void fvsBlast(Context &ctx, uint32_t tx, uint32_t ty,
     for (int arch = 0; arch < 2; arch++) {
         const Position *pos = ctx.column<Position>(arch, 1);
         Health *hp = ctx.column<Health>(arch, 2);
-        for (int32_t i = laneId(), n = ctx.numRows(arch); i < n; i += 32) {
-            const mdr_vec3 p = pos[i];
-            if (mdr_fvs_in_blast(&target, &p)) atomicSub(&hp[i].hp, MDR_FVS_BLAST_DAMAGE);
+        // four independent loads in flight per lane before the first test (the rows are independent; one load,
+        // one test, one atomic at a time makes every 32-row slice wait a full memory latency)
+        const int32_t n = ctx.numRows(arch);
+        for (int32_t base = laneId(); base < n; base += 128) {
+            mdr_vec3 p[4];
+#pragma unroll
+            for (int k = 0; k < 4; k++) if (base + 32 * k < n) p[k] = pos[base + 32 * k];
+#pragma unroll
+            for (int k = 0; k < 4; k++)
+                if (base + 32 * k < n && mdr_fvs_in_blast(&target, &p[k])) atomicSub(&hp[base + 32 * k].hp, MDR_FVS_BLAST_DAMAGE);
         }
     }
 }

@@ -714,6 +714,28 @@ __device__ inline void storeWorld(Context &ctx)
 // ParallelForNode<ContextT, Fn, Components...>::run (include/madrona/taskgraph.inl:
 // 63-71) -> Context::forEach -> StateManager::iterateEntities (state.inl:358-396):
 // matching archetypes in id order, rows in order; lanes take consecutive rows.
+// The 32-row slices of one table; the column tile addresses arrive as arguments (computed once per table).
+// Asks for the rows of the NEXT slice while this one is worked on (non-binding L1 prefetch): a slice otherwise
+// starts with a load nobody has asked for yet, and the warp has nothing else in flight.
+template <typename T> __device__ __forceinline__ void prefetchRow(const T *p)
+{
+#ifndef MDR_ECS_NO_PREFETCH
+    asm volatile("prefetch.global.L1 [%0];" ::"l"(p));
+#endif
+}
+
+template <auto Fn, typename... Cs>
+__device__ __forceinline__ void sliceLoop(Context &ctx, int32_t n, int lane, Cs *...cols)
+{
+    for (int32_t base = 0; base < n; base += 32) {
+        const int32_t row = base + lane;
+        if (row + 32 < n) (prefetchRow(cols + row + 32), ...);
+        if (row < n) Fn(ctx, cols[row]...);
+        __syncwarp();
+        if (__any_sync(kFull, ctx.pend != 0u)) applyPending(ctx);
+    }
+}
+
 template <auto Fn, typename... Cs, int... Is>
 __device__ __forceinline__ void parallelForImpl(Context &ctx, const NodeDev &nd, std::integer_sequence<int, Is...>)
 {
@@ -721,12 +743,9 @@ __device__ __forceinline__ void parallelForImpl(Context &ctx, const NodeDev &nd,
     for (int m = 0; m < nd.num_match; m++) {
         const MatchDev &mt = nd.match[m];
         const int32_t n = ctx.numRows(mt.arch);
-        for (int32_t base = 0; base < n; base += 32) {
-            const int32_t row = base + lane;
-            if (row < n) Fn(ctx, ctx.column<Cs>(mt.arch, mt.col[Is])[row]...);
-            __syncwarp();
-            if (__any_sync(kFull, ctx.pend != 0u)) applyPending(ctx);
-        }
+        // the tile addresses of this world's columns, once per table (not once per row: the descriptors sit in
+        // shared memory and the compiler must assume every store of a system may change them)
+        sliceLoop<Fn, Cs...>(ctx, n, lane, ctx.column<Cs>(mt.arch, mt.col[Is])...);
         __syncwarp();
     }
 }
@@ -741,6 +760,26 @@ __device__ __forceinline__ void parallelFor(Context &ctx, const NodeDev &nd)
 // order, each executed by ALL 32 lanes: Nested(ctx, args) is called converged and
 // strides its own loop by lane. Valid when the nested job's effects are not read by
 // later rows of the same node (the reference runs it inline).
+template <auto Fn, auto Nested, typename... Cs>
+__device__ __forceinline__ void sliceLoopNested(Context &ctx, int32_t n, int lane, Cs *...cols)
+{
+    for (int32_t base = 0; base < n; base += 32) {
+        const int32_t row = base + lane;
+        if (row + 32 < n) (prefetchRow(cols + row + 32), ...);
+        if (row < n) Fn(ctx, cols[row]...);
+        __syncwarp();
+        unsigned jobs = __ballot_sync(kFull, (ctx.pend & 4u) != 0u);
+        while (jobs) {
+            const int src = __ffs(jobs) - 1;
+            jobs &= jobs - 1;
+            Nested(ctx, __shfl_sync(kFull, ctx.nested[0], src), __shfl_sync(kFull, ctx.nested[1], src),
+                   __shfl_sync(kFull, ctx.nested[2], src), __shfl_sync(kFull, ctx.nested[3], src));
+        }
+        ctx.pend &= ~4u;
+        __syncwarp();
+        if (__any_sync(kFull, ctx.pend != 0u)) applyPending(ctx);
+    }
+}
 template <auto Fn, auto Nested, typename... Cs, int... Is>
 __device__ __forceinline__ void parallelForNestedImpl(Context &ctx, const NodeDev &nd, std::integer_sequence<int, Is...>)
 {
@@ -748,21 +787,7 @@ __device__ __forceinline__ void parallelForNestedImpl(Context &ctx, const NodeDe
     for (int m = 0; m < nd.num_match; m++) {
         const MatchDev &mt = nd.match[m];
         const int32_t n = ctx.numRows(mt.arch);
-        for (int32_t base = 0; base < n; base += 32) {
-            const int32_t row = base + lane;
-            if (row < n) Fn(ctx, ctx.column<Cs>(mt.arch, mt.col[Is])[row]...);
-            __syncwarp();
-            unsigned jobs = __ballot_sync(kFull, (ctx.pend & 4u) != 0u);
-            while (jobs) {
-                const int src = __ffs(jobs) - 1;
-                jobs &= jobs - 1;
-                Nested(ctx, __shfl_sync(kFull, ctx.nested[0], src), __shfl_sync(kFull, ctx.nested[1], src),
-                       __shfl_sync(kFull, ctx.nested[2], src), __shfl_sync(kFull, ctx.nested[3], src));
-            }
-            ctx.pend &= ~4u;
-            __syncwarp();
-            if (__any_sync(kFull, ctx.pend != 0u)) applyPending(ctx);
-        }
+        sliceLoopNested<Fn, Nested, Cs...>(ctx, n, lane, ctx.column<Cs>(mt.arch, mt.col[Is])...);
         __syncwarp();
     }
 }
@@ -775,26 +800,31 @@ __device__ __forceinline__ void parallelForNested(Context &ctx, const NodeDev &n
 // ParallelForNode in immediate mode: systems may call makeEntityNowImmediate / destroyEntityNowImmediate
 // (any number, results returned at once); see Context::waitTurn. The row count of a table is read once
 // per archetype, as the reference's loop bound is (state.inl:358-396).
+template <auto Fn, typename... Cs>
+__device__ __forceinline__ void sliceLoopImmediate(Context &ctx, int32_t n, int lane, Cs *...cols)
+{
+    volatile WarpShared *vws = ctx.ws;
+    for (int32_t base = 0; base < n; base += 32) {
+        const int32_t row = base + lane;
+        const unsigned active = __ballot_sync(kFull, row < n);
+        if (lane == 0) vws->done = ~active;
+        __syncwarp();
+        if (row < n) {
+            Fn(ctx, cols[row]...);
+            __threadfence_block();
+            atomicOr(&ctx.ws->done, 1u << lane);
+        }
+        __syncwarp();
+    }
+}
 template <auto Fn, typename... Cs, int... Is>
 __device__ __forceinline__ void parallelForImmediateImpl(Context &ctx, const NodeDev &nd, std::integer_sequence<int, Is...>)
 {
     const int lane = laneId();
-    volatile WarpShared *vws = ctx.ws;
     for (int m = 0; m < nd.num_match; m++) {
         const MatchDev &mt = nd.match[m];
         const int32_t n = ctx.numRows(mt.arch);
-        for (int32_t base = 0; base < n; base += 32) {
-            const int32_t row = base + lane;
-            const unsigned active = __ballot_sync(kFull, row < n);
-            if (lane == 0) vws->done = ~active;
-            __syncwarp();
-            if (row < n) {
-                Fn(ctx, ctx.column<Cs>(mt.arch, mt.col[Is])[row]...);
-                __threadfence_block();
-                atomicOr(&ctx.ws->done, 1u << lane);
-            }
-            __syncwarp();
-        }
+        sliceLoopImmediate<Fn, Cs...>(ctx, n, lane, ctx.column<Cs>(mt.arch, mt.col[Is])...);
         __syncwarp();
     }
 }
@@ -834,10 +864,20 @@ __device__ __forceinline__ const NodeDev *loadDescriptors(BlockDescriptors *bd, 
     return nodes_fit ? bd->node : E->node + first;
 }
 
+#ifdef MDR_ECS_NODE_CLOCKS
+__device__ unsigned long long g_node_clocks[kMaxNodes + 2];     // profiling builds: clock64 per node, summed over warps
+#endif
+
 template <typename Builtin>
 __device__ __forceinline__ void runNodes(Context &ctx, const NodeDev *nodes, int count, Builtin builtin)
 {
+#ifdef MDR_ECS_NODE_CLOCKS
+    long long t_last = clock64();
+#endif
     for (int ni = 0; ni < count; ni++) {
+#ifdef MDR_ECS_NODE_CLOCKS
+        if (ni > 0 && laneId() == 0) { const long long now = clock64(); atomicAdd(&g_node_clocks[ni - 1], (unsigned long long)(now - t_last)); t_last = now; }
+#endif
         const NodeDev &nd = nodes[ni];
         switch (nd.kind) {
         case kNodeParallelFor:
@@ -854,6 +894,9 @@ __device__ __forceinline__ void runNodes(Context &ctx, const NodeDev *nodes, int
         }
         __syncwarp();
     }
+#ifdef MDR_ECS_NODE_CLOCKS
+    if (count > 0 && laneId() == 0) atomicAdd(&g_node_clocks[count - 1], (unsigned long long)(clock64() - t_last));
+#endif
 }
 
 constexpr int kWarpsPerBlock = 8;
