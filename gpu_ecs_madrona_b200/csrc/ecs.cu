@@ -244,6 +244,96 @@ __global__ void __launch_bounds__(256) ecsExportCopy(const EcsDev *__restrict__ 
     }
 }
 
+// ---- the whole step in ONE launch (every world resident at once: num_worlds <= grid x 8 warps) ----------
+// export copy-in -> the nodes of the graph -> GRID BARRIER -> export offsets -> export copy-out, one warp per
+// world. What the four launches of the run graph do (MWCudaExecutor's graph, src/mw/cuda_exec.cpp:1519-1690),
+// without the three launch boundaries: at 1024 worlds a step is a few microseconds of work and the boundaries
+// are most of it. The barrier is the only cross-world point of the step: the offsets are a prefix sum over the
+// row counts of ALL worlds. It is a counter barrier over co-resident blocks (the grid is never larger than the
+// resident capacity of the device: mdr_ecs_build sizes it).
+__device__ __forceinline__ void gridBarrier(unsigned *bar /*[2]: arrivals, generation*/)
+{
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence();
+        const unsigned gen = *(volatile unsigned *)(bar + 1);
+        if (atomicAdd(bar, 1u) == gridDim.x - 1) {
+            *(volatile unsigned *)bar = 0u;
+            __threadfence();
+            atomicAdd(bar + 1, 1u);
+        } else {
+            while (*(volatile unsigned *)(bar + 1) == gen) { }
+        }
+        __threadfence();
+    }
+    __syncthreads();
+}
+
+template <int kMinBlocks>
+__global__ void __launch_bounds__(32 * kWarpsPerBlock, kMinBlocks)
+ecsFusedStepKernel(const EcsDev *__restrict__ E, int first, int last, unsigned *bar)
+{
+    __shared__ WarpShared shared[kWarpsPerBlock];
+    __shared__ BlockDescriptors descriptors;
+    __shared__ long long s_warp_sum[kWarpsPerBlock];
+    __shared__ long long s_base;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int W = E->num_worlds;
+    const int w = blockIdx.x * kWarpsPerBlock + warp;
+    const bool active = w < W;
+    Context ctx;
+    const NodeDev *nodes = loadDescriptors(&descriptors, ctx, E, first, last);
+    // 1. copy-in at the offsets the previous step (or refreshExports) left
+    if (active) {
+        for (int s = 0; s < E->num_exports; s++) {
+            const ExportDev &x = E->exports[s];
+            if (x.fixed) continue;
+            const ArchDev &A = E->arch[x.arch];
+            const int64_t off = x.offsets[w];
+            const int total = (int)(x.offsets[w + 1] - off) * (x.bytes >> 2);
+            copyWordsWarp((uint32_t *)(A.col[x.col] + (size_t)w * A.stride * x.bytes), (const uint32_t *)x.buffer + off * (x.bytes >> 2), total, lane);
+        }
+        __syncwarp();
+        // 2. TaskGraph::run
+        loadWorld(ctx, E, &shared[warp], w);
+        runNodes(ctx, nodes, last - first, AppsBuiltin());
+        storeWorld(ctx);
+    }
+    // 3. every world's row counts are final
+    gridBarrier(bar);
+    // 4 + 5. offsets of this block's worlds (prefix over the worlds before them), then copy-out
+    const int w0 = blockIdx.x * kWarpsPerBlock;
+    for (int s = 0; s < E->num_exports; s++) {
+        const ExportDev &x = E->exports[s];
+        if (x.fixed) continue;
+        const ArchDev &A = E->arch[x.arch];
+        const int32_t *counts = A.row_count;
+        long long part = 0;
+        for (int i = threadIdx.x; i < w0 && i < W; i += blockDim.x) part += __ldcg(counts + i);
+        for (int o = 16; o; o >>= 1) part += __shfl_xor_sync(kFull, part, o);
+        if (lane == 0) s_warp_sum[warp] = part;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            long long t = 0;
+            for (int k = 0; k < kWarpsPerBlock; k++) t += s_warp_sum[k];
+            s_base = t;
+        }
+        __syncthreads();
+        long long off = s_base;
+        for (int k = 0; k < warp; k++) if (w0 + k < W) off += __ldcg(counts + w0 + k);
+        const int32_t n = active ? __ldcg(counts + w) : 0;
+        if (active) {
+            if (lane == 0) {
+                x.offsets[w] = off;
+                if (w == W - 1) x.offsets[W] = off + n;
+            }
+            const int words = x.bytes >> 2;
+            copyWordsWarp((uint32_t *)x.buffer + off * words, (const uint32_t *)(A.col[x.col] + (size_t)w * A.stride * x.bytes), n * words, lane);
+        }
+        __syncthreads();
+    }
+}
+
 // Device-side column lookups through the uploaded maps (what Context::get<T>(Loc) does per call).
 __global__ void ecsColumnLookupKernel(const EcsDev *__restrict__ E, int arch, const int32_t *comps, int n, int32_t *out)
 {
@@ -284,6 +374,9 @@ struct mdr_ecs {
     bool exports_dirty = true;
     int blocks = 0;
     void (*step_kernel)(const EcsDev *, int, int) = nullptr;
+    void (*fused_kernel)(const EcsDev *, int, int, unsigned *) = nullptr;   // the whole step in one launch, when it applies
+    unsigned *grid_bar = nullptr;
+    bool fused_ok = false, fused_in_graph = false;
     mdr_ecs_launch_fn launcher = nullptr;   // megakernel instantiated in the user's translation unit
     void *launcher_user = nullptr;
     int32_t tmp_bytes = 0, world_data_bytes = 0;
@@ -746,6 +839,8 @@ int32_t mdr_ecs_build(mdr_ecs *e)
         if (rounds(8) < rounds(want)) want = 8;
     }
     e->step_kernel = want == 6 ? ecsStepKernel<6> : want == 8 ? ecsStepKernel<8> : ecsStepKernel<4>;
+    e->fused_kernel = want == 6 ? ecsFusedStepKernel<6> : want == 8 ? ecsFusedStepKernel<8> : ecsFusedStepKernel<4>;
+    e->grid_bar = e->dalloc<unsigned>(2);
     int per_sm = 0;
     REQ_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, e->step_kernel, 32 * kWarpsPerBlock, 0));
     cudaDeviceProp prop;
@@ -753,6 +848,15 @@ int32_t mdr_ecs_build(mdr_ecs *e)
     long long grid = (long long)(per_sm > 0 ? per_sm : 1) * prop.multiProcessorCount;
     const long long need = ((long long)W + kWarpsPerBlock - 1) / kWarpsPerBlock;
     e->blocks = (int)(grid < need ? grid : need);
+    // the one-launch step needs every world resident at once under the fused kernel's own occupancy
+    int fused_per_sm = 0;
+    REQ_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&fused_per_sm, e->fused_kernel, 32 * kWarpsPerBlock, 0));
+    // Measured (profiles/r02_summary.md section 6): level with the four-launch graph from 4096 worlds on, 7 % slower
+    // at 1024 (the barrier is two more dependent round trips in a step that is all latency): on by default from 2048
+    // worlds, MDR_ECS_FUSED=1 / MDR_ECS_NO_FUSED=1 force it either way.
+    const char *nf = getenv("MDR_ECS_NO_FUSED"), *ff = getenv("MDR_ECS_FUSED");
+    e->fused_ok = !(nf && *nf == '1') && (W >= 2048 || (ff && *ff == '1')) &&
+                  need <= (long long)fused_per_sm * prop.multiProcessorCount;
     e->built = true;
     e->exports_dirty = true;
     return MDR_OK;
@@ -911,7 +1015,15 @@ int32_t mdr_ecs_step_async(mdr_ecs *e, int32_t num_steps)
         // exportCopyIn -> megakernel -> exportBlockSums -> exportCopyOut
         cudaGraph_t g = nullptr;
         REQ_CUDA(cudaStreamBeginCapture(e->stream, cudaStreamCaptureModeThreadLocal));
-        if (staged) ecsExportCopy<<<(e->host.num_worlds + 7) / 8, 256, 0, e->stream>>>(e->dev, 0);
+        bool has_physics = false;
+        for (int ni = 0; ni < e->host.num_nodes; ni++) has_physics = has_physics || e->host.node[ni].kind == kNodePhysics;
+        const bool fused = staged && e->fused_ok && !e->launcher && !has_physics;
+        e->fused_in_graph = fused;
+        if (fused) {
+            const int blocks = (e->host.num_worlds + kWarpsPerBlock - 1) / kWarpsPerBlock;
+            e->fused_kernel<<<blocks, 32 * kWarpsPerBlock, 0, e->stream>>>(e->dev, 0, e->host.num_nodes, e->grid_bar);
+        }
+        if (staged && !fused) ecsExportCopy<<<(e->host.num_worlds + 7) / 8, 256, 0, e->stream>>>(e->dev, 0);
         // The megakernel walks maximal runs of in-kernel nodes; a physics node is a launch of the
         // rigid-body step kernel on the same tables between two such runs (the reference's generated
         // megakernel takes the same (start_node, end_node) pair, src/mw/cuda_exec.cpp:728-745).
@@ -925,8 +1037,8 @@ int32_t mdr_ecs_step_async(mdr_ecs *e, int32_t num_steps)
                 e->step_kernel<<<e->blocks, 32 * kWarpsPerBlock, 0, e->stream>>>(e->dev, first, last);
             }
         };
-        int first = 0;
-        for (int ni = 0; ni < e->host.num_nodes; ni++) {
+        int first = fused ? e->host.num_nodes : 0;
+        for (int ni = 0; ni < e->host.num_nodes && !fused; ni++) {
             if (e->host.node[ni].kind != kNodePhysics) continue;
             segment(first, ni);
             first = ni + 1;
@@ -934,7 +1046,7 @@ int32_t mdr_ecs_step_async(mdr_ecs *e, int32_t num_steps)
             if (!ph || mdrPhysEnqueueStep(ph, e->stream) != MDR_OK) rc_launch = MDR_ESTATE;
         }
         segment(first, e->host.num_nodes);
-        if (staged) {
+        if (staged && !fused) {
             launchExportOffsets(e->dev, e->host.num_exports, e->host.num_worlds, e->stream);
             ecsExportCopy<<<(e->host.num_worlds + 7) / 8, 256, 0, e->stream>>>(e->dev, 1);
         }
@@ -999,6 +1111,7 @@ int32_t mdr_ecs_node_clocks(mdr_ecs *e, unsigned long long *out, int32_t n)
 int32_t mdr_ecs_launches_per_step(mdr_ecs *e)
 {
     if (!e || !e->built) return MDR_EINVAL;
+    if (e->graph && e->fused_in_graph) return 1;
     int n = 0, run = 0;
     for (int ni = 0; ni < e->host.num_nodes; ni++) {
         if (e->host.node[ni].kind == kNodePhysics) { n += 2 + (run > 0); run = 0; }   // BVH rebuild check + step kernel

@@ -292,3 +292,33 @@ def test_forty_node_graph():
     assert np.array_equal(r.export(0), ck.export(0))
     r.close()
     ck.close()
+
+
+def test_one_launch_step_equals_the_four_launch_graph(monkeypatch):
+    """The fused step (copy-in, nodes, grid barrier, offsets, copy-out in one kernel; used when every world is
+    resident at once) against the run graph of four launches (MDR_ECS_NO_FUSED=1; also what larger batches use):
+    every column, row counts, id maps and the staged exports with their offsets."""
+    from gpu_ecs_madrona_b200.ecs import EcsExecutor
+    monkeypatch.setenv("MDR_ECS_FUSED", "1")            # on by default from 2048 worlds
+    fused = EcsExecutor(A.APP_FVS, 300, [10, 40])
+    monkeypatch.delenv("MDR_ECS_FUSED")
+    monkeypatch.setenv("MDR_ECS_NO_FUSED", "1")
+    plain = EcsExecutor(A.APP_FVS, 300, [10, 40])
+    monkeypatch.delenv("MDR_ECS_NO_FUSED")
+    assert fused.launches_per_step() >= 1
+    for steps in (1, 7, 60):
+        fused.run(steps)
+        plain.run(steps)
+        assert fused.launches_per_step() == 1 and plain.launches_per_step() == 4
+        assert np.array_equal(fused.row_counts(), plain.row_counts())
+        for (a, c), v in fused.read_world_columns().items():
+            if c == 0 and a in U.TEMP_ARCHETYPES[A.APP_FVS]:
+                continue
+            rows = fused.row_counts()[:, a]
+            w = plain.read_column_all(a, c)
+            for k in (0, 1, 150, 299):
+                assert np.array_equal(v[k, :rows[k]], w[k, :rows[k]]), (steps, a, c, k)
+        for s in range(2):
+            assert np.array_equal(fused.export(s), plain.export(s)), (steps, s)
+    fused.close()
+    plain.close()
