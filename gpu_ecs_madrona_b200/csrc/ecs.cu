@@ -386,11 +386,17 @@ struct mdr_ecs {
     int timed_steps = 0, pending_steps = 0;
     bool timing_open = false;
 
+    bool alloc_failed = false;      // a table did not fit the device: mdr_ecs_build frees everything, MDR_ECAPACITY
     template <typename T> T *dalloc(size_t n, bool zero = true)
     {
         void *p = nullptr;
         const size_t bytes = (n ? n : 1) * sizeof(T);
-        REQ_CUDA(cudaMalloc(&p, bytes));
+        if (alloc_failed) return nullptr;
+        if (cudaMalloc(&p, bytes) != cudaSuccess) {
+            cudaGetLastError();     // out of memory is not sticky
+            alloc_failed = true;
+            return nullptr;
+        }
         if (zero) REQ_CUDA(cudaMemset(p, 0, bytes));
         allocs.push_back(p);
         return (T *)p;
@@ -680,11 +686,32 @@ int32_t mdr_ecs_add_sort(mdr_ecs *e, int32_t arch, int32_t key_comp, int32_t rem
     return addNode(e, HostNode { kNodeSort, 0, arch, key_comp, remap_entities, {}, {} }, deps, ndeps);
 }
 
+static int32_t buildImpl(mdr_ecs *e);
+
+// A build that fails (capacity of the descriptor, or tables that do not fit the device) leaves nothing behind:
+// every allocation is released and the registry can be built again (with fewer worlds, say).
 int32_t mdr_ecs_build(mdr_ecs *e)
 {
     if (!e) return MDR_EINVAL;
     if (e->built) return MDR_ESTATE;
     if (e->archs.empty()) return MDR_EINVAL;
+    int32_t rc = buildImpl(e);
+    if (rc == MDR_OK && e->alloc_failed) rc = MDR_ECAPACITY;
+    if (rc != MDR_OK) {
+        if (e->alloc_failed)
+            fprintf(stderr, "madrona_b200: %d worlds of this registry do not fit the device memory\n", e->cfg.num_worlds);
+        for (void *a : e->allocs) cudaFree(a);
+        e->allocs.clear();
+        e->alloc_failed = false;
+        e->built = false;
+        e->dev = nullptr;
+        memset(&e->host, 0, sizeof(e->host));
+    }
+    return rc;
+}
+
+static int32_t buildImpl(mdr_ecs *e)
+{
     REQ_CUDA(cudaSetDevice(e->cfg.gpu_id));
     EcsDev &H = e->host;
     memset(&H, 0, sizeof(H));
@@ -699,6 +726,7 @@ int32_t mdr_ecs_build(mdr_ecs *e)
     for (int a = 0; a < H.num_arch; a++)
         if (!buildArchColumnMap(e->col_maps[a], e->archs[a])) return MDR_ECAPACITY;   // the reference FATALs
     H.col_maps = e->dalloc<ColumnMapDev>((size_t)H.num_arch, false);
+    if (e->alloc_failed) return MDR_ECAPACITY;
     REQ_CUDA(cudaMemcpy(H.col_maps, e->col_maps.data(), sizeof(ColumnMapDev) * (size_t)H.num_arch, cudaMemcpyHostToDevice));
     for (int a = 0; a < H.num_arch; a++) {
         const HostArchetype &ha = e->archs[a];
@@ -733,6 +761,8 @@ int32_t mdr_ecs_build(mdr_ecs *e)
         H.num_handles = e->dalloc<int32_t>(W);
     }
 
+    if (e->alloc_failed) return MDR_ECAPACITY;
+
     // Initial id state of every world. registerSingleton (include/madrona/state.inl:
     // 171-187) makes one entity per singleton through the StateManager's own init cache.
     std::vector<IdNode> nodes0(H.id_cap, IdNode { 0, 0, 0u });
@@ -756,6 +786,7 @@ int32_t mdr_ecs_build(mdr_ecs *e)
     }
     if (st0.num_ids > 0) {
         IdNode *d0 = e->dalloc<IdNode>(st0.num_ids, false);
+        if (e->alloc_failed) return MDR_ECAPACITY;
         REQ_CUDA(cudaMemcpy(d0, nodes0.data(), sizeof(IdNode) * (size_t)st0.num_ids, cudaMemcpyHostToDevice));
         const int64_t total = (int64_t)W * st0.num_ids;
         ecsBroadcastNodes<<<(unsigned)((total + 255) / 256), 256>>>(H.id_nodes, H.id_cap, d0, st0.num_ids, W);
@@ -818,6 +849,7 @@ int32_t mdr_ecs_build(mdr_ecs *e)
         }
     }
     e->dev = e->dalloc<EcsDev>(1, false);
+    if (e->alloc_failed) return MDR_ECAPACITY;
     REQ_CUDA(cudaMemcpy(e->dev, &H, sizeof(H), cudaMemcpyHostToDevice));
 
     // Register budget of the megakernel: more resident warps hide the latency of the
@@ -841,6 +873,7 @@ int32_t mdr_ecs_build(mdr_ecs *e)
     e->step_kernel = want == 6 ? ecsStepKernel<6> : want == 8 ? ecsStepKernel<8> : ecsStepKernel<4>;
     e->fused_kernel = want == 6 ? ecsFusedStepKernel<6> : want == 8 ? ecsFusedStepKernel<8> : ecsFusedStepKernel<4>;
     e->grid_bar = e->dalloc<unsigned>(2);
+    if (e->alloc_failed) return MDR_ECAPACITY;
     int per_sm = 0;
     REQ_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, e->step_kernel, 32 * kWarpsPerBlock, 0));
     cudaDeviceProp prop;

@@ -347,15 +347,23 @@ int32_t mdr_sort_create(int32_t gpu_id, int32_t max_rows, int32_t num_columns, c
     REQ_CUDA(cudaGetDeviceProperties(&prop, gpu_id));
     s->sms = prop.multiProcessorCount;
     const size_t tiles = ((size_t)max_rows + kTile - 1) / kTile;
-    REQ_CUDA(cudaMalloc((void **)&s->keys_a, 4 * (size_t)max_rows));
-    REQ_CUDA(cudaMalloc((void **)&s->keys_b, 4 * (size_t)max_rows));
-    REQ_CUDA(cudaMalloc((void **)&s->vals_a, 4 * (size_t)max_rows));
-    REQ_CUDA(cudaMalloc((void **)&s->vals_b, 4 * (size_t)max_rows));
     // bins | tile counters | look-back words in one block: one memset per run
-    REQ_CUDA(cudaMalloc((void **)&s->bins, 4 * ((size_t)kMaxPasses * kDigits + kDigits + tiles * kDigits * kMaxPasses)));
+    bool ok = true;
+    auto take = [&](void **ptr, size_t bytes) {
+        if (ok && cudaMalloc(ptr, bytes) != cudaSuccess) { cudaGetLastError(); ok = false; }
+    };
+    take((void **)&s->keys_a, 4 * (size_t)max_rows);
+    take((void **)&s->keys_b, 4 * (size_t)max_rows);
+    take((void **)&s->vals_a, 4 * (size_t)max_rows);
+    take((void **)&s->vals_b, 4 * (size_t)max_rows);
+    take((void **)&s->bins, 4 * ((size_t)kMaxPasses * kDigits + kDigits + tiles * kDigits * kMaxPasses));
+    take((void **)&s->d_cols, sizeof(ColumnDesc) * (size_t)num_columns);
+    if (!ok) {      // the scratch of a table this size does not fit the device
+        mdr_sort_destroy(s);
+        return MDR_ECAPACITY;
+    }
     s->counters = s->bins + kMaxPasses * kDigits;
     s->lookback = s->counters + kDigits;
-    REQ_CUDA(cudaMalloc((void **)&s->d_cols, sizeof(ColumnDesc) * (size_t)num_columns));
     s->staging_bytes = max_col * (size_t)max_rows;
     REQ_CUDA(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
     REQ_CUDA(cudaEventCreate(&s->ev0));
@@ -426,7 +434,11 @@ int32_t mdr_sort_run(mdr_sort *s, const void *const *columns_in, void *const *co
         const int num_direct = (int)descs.size();
         for (const ColumnDesc &d : descs)
             if ((int64_t)d.words * num_rows >= (int64_t)1 << 32) return MDR_ECAPACITY;   // word index is 32-bit
-        if (!inplace.empty() && !s->staging) REQ_CUDA(cudaMalloc((void **)&s->staging, s->staging_bytes));
+        if (!inplace.empty() && !s->staging && cudaMalloc((void **)&s->staging, s->staging_bytes) != cudaSuccess) {
+            cudaGetLastError();
+            s->staging = nullptr;
+            return MDR_ECAPACITY;       // no room for the staging copy of an in-place column
+        }
         for (int c : inplace)
             { ColumnDesc d; memset(&d, 0, sizeof(d)); d.src = (const char *)columns_in[c]; d.dst = s->staging; d.words = s->col_bytes[c] / 4; descs.push_back(d); }
         if (descs.size() != s->h_cols.size() || memcmp(descs.data(), s->h_cols.data(), sizeof(ColumnDesc) * descs.size())) {

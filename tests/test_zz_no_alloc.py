@@ -80,3 +80,27 @@ def test_static_sort_rejects_what_it_cannot_hold(cuda_lib):
     assert lib.mdr_sort_pairs_static(0, a.data_ptr(), a.data_ptr(), c.data_ptr(), 16, 32, None) == -1    # in place
     assert lib.mdr_sort_pairs_static(0, a.data_ptr(), b.data_ptr(), c.data_ptr(), 16, 33, None) == -1
     assert lib.mdr_sort_pairs_static(0, a.data_ptr(), b.data_ptr(), c.data_ptr(), 0, 32, None) == 0
+
+
+def test_tables_that_do_not_fit_are_an_error_code_not_an_abort(cuda_lib):
+    """cudaMalloc failures used to abort() the host process. A batch that cannot fit the device answers
+    MDR_ECAPACITY from mdr_phys_create / mdr_ecs_build (mdr_sort_create likewise), frees what it took, and the process goes on."""
+    from gpu_ecs_madrona_b200 import phys, scenes
+    from gpu_ecs_madrona_b200.ecs import EcsRegistry
+    sc = scenes.collisions64(4)
+    sc.num_worlds = 400_000_000                    # the first column alone is 217 GB: fails at once
+    with pytest.raises(phys.MadronaError) as ei:
+        phys.PhysExecutor(sc)
+    assert ei.value.code == phys.MDR_ECAPACITY
+    r = EcsRegistry(1 << 20)
+    c = r.register_component(1024)
+    r.register_archetype([c], 1 << 15)             # 2^20 worlds x 32768 rows: the Entity column alone is 275 GB
+    with pytest.raises(phys.MadronaError) as ei:
+        r.build()
+    assert ei.value.code == phys.MDR_ECAPACITY
+    r.close()
+    # and the device is still usable
+    ex = phys.PhysExecutor(scenes.collisions64(8))
+    ex.run(2)
+    assert np.isfinite(ex.state()[0]).all()
+    ex.close()
