@@ -3,7 +3,7 @@
 
 static const mdr::KernelVariant kPart[] = {
     MDR_STEP_VARIANT(128, 6),      // 80 registers,
-    MDR_STEP_VARIANT(256, 2),      // 128 registers
+    MDR_STEP_VARIANT_C64(256, 2),  // 128 registers; + the collisions-64 shape with a compile-time layout
 };
 
 const mdr::KernelVariant *mdrStepVariants1(int *n)

@@ -10,15 +10,30 @@ namespace mdr {
 
 extern __shared__ __align__(16) char mdr_smem[];
 
+// Layout: the shared-memory layout of a world slot (row stride, pair capacity, contact slots) and the threads per world
+// either come with the launch (RuntimeLayout) or are compile-time constants (FixedLayout). With constants every array of
+// the world view is "slot base + immediate" and the loops stride by an immediate: the view costs one register instead of
+// twenty-odd, the 128-register kernel stops spilling, and the step is 8-10 % faster (profiles/r02_summary.md section 7).
+// A fixed variant is compiled per registered shape (the table below holds collisions-64's); physics.cu selects it when
+// the configuration matches and falls back to the runtime layout otherwise.
+struct RuntimeLayout { static constexpr int kNp = 0, kPairs = 0, kContacts = 0, kTpw = 0; };
+template <int N, int P, int C, int T> struct FixedLayout { static constexpr int kNp = N, kPairs = P, kContacts = C, kTpw = T; };
+using Collisions64Layout = FixedLayout<68, 640, 72, 64>;     // 65 bodies, 640 candidate pairs, 72 SMEM contacts, 64 threads
+
 // kHullSlots: 1 = hulls of up to 32 vertices / faces, 2 = up to 64 (phys_sat_warp.cuh); the big-hull variant carries
 // the joint solve as well (one extra instantiation per register budget instead of two).
-template <int kMaxThreads, int kMinBlocks, bool kJoints, int kHullSlots = 1>
+template <int kMaxThreads, int kMinBlocks, bool kJoints, int kHullSlots = 1, typename Layout = RuntimeLayout>
 __global__ void __launch_bounds__(kMaxThreads, kMinBlocks)
 physStepKernel(const __grid_constant__ StepParams p, int threads_per_world, int slot_bytes,
                int overflow_per_slot, int lockstep, int first_world, int end_world)
 {
     __shared__ int group_level;
     __shared__ BlockSolve block_solve;
+    constexpr bool kFixed = Layout::kNp > 0;
+    if (kFixed) {                 // the host launches this variant only with these values
+        threads_per_world = Layout::kTpw;
+        lockstep = 1;
+    }
     const int slots = blockDim.x / threads_per_world;
     const int slot = threadIdx.x / threads_per_world;
     BlockCtx ctx;
@@ -26,10 +41,16 @@ physStepKernel(const __grid_constant__ StepParams p, int threads_per_world, int 
     ctx.nth_ = threads_per_world;
     ctx.bar_ = lockstep ? 0 : slot + 1;
     WorldView v;
-    carveWorld(v, mdr_smem + (size_t)slot * slot_bytes, p.t.stride, p.max_pairs, p.smem_contacts);
+    if (kFixed) {
+        carveWorld(v, mdr_smem + (size_t)slot * carveWorld(v, nullptr, Layout::kNp, Layout::kPairs, Layout::kContacts),
+                   Layout::kNp, Layout::kPairs, Layout::kContacts);
+    } else {
+        carveWorld(v, mdr_smem + (size_t)slot * slot_bytes, p.t.stride, p.max_pairs, p.smem_contacts);
+    }
     v.overflow = p.overflow + ((size_t)blockIdx.x * slots + slot) * overflow_per_slot;
     // dense solver lanes need block-wide barriers, pair slots in 10 bits and a view per slot
-    BlockSolve *bs = lockstep && slots <= kDenseSlots && p.max_pairs <= 1024 ? &block_solve : nullptr;
+    BlockSolve *bs = kFixed ? &block_solve
+                            : (lockstep && slots <= kDenseSlots && p.max_pairs <= 1024 ? &block_solve : nullptr);
     v.level_any = bs ? block_solve.level_any : nullptr;
     if (bs && ctx.tid_ == 0) { v.n = 0; v.active = false; bs->views[slot] = v; }
     __syncthreads();
@@ -46,9 +67,20 @@ physStepKernel(const __grid_constant__ StepParams p, int threads_per_world, int 
 typedef void (*StepKernel)(const StepParams, int, int, int, int, int, int);
 // {max block threads, min resident blocks}; fn_joints is the same kernel with the joint
 // solve compiled in (mdr_phys_set_joints), so that batches without joints do not carry it.
-struct KernelVariant { int threads, min_blocks; StepKernel fn, fn_joints, fn_big; };
+struct KernelVariant {
+    int threads, min_blocks;
+    StepKernel fn, fn_joints, fn_big;
+    StepKernel fn_fixed;                                   // plain kernel with a compile-time layout, or null
+    int fixed_np, fixed_pairs, fixed_contacts, fixed_tpw;  // the shape fn_fixed was compiled for
+};
 #define MDR_STEP_VARIANT(T, B) { T, B, mdr::physStepKernel<T, B, false>, mdr::physStepKernel<T, B, true>, \
-                                 mdr::physStepKernel<T, B, true, 2> }
+                                 mdr::physStepKernel<T, B, true, 2>, nullptr, 0, 0, 0, 0 }
+// the same plus the collisions-64 shape as a fixed-layout instantiation
+#define MDR_STEP_VARIANT_C64(T, B) { T, B, mdr::physStepKernel<T, B, false>, mdr::physStepKernel<T, B, true>, \
+                                     mdr::physStepKernel<T, B, true, 2>, \
+                                     mdr::physStepKernel<T, B, false, 1, mdr::Collisions64Layout>, \
+                                     mdr::Collisions64Layout::kNp, mdr::Collisions64Layout::kPairs, \
+                                     mdr::Collisions64Layout::kContacts, mdr::Collisions64Layout::kTpw }
 
 }  // namespace mdr
 

@@ -99,6 +99,7 @@ struct mdr_phys {
     bool external_tables = false;            // columns and row counts belong to an ECS archetype
     StepKernel kernel = nullptr;             // the variant in use: kernel_plain, or kernel_joints once joints are set
     StepKernel kernel_plain = nullptr, kernel_joints = nullptr;
+    bool fixed_layout = false;               // the plain kernel is a compile-time-layout instantiation
     bool big_hulls = false;                  // an object has more than 32 vertices / faces: the two-slot SAT variant
     int threads = 0, blocks = 0, blocks_per_sm = 0, overflow_per_slot = 0;
     int threads_per_world = 0, worlds_per_block = 0, lockstep = 1;
@@ -306,6 +307,13 @@ static int32_t createImpl(const mdr_phys_config *cfg, const mdr_object *objs, in
     p->big_hulls = p->assets.max_verts > 32 || p->assets.max_faces > 32;
     p->kernel = p->kernel_plain = p->big_hulls ? var->fn_big : var->fn;
     p->kernel_joints = p->big_hulls ? var->fn_big : var->fn_joints;
+    // a variant compiled for exactly this shape (phys_kernel.cuh, FixedLayout); MDR_NO_FIXED_LAYOUT=1 keeps the runtime one
+    if (!p->big_hulls && var->fn_fixed && !envInt("MDR_NO_FIXED_LAYOUT", 0) && p->lockstep && wpb <= kDenseSlots &&
+        stride == var->fixed_np && sp.max_pairs == var->fixed_pairs && sp.smem_contacts == var->fixed_contacts &&
+        tpw == var->fixed_tpw) {
+        p->kernel = p->kernel_plain = var->fn_fixed;
+        p->fixed_layout = true;
+    }
     for (StepKernel k : { p->kernel_plain, p->kernel_joints }) {
         REQ_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p->smem_bytes));
         REQ_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributePreferredSharedMemoryCarveout, 100));

@@ -5,8 +5,14 @@
 #include "exp_list.h"      // written by build_exp.sh from $VARIANTS: #define MDR_EXP_LIST MDR_STEP_VARIANT(T, B), ...
 #undef MDR_STEP_VARIANT
 // joints variant aliased to the plain one: halves the build
+#ifdef MDR_EXP_FIXED
 #define MDR_STEP_VARIANT(T, B) { T, B, mdr::physStepKernel<T, B, false>, mdr::physStepKernel<T, B, false>, \
-                                 mdr::physStepKernel<T, B, false> }
+                                 mdr::physStepKernel<T, B, false>, mdr::physStepKernel<T, B, false, 1, mdr::Collisions64Layout>, \
+                                 68, 640, 72, 64 }
+#else
+#define MDR_STEP_VARIANT(T, B) { T, B, mdr::physStepKernel<T, B, false>, mdr::physStepKernel<T, B, false>, \
+                                 mdr::physStepKernel<T, B, false>, nullptr, 0, 0, 0, 0 }
+#endif
 static const mdr::KernelVariant kPart[] = { MDR_EXP_LIST };
 const mdr::KernelVariant *mdrStepVariants0(int *n) { *n = (int)(sizeof(kPart) / sizeof(kPart[0])); return kPart; }
 const mdr::KernelVariant *mdrStepVariants1(int *n) { *n = 0; return kPart; }
