@@ -8,17 +8,6 @@
 
 namespace mdr {
 
-extern __shared__ __align__(16) char mdr_smem[];
-
-// Layout: the shared-memory layout of a world slot (row stride, pair capacity, contact slots) and the threads per world
-// either come with the launch (RuntimeLayout) or are compile-time constants (FixedLayout). With constants every array of
-// the world view is "slot base + immediate" and the loops stride by an immediate: the view costs one register instead of
-// twenty-odd, the 128-register kernel stops spilling, and the step is 8-10 % faster (profiles/r02_summary.md section 7).
-// A fixed variant is compiled per registered shape (the table below holds collisions-64's); physics.cu selects it when
-// the configuration matches and falls back to the runtime layout otherwise.
-struct RuntimeLayout { static constexpr int kNp = 0, kPairs = 0, kContacts = 0, kTpw = 0; };
-template <int N, int P, int C, int T> struct FixedLayout { static constexpr int kNp = N, kPairs = P, kContacts = C, kTpw = T; };
-using Collisions64Layout = FixedLayout<68, 640, 72, 64>;     // 65 bodies, 640 candidate pairs, 72 SMEM contacts, 64 threads
 
 // kHullSlots: 1 = hulls of up to 32 vertices / faces, 2 = up to 64 (phys_sat_warp.cuh); the big-hull variant carries
 // the joint solve as well (one extra instantiation per register budget instead of two).
@@ -59,7 +48,7 @@ physStepKernel(const __grid_constant__ StepParams p, int threads_per_world, int 
     for (int base = first_world + blockIdx.x * slots; base < end_world; base += gridDim.x * slots) {
         const int w = base + slot;
         v.active = w < end_world;
-        stepWorld<kJoints, kHullSlots>(ctx, v, p, v.active ? w : first_world, &group_level, bs, slot);
+        stepWorld<kJoints, kHullSlots, Layout>(ctx, v, p, v.active ? w : first_world, &group_level, bs, slot);
     }
 }
 

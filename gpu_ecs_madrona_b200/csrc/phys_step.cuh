@@ -28,6 +28,20 @@ struct BlockSolve {
     WorldView views[kDenseSlots];
 };
 
+#if defined(__CUDACC__)
+extern __shared__ __align__(16) char mdr_smem[];
+#endif
+
+// Layout: the shared-memory layout of a world slot (row stride, pair capacity, contact slots) and the threads per world
+// either come with the launch (RuntimeLayout) or are compile-time constants (FixedLayout). With constants every array of
+// the world view is "slot base + immediate" and the loops stride by an immediate: the view costs one register instead of
+// twenty-odd, the 128-register kernel stops spilling, and the step is 8-10 % faster (profiles/r02_summary.md section 7).
+// A fixed variant is compiled per registered shape (the table below holds collisions-64's); physics.cu selects it when
+// the configuration matches and falls back to the runtime layout otherwise.
+struct RuntimeLayout { static constexpr int kNp = 0, kPairs = 0, kContacts = 0, kTpw = 0; };
+template <int N, int P, int C, int T> struct FixedLayout { static constexpr int kNp = N, kPairs = P, kContacts = C, kTpw = T; };
+using Collisions64Layout = FixedLayout<68, 640, 72, 64>;     // 65 bodies, 640 candidate pairs, 72 SMEM contacts, 64 threads
+
 #if defined(__CUDA_ARCH__)
 // All threads of the block, once per step, after every world slot has its pair list and levels (block
 // barrier passed): the PAIRS of all slots bucketed by level. Which of them carry a contact changes from
@@ -73,7 +87,9 @@ __device__ __forceinline__ bool buildLevelLists(const BlockCtx &c, const WorldVi
 }
 
 // `any`: the levels that hold a contact in this substep (bit lv), read by every thread after a block barrier.
-template <bool kVelocity>
+// With a compile-time layout the view of the contact's world slot is arithmetic on the slot index; with the runtime
+// layout it is read from the block's table of views in shared memory (a dependent load at the head of every contact).
+template <bool kVelocity, typename Layout>
 __device__ __forceinline__ void solveDense(BlockSolve *bs, const StepParams &p, int max_level, uint32_t any)
 {
     for (int lv = 1; lv <= max_level; lv++) {
@@ -81,11 +97,22 @@ __device__ __forceinline__ void solveDense(BlockSolve *bs, const StepParams &p, 
         const int begin = bs->off[lv], end = bs->off[lv + 1];
         for (int k = begin + (int)threadIdx.x; k < end; k += (int)blockDim.x) {
             const uint32_t code = bs->items[k];
-            WorldView &vv = bs->views[code >> 10];
-            SolverContact *ct = contactSlot(vv, (int)(code & 1023u));
-            if (ct->hdr == 0) continue;
-            if (kVelocity) solveContactVelocities(vv, p, ct);
-            else solveContactPositions(vv, p, ct);
+            const int slot = (int)(code >> 10), pi = (int)(code & 1023u);
+            if constexpr (Layout::kNp > 0) {
+                WorldView vv;
+                const size_t slot_bytes = carveWorld(vv, nullptr, Layout::kNp, Layout::kPairs, Layout::kContacts);
+                carveWorld(vv, mdr_smem + (size_t)slot * slot_bytes, Layout::kNp, Layout::kPairs, Layout::kContacts);
+                SolverContact *ct = pi < Layout::kContacts ? vv.contacts + pi : bs->views[slot].overflow + (pi - Layout::kContacts);
+                if (ct->hdr == 0) continue;
+                if (kVelocity) solveContactVelocities(vv, p, ct);
+                else solveContactPositions(vv, p, ct);
+            } else {
+                WorldView &vv = bs->views[slot];
+                SolverContact *ct = contactSlot(vv, pi);
+                if (ct->hdr == 0) continue;
+                if (kVelocity) solveContactVelocities(vv, p, ct);
+                else solveContactPositions(vv, p, ct);
+            }
         }
         __syncthreads();
     }
@@ -96,7 +123,7 @@ __device__ __forceinline__ void solveDense(BlockSolve *bs, const StepParams &p, 
 // whole block: the level loops must run the same number of barriers in every
 // world slot, so they run to the block-wide maximum. A slot without a world
 // this round (`!v.active`) walks the same barriers with zero rows.
-template <bool kJoints = true, int kHullSlots = 1>
+template <bool kJoints = true, int kHullSlots = 1, typename Layout = RuntimeLayout>
 MDR_HD void stepWorld(const BlockCtx &c, WorldView &v, const StepParams &p, int w, int *group_level,
                       BlockSolve *bs = nullptr, int slot = 0)
 {
@@ -148,13 +175,13 @@ MDR_HD void stepWorld(const BlockCtx &c, WorldView &v, const StepParams &p, int 
 #if defined(__CUDA_ARCH__)
         if (dense) {
             const uint32_t any = bs->level_any[sub & 1];      // final: a block barrier has passed since the last emit
-            solveDense<false>(bs, p, max_level, any);
+            solveDense<false, Layout>(bs, p, max_level, any);
             MDR_PHASE(7);
             if (kJoints) solveJoints(c, v, p, w);
             setVelocities(c, v, p, sub);
             c.sync();
             MDR_PHASE(8);
-            solveDense<true>(bs, p, max_level, any);
+            solveDense<true, Layout>(bs, p, max_level, any);
             MDR_PHASE(9);
             continue;
         }
