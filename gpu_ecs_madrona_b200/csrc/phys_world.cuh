@@ -569,19 +569,28 @@ MDR_HD void findPairs(const BlockCtx &c, WorldView &v, const StepParams &p, int 
                 }
                 i = end;
             } else {
+                // a stretch of pairs whose first body orders contacts: the first lane walks it alone, without a
+                // warp barrier per pair, up to the next run the whole warp can take
+                int j = i;
                 if (lane == 0) {
-                    const int b = (pr >> 10) & 1023;
-                    const bool db = (v.meta[b] & META_DEP) != 0;
-                    const int la = v.last_level[a];
-                    const int lb = db ? v.last_level[b] : 0;
-                    int lv = (la > lb ? la : lb) + 1;
-                    if (lv > MDR_MAX_LEVEL) { lv = MDR_MAX_LEVEL; too_deep = true; }
-                    v.last_level[a] = (uint16_t)lv;
-                    if (db) v.last_level[b] = (uint16_t)lv;
-                    v.pairs[i] = pr | ((uint32_t)lv << 20);
-                    if (lv > max_level) max_level = lv;
+                    while (j < np) {
+                        const uint32_t q = v.pairs[j];
+                        const int qa = q & 1023;
+                        if (!(v.meta[qa] & META_DEP)) break;
+                        const int b = (q >> 10) & 1023;
+                        const bool db = (v.meta[b] & META_DEP) != 0;
+                        const int la = v.last_level[qa];
+                        const int lb = db ? v.last_level[b] : 0;
+                        int lv = (la > lb ? la : lb) + 1;
+                        if (lv > MDR_MAX_LEVEL) { lv = MDR_MAX_LEVEL; too_deep = true; }
+                        v.last_level[qa] = (uint16_t)lv;
+                        if (db) v.last_level[b] = (uint16_t)lv;
+                        v.pairs[j] = q | ((uint32_t)lv << 20);
+                        if (lv > max_level) max_level = lv;
+                        j++;
+                    }
                 }
-                i++;
+                i = __shfl_sync(0xffffffffu, j, 0);
             }
             __syncwarp();
         }
