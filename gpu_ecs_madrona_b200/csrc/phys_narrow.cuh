@@ -228,7 +228,8 @@ struct Manifold { V3 pts[4]; float depths[4]; int n; V3 normal; };
 // a zero component depends on the zeros inside rotate(): it is evaluated as is.
 MDR_HD void finishManifold(Manifold &m, V3 n)
 {
-    for (int i = 0; i < 4; i++) {
+#pragma unroll
+    for (int i = 0; i < 4; i++) {       // unrolled: the manifold stays in registers
         if (i < m.n) m.pts[i] = mk3(m.pts[i].x + 0.f, m.pts[i].y + 0.f, m.pts[i].z + 0.f);
     }
     m.normal = rotate(mk4(1.f, 0.f, 0.f, 0.f), n);
@@ -425,10 +426,9 @@ MDR_HD bool hullPlaneContact(Manifold &m, const BodyXf &x, const StepParams &p, 
     } else {
         V3 pts[MDR_MAX_POLY];
         float depths[MDR_MAX_POLY];
-        for (int i = 0; i < n; i++) {
-            pts[i] = i < 4 ? m.pts[i] : more[i - 4];
-            depths[i] = i < 4 ? m.depths[i] : more_d[i - 4];
-        }
+#pragma unroll
+        for (int i = 0; i < 4; i++) { pts[i] = m.pts[i]; depths[i] = m.depths[i]; }
+        for (int i = 4; i < n; i++) { pts[i] = more[i - 4]; depths[i] = more_d[i - 4]; }
         buildManifold(m, plane.n, pts, depths, n);
     }
     return true;
@@ -497,8 +497,10 @@ MDR_HD void emitContact(WorldView &v, const StepParams &p, SolverContact *sc, co
     for (int i = 0; i < 4; i++) {
         sc->lambda[i] = 0.f;
         if (i >= m.n) continue;
-        V3 c1 = m.pts[i];
-        V3 c2 = c1 - m.normal * m.depths[i];
+        // selected, not indexed: an indexed read would put the whole manifold in local memory
+        const V3 c1 = i == 0 ? m.pts[0] : i == 1 ? m.pts[1] : i == 2 ? m.pts[2] : m.pts[3];
+        const float depth = i == 0 ? m.depths[0] : i == 1 ? m.depths[1] : i == 2 ? m.depths[2] : m.depths[3];
+        V3 c2 = c1 - m.normal * depth;
         const V3 u1 = c1 - x1, u2 = c2 - x2;
         V3 r1 = zero, r2 = zero, r1w = u1, r2w = u2;      // for an identity static only r*w + x is used below
         if (!id1) { r1 = rotate(qinv(q1), u1); r1w = rotate(q1, r1); }
@@ -519,6 +521,7 @@ MDR_HD void probeContact(const StepParams &p, int sub, int pi, const Manifold *m
     if (pi >= p.probe.max_contacts) return;
     ContactDev o;
     o.ref = ref; o.ref_pad = 0; o.alt = alt; o.alt_pad = 0;
+#pragma unroll
     for (int i = 0; i < 4; i++) {
         const bool on = m && i < m->n;
         o.pts[i][0] = on ? m->pts[i].x : 0.f; o.pts[i][1] = on ? m->pts[i].y : 0.f;

@@ -15,7 +15,7 @@ from collections import defaultdict
 
 
 def parse_dis(path, kernel):
-    chains, cur, on = {}, [], False
+    chains, cur, on, last = {}, [], False, []
     for line in open(path, errors="replace"):
         if ".section" in line and ".text." in line:
             on = kernel in line
@@ -28,8 +28,10 @@ def parse_dis(path, kernel):
             continue
         m = re.match(r"\s*/\*([0-9a-f]{4,})\*/\s+(\S+)", line)
         if m:
-            chains[int(m.group(1), 16)] = (list(cur), m.group(2))
-            cur = []
+            if cur:                 # an instruction without markers of its own belongs to the line of the one before
+                last = list(cur)
+                cur = []
+            chains[int(m.group(1), 16)] = (list(last), m.group(2))
     return chains
 
 
