@@ -121,6 +121,10 @@ class EcsRegistry:
         if self.h and not getattr(self, "_borrowed", False):
             self.lib.mdr_ecs_destroy(self.h)
         self.h = None
+        for ptr in getattr(self, "_pinned", []):
+            self.lib.mdr_host_free.argtypes = [C.c_void_p]
+            self.lib.mdr_host_free(ptr)
+        self._pinned = []
 
     def __del__(self):
         try:
@@ -270,6 +274,27 @@ class EcsRegistry:
         nb = self.col_bytes[arch][col]
         return as_torch(self.column_ptr(arch, col), (self.num_worlds, self.stride[arch], nb // np.dtype(dtype).itemsize),
                         dtype, self.gpu_id, owner=self)
+
+    def pinned_export_buffer(self, slot):
+        """A page-locked host array large enough for any row count of exported column `slot` (u8)."""
+        a = self.lib.mdr_ecs_get_exported  # noqa: F841  (the library is loaded)
+        arch_rows = max(self.stride) * self.num_worlds
+        nb = self.lib.mdr_ecs_export_bytes_per_row(self.h, slot)
+        n = int(arch_rows) * int(nb)
+        self.lib.mdr_host_alloc.restype = C.c_void_p
+        self.lib.mdr_host_alloc.argtypes = [C.c_uint64]
+        ptr = self.lib.mdr_host_alloc(n)
+        if not ptr:
+            raise MemoryError("mdr_host_alloc")
+        self._pinned = getattr(self, "_pinned", [])
+        self._pinned.append(ptr)
+        return np.ctypeslib.as_array((C.c_uint8 * n).from_address(ptr))
+
+    def export_into(self, slot, host):
+        """Copies exported column `slot` into the (pinned) host array; returns the bytes copied."""
+        n = self.lib.mdr_ecs_read_exported(self.h, slot, host.ctypes.data, host.nbytes)
+        _check(n, "read_exported")
+        return int(n)
 
     def export(self, slot):
         """Host copy of an exported column (u8)."""
