@@ -32,6 +32,12 @@ MDR_HD BodyXf bodyXf(const WorldView &v, const StepParams &p, int row)
     x.t = ld3(v.pos, row);
     const V3 s = ld3(v.scale, row);
     M3 rot = matFromQuat(ld4(v.rot, row));
+    if (s.x == 1.f && s.y == 1.f && s.z == 1.f) {
+        // unit scale: every product below is x * 1.f (and 1.f / 1.f = 1.f), the same bits as x
+        x.vtx = rot;
+        x.nrm = rot;
+        return x;
+    }
     x.vtx = matMulDiag(rot, s);
     x.nrm = matMulDiag(rot, mk3(1.f / s.x, 1.f / s.y, 1.f / s.z));
     return x;
