@@ -131,7 +131,7 @@ struct StepParams {
 #endif
 };
 
-enum { MDR_ERR_PAIR_OVERFLOW = 1 };
+enum { MDR_ERR_PAIR_OVERFLOW = 1, MDR_ERR_BAD_OBJECT = 2 };
 
 // Caps of the hull-hull path: 32 vertices / faces per slot of the warp SAT (phys_sat_warp.cuh), two slots in the
 // big-hull kernel variant; also the per-thread arrays of the host emulation.

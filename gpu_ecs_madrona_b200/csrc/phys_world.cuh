@@ -257,6 +257,15 @@ MDR_HD bool staticStable(V3 x, Q4 q)
 #define MDR_PHASE_BEGIN
 #endif
 
+MDR_HD void raiseError(const StepParams &p, int bit)
+{
+#if defined(__CUDA_ARCH__)
+    atomicOr(p.error_flags, bit);
+#else
+    *p.error_flags |= bit;
+#endif
+}
+
 // ------------------------------------------------------------- load/store ---
 MDR_HD void loadWorld(const BlockCtx &c, WorldView &v, const StepParams &p, int w)
 {
@@ -275,7 +284,10 @@ MDR_HD void loadWorld(const BlockCtx &c, WorldView &v, const StepParams &p, int 
     for (int i = c.tid(); i < n; i += c.nthreads()) {
         // four independent loads, then the object table (cached)
         const int32_t ent = t.entity[2 * (r0 + i) + 1];
-        const uint32_t obj = (uint32_t)t.obj[r0 + i];
+        uint32_t obj = (uint32_t)t.obj[r0 + i];
+        // the ObjectID column is the caller's (raw writes, tensors, an ECS system): an id outside the object table is
+        // flagged and treated as object 0 instead of being dereferenced (mdr_phys_sync answers MDR_EINVAL)
+        if (obj >= (uint32_t)p.a.num_objs) { raiseError(p, MDR_ERR_BAD_OBJECT); obj = 0u; }
         const uint32_t resp = t.resp[r0 + i];
         const uint32_t b = t.order[r0 + i];
         v.ent_id[i] = ent;
@@ -395,14 +407,6 @@ MDR_HD void groupExclusiveScan(const BlockCtx &c, int32_t *cnt, int n)
 #endif
 }
 
-MDR_HD void raiseError(const StepParams &p, int bit)
-{
-#if defined(__CUDA_ARCH__)
-    atomicOr(p.error_flags, bit);
-#else
-    *p.error_flags |= bit;
-#endif
-}
 
 // One rank-ordered broadphase entry against row a's current box.
 struct alignas(16) RankEntry { float lx, ly, lz; int32_t ent; float hx, hy, hz; uint32_t info; };

@@ -44,7 +44,8 @@ __global__ void __launch_bounds__(32 * kRebuildWarps) bvhRebuildKernel(const __g
     const size_t r0 = (size_t)w * t.stride;
     const int n = t.row_count[w];
     for (int i = lane; i < n; i += 32) {
-        const ObjDev *o = p.a.objs + t.obj[r0 + i];
+        const uint32_t oid = (uint32_t)t.obj[r0 + i];
+        const ObjDev *o = p.a.objs + (oid < (uint32_t)p.a.num_objs ? oid : 0u);      // flagged by the step kernel
         Box wb = applyTRS(objAABB(o), ld3(t.pos + 3 * r0, i), ld4(t.rot + 4 * r0, i), ld3(t.scale + 3 * r0, i));
         const Box leaf = expandWithMotion(wb, ldVelLin(t.vel + 6 * r0, i), p.vel_expand, p.accel_expand);
         stBox(t.leaf_aabb + 6 * r0, i, leaf);
@@ -773,10 +774,9 @@ int32_t mdr_phys_sync(mdr_phys *p)
     closeTiming(p);
     int32_t err = 0;
     REQ_CUDA(cudaMemcpy(&err, p->d_err, 4, cudaMemcpyDeviceToHost));
-    if (err & MDR_ERR_PAIR_OVERFLOW) {
-        REQ_CUDA(cudaMemset(p->d_err, 0, 4));
-        return MDR_EOVERFLOW;
-    }
+    if (err) REQ_CUDA(cudaMemset(p->d_err, 0, 4));
+    if (err & MDR_ERR_BAD_OBJECT) return MDR_EINVAL;       // an ObjectID outside the object table reached the step
+    if (err & MDR_ERR_PAIR_OVERFLOW) return MDR_EOVERFLOW;
     return MDR_OK;
 }
 

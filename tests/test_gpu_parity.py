@@ -299,3 +299,28 @@ def test_step_io_with_a_flagged_rebuild_reads_the_new_poses(cuda_lib, port_oracl
     e.run(5)
     assert_state_equal(e.state(), o.state(), None, "after")
     e.close(); o.close()
+
+
+def test_object_id_outside_the_table_is_an_error_code(cuda_lib):
+    """an ObjectID the caller writes through a raw / tensor path used to be dereferenced on the device.
+    It is flagged, treated as object 0 for the step, and mdr_phys_sync answers MDR_EINVAL; the executor stays usable."""
+    sc = scenes.collisions64(8)
+    e = phys.PhysExecutor(sc)
+    e.run(2)
+    ids = e.pinned(phys.COL_OBJECT_ID)
+    good = np.zeros((8, e.row_stride()), np.int32)
+    good[:, :sc.bodies_per_world] = sc.obj_ids
+    bad = good.copy()
+    bad[3, 5] = 77
+    ids.view(np.int32).reshape(8, e.row_stride())[:] = bad
+    e.write_raw_async(phys.COL_OBJECT_ID, ids)
+    with pytest.raises(phys.MadronaError) as ei:
+        e.run(1)
+    assert ei.value.code == phys.MDR_EINVAL
+    ids.view(np.int32).reshape(8, e.row_stride())[:] = good
+    e.write_raw_async(phys.COL_OBJECT_ID, ids)
+    e.run(3)
+    assert np.isfinite(e.state()[0]).all()
+    with pytest.raises(phys.MadronaError):          # the checked path refuses it up front
+        e.write(phys.COL_OBJECT_ID, np.full((8, sc.bodies_per_world), 9, np.int32))
+    e.close()
