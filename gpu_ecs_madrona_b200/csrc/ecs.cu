@@ -262,7 +262,7 @@ __device__ __forceinline__ void gridBarrier(unsigned *bar /*[2]: arrivals, gener
             __threadfence();
             atomicAdd(bar + 1, 1u);
         } else {
-            while (*(volatile unsigned *)(bar + 1) == gen) { }
+            while (*(volatile unsigned *)(bar + 1) == gen) __nanosleep(100);   // leave the issue slots to the blocks still at work
         }
         __threadfence();
     }
