@@ -100,7 +100,9 @@ struct EcsDev {
 
 // Per-warp shared memory: the world's row counts and id caches live here for the
 // whole step (loaded once, written back once), plus the radix-sort histogram.
+constexpr int kTileArch = 4, kTileCols = 8;      // column tile addresses kept per warp for the first archetypes / columns
 struct WarpShared {
+    char *tile[kTileArch * kTileCols];              // this world's tile of (archetype a < 4, column c < 8), filled by loadWorld
     int32_t count[kMaxArch];
     IdState ids;
     int32_t tmp_used;               // bump pointer of the world's tmpAlloc arena
@@ -251,6 +253,9 @@ struct Context {
 
     __device__ __forceinline__ char *colPtr(int arch, int col) const
     {
+        // the address of this world's tile: from the per-warp table (one shared-memory load) for the first
+        // archetypes / columns, computed from the descriptor otherwise
+        if (arch < kTileArch && col < kTileCols) return ws->tile[arch * kTileCols + col];
         const ArchDev &A = archs[arch];
         return A.col[col] + (size_t)world * A.stride * A.col_bytes[col];
     }
@@ -694,6 +699,15 @@ __device__ inline void loadWorld(Context &ctx, const EcsDev *E, WarpShared *ws, 
     ctx.created_row = -1;
     __syncwarp();
     if (lane == 0) { ws->tmp_used = E->tmp_used ? E->tmp_used[world] : 0; ws->done = 0u; }
+    {
+        const int a = lane / kTileCols, c = lane % kTileCols;      // 32 lanes = kTileArch x kTileCols entries
+        char *ptr = nullptr;
+        if (a < E->num_arch && c < ctx.archs[a].num_cols) {
+            const ArchDev &A = ctx.archs[a];
+            ptr = A.col[c] + (size_t)world * A.stride * A.col_bytes[c];
+        }
+        ws->tile[lane] = ptr;
+    }
     if (lane < E->num_arch) ws->count[lane] = ctx.archs[lane].row_count[world];
     if (lane < (int)(sizeof(IdState) / 4)) ((int32_t *)&ws->ids)[lane] = ((const int32_t *)(E->id_state + world))[lane];
     __syncwarp();
