@@ -701,8 +701,27 @@ int32_t mdr_phys_step_io_async(mdr_phys *p, int32_t num_in, const int32_t *in_co
     const int waves = (W + wave - 1) / wave;
     if (chunks < 1) chunks = 1;
     if (chunks > waves) chunks = waves;
-    const int per = (waves + chunks - 1) / chunks * wave;       // worlds per range
-    const int ranges = (W + per - 1) / per;
+    // World ranges in whole resident waves. What the pipeline cannot hide is the copy-in of the FIRST range and the
+    // copy-out of the LAST one, so with five ranges or more the ends are short (1 and 2 waves) and the middle carries
+    // the rest: 14 waves in 7 ranges = 1 2 3 3 2 2 1 ... the exposed copies shrink from a quarter of the batch to 1/14.
+    std::vector<int> range_waves;
+    if (chunks >= 5 && waves >= chunks + 2) {
+        const int mid = chunks - 4, rest = waves - 6;
+        range_waves = { 1, 2 };
+        for (int k = 0; k < mid; k++) range_waves.push_back(rest / mid + (k < rest % mid ? 1 : 0));
+        range_waves.push_back(2);
+        range_waves.push_back(1);
+    } else {
+        const int per_waves = (waves + chunks - 1) / chunks;
+        for (int left = waves; left > 0; left -= per_waves) range_waves.push_back(left < per_waves ? left : per_waves);
+    }
+    const int ranges = (int)range_waves.size();
+    std::vector<int> range_first(ranges + 1, 0);
+    for (int r = 0; r < ranges; r++) {
+        const long long nxt = (long long)range_first[r] + (long long)range_waves[r] * wave;
+        range_first[r + 1] = nxt < W ? (int)nxt : W;
+    }
+    range_first[ranges] = W;
     if (!p->io_in) {
         REQ_CUDA(cudaStreamCreateWithFlags(&p->io_in, cudaStreamNonBlocking));
         REQ_CUDA(cudaStreamCreateWithFlags(&p->io_out, cudaStreamNonBlocking));
@@ -734,7 +753,8 @@ int32_t mdr_phys_step_io_async(mdr_phys *p, int32_t num_in, const int32_t *in_co
         p->maybe_rebuild = false;
     }
     for (int r = 0; r < ranges; r++) {
-        const int first = r * per, end = first + per < W ? first + per : W;
+        const int first = range_first[r], end = range_first[r + 1];
+        if (end <= first) continue;
         for (int i = 0; i < num_in && !inputs_first; i++) {
             const size_t row = (size_t)kColBytes[in_cols[i]] * stride;
             REQ_CUDA(cudaMemcpyAsync((char *)*colSlot(p->params.t, in_cols[i]) + row * first,
