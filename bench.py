@@ -375,6 +375,7 @@ def run_ours(args):
                        "launch": info, "wall_ms_per_step": 1e3 * wall / args.steps,
                        "parallelism": f"worlds sharded over {world} GPU(s), no per-step communication",
                        "episode_stats_all_gather": episode},
+            "mean_contacts_per_world": C, "mean_pairs_per_world": P,      # the regime the value was measured in
             "gpu_launches": args.steps,
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d,
                     "d2h_bytes_per_step": d2h, "steps": e2e_steps, "finite": finite,
