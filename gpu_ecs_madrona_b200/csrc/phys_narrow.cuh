@@ -253,9 +253,11 @@ MDR_HD void setManifoldPoint(Manifold &m, int idx, V3 pt, float depth)
 // buildFaceContactManifold, narrowphase.cpp:790-864. The >4-point reduction
 // reproduces the reference as written: `largestArea` is never updated, so point
 // 2 is the LAST candidate of positive signed area and point 3 the LAST of
-// negative area; when none qualifies the reference reads an
-// uninitialised slot -- here the slot repeats point 0 (point 1: zeros), like
-// the CPU checker, and such worlds are excluded from bit-exact comparison.
+// negative area; when none qualifies the reference reads a slot
+// of its local manifold that it never wrote. The slot is zero here: the value
+// the unmodified reference computes once its locals are defined (compiled with
+// -ftrivial-auto-var-init=zero -fno-elide-constructors), so
+// every world compares bit for bit with that build.
 MDR_HD void buildManifold(Manifold &m, V3 n, V3 *contacts, float *depths, int num)
 {
     const V3 zero = mk3(0.f, 0.f, 0.f);
@@ -282,8 +284,6 @@ MDR_HD void buildManifold(Manifold &m, V3 n, V3 *contacts, float *depths, int nu
         contacts[far_idx] = m.pts[0];
         V3 diff0 = m.pts[1] - p0;
         int area_idx = 0;
-        m.pts[2] = m.pts[3] = m.pts[0];
-        m.depths[2] = m.depths[3] = m.depths[0];
         for (int i = 1; i < num; i++) {
             float area = dot(n, cross(diff0, contacts[i] - p0));
             if (area > 0.0f) { m.pts[2] = contacts[i]; m.depths[2] = depths[i]; area_idx = i; }

@@ -115,8 +115,11 @@ int32_t orc_get_hull(void *h, int32_t obj,
                      uint32_t *edges, uint32_t *polys, float *planes /*[4*n]*/,
                      int32_t *counts /*[4] hedges,edges,polys,verts*/);
 /* Per-world count of manifold reductions whose 3rd/4th point the reference
- * leaves uninitialised (narrowphase.cpp:830-853, undefined behaviour): worlds
- * with a non-zero count are excluded from bit-exact comparison. The compiled
+ * never writes (narrowphase.cpp:830-853, undefined behaviour): worlds with a
+ * non-zero count are excluded from bit-exact comparison against the STOCK
+ * reference build (_ref/libmadrona_ref.so); against the build whose locals are
+ * defined (_ref/libmadrona_ref_defined.so, oracle/Makefile) every world is
+ * compared -- the restatement uses that build's value, zero. The compiled
  * reference cannot know and reports -1. */
 void orc_indeterminate(void *h, int64_t *out /*[W]*/);
 /* BVH::traceRay (src/physics/broadphase.cpp:653-856) for n rays in world `world`,

@@ -11,6 +11,8 @@ import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 REF_SO = os.path.join(HERE, "_ref", "libmadrona_ref.so")
+# the same sources with automatic variables zero-initialised (oracle/Makefile): kind "reference_defined"
+REF_DEFINED_SO = os.path.join(HERE, "_ref", "libmadrona_ref_defined.so")
 PORT_SO = os.path.join(HERE, "libmadrona_port.so")
 
 COL_BYTES = [8, 12, 16, 12, 24, 4, 4, 28, 28, 24, 12, 12, 4]
@@ -52,8 +54,12 @@ def build(kind):
     subprocess.run(["make", "-C", HERE, kind], check=True, capture_output=True)
 
 
+def _path(kind):
+    return {"reference": REF_SO, "reference_defined": REF_DEFINED_SO}.get(kind, PORT_SO)
+
+
 def available(kind):
-    return os.path.exists(REF_SO if kind == "reference" else PORT_SO)
+    return os.path.exists(_path(kind))
 
 
 def pack_objects(objects):
@@ -85,7 +91,7 @@ class Oracle:
     """One checker instance over a `gpu_ecs_madrona_b200.scenes.Scene`."""
 
     def __init__(self, scene, kind="port"):
-        path = REF_SO if kind == "reference" else PORT_SO
+        path = _path(kind)
         if not os.path.exists(path):
             raise FileNotFoundError(f"{path} not built (make -C oracle)")
         self.lib = C.CDLL(path)

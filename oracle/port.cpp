@@ -926,9 +926,14 @@ struct Manifold { V3 pts[4]; float depths[4]; int n; V3 normal; };
 // reference's reduction as written: `largestArea` is never updated, so point 2
 // is the LAST candidate with positive signed area and point 3 the LAST with
 // negative area. When no candidate qualifies the reference reads
-// an uninitialised stack slot (undefined behaviour, cannot be restated): here
-// the slot repeats point 0 and `*indeterminate` is bumped so tests can exclude
-// the world from bit-exact comparison.
+// a slot of `Manifold manifold;` it never wrote (undefined behaviour: the
+// stock build returns stale stack bytes). The slot is ZERO here, which is what
+// the unmodified reference computes when its locals are defined:
+// oracle/_ref/libmadrona_ref_defined.so = the same sources compiled with
+// -ftrivial-auto-var-init=zero -fno-elide-constructors (without the second
+// flag `manifold` is the function's return slot, which the first does not
+// touch). `*indeterminate` is still bumped so tests against the STOCK build
+// can exclude the world.
 Manifold buildManifold(V3 n, V3 *contacts, float *depths, int num, int64_t *indeterminate)
 {
     Manifold m;
@@ -957,8 +962,6 @@ Manifold buildManifold(V3 n, V3 *contacts, float *depths, int num, int64_t *inde
         const float largest_area = 0.0f;
         int area_idx = 0;
         bool found2 = false, found3 = false;
-        m.pts[2] = m.pts[3] = m.pts[0];
-        m.depths[2] = m.depths[3] = m.depths[0];
         for (int i = 1; i < num; i++) {
             float area = dot(n, cross(diff0, contacts[i] - p0));
             if (area > largest_area) {

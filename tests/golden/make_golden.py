@@ -1,8 +1,15 @@
 """Generates tests/golden/*.npz from the UNMODIFIED reference compiled by
-oracle/Makefile (oracle/_ref/libmadrona_ref.so, needs /root/reference). Run in
-the build container: `python tests/golden/make_golden.py`. The fixtures pin the
-oracle restatement (tests/test_oracle_pin.py) and the CUDA path
-(tests/test_gpu_parity.py) on machines where the reference is not mounted.
+oracle/Makefile (needs /root/reference). Run in the build container:
+`python tests/golden/make_golden.py`. The fixtures pin the oracle restatement
+(tests/test_oracle_pin.py) and the CUDA path (tests/test_gpu_parity.py) on
+machines where the reference is not mounted.
+
+The values come from oracle/_ref/libmadrona_ref_defined.so: the reference's
+sources with automatic variables zero-initialised, so that the manifold slots
+buildFaceContactManifold never writes (narrowphase.cpp:830-853) are defined and
+EVERY world of every case is comparable. The stock build
+(oracle/_ref/libmadrona_ref.so) runs beside it here and must agree bit for bit
+in every world that never reads such a slot.
 """
 import os
 import sys
@@ -37,7 +44,7 @@ def main():
         if only and name not in only:
             continue
         sc = fn(**kw)
-        ref = orc.Oracle(sc, "reference")
+        ref = orc.Oracle(sc, "reference_defined")
         # the probe step doubles as step 1
         out = {}
         pr = ref.probe_step(pw)
@@ -50,15 +57,21 @@ def main():
         out["probe_leaf_aabbs"] = pr["leaf_aabbs"]
         out["probe_ref_rank"] = pr["ref_rank"]
         # every other world takes its first step too
-        rest = orc.Oracle(sc, "reference")
-        rest.step()
+        rest = orc.Oracle(sc, "reference_defined")
+        stock = orc.Oracle(sc, "reference")
+        flags = orc.Oracle(sc, "port")      # only for its count of undefined-slot reads per world
+        rest.step(); stock.step(); flags.step()
         step = 1
         for snap in snaps:
             while step < snap:
-                rest.step()
+                rest.step(); stock.step(); flags.step()
                 step += 1
             pos, rot, vel = rest.state()
             out[f"pos_{snap}"], out[f"rot_{snap}"], out[f"vel_{snap}"] = pos, rot, vel
+            det = flags.indeterminate() == 0
+            for a, b in zip(rest.state(), stock.state()):
+                assert np.array_equal(a.view(np.uint32)[det], b.view(np.uint32)[det]), (name, snap)
+        out["undefined_reads"] = flags.indeterminate()
         # the probed world of `ref` must agree with the plain run after step 1
         p1 = ref.state()
         assert np.array_equal(p1[0][pw].view(np.uint32), out["pos_%d" % snaps[0]][pw].view(np.uint32)) \

@@ -1,5 +1,6 @@
 """Generates tests/golden/rays_*.npz: BVH::traceRay of the UNMODIFIED reference
-(oracle/_ref/libmadrona_ref.so, needs /root/reference) on seeded rays, after the
+(oracle/_ref/libmadrona_ref_defined.so -- the build whose manifold slots are
+defined, see make_golden.py; needs /root/reference) on seeded rays, after the
 step counts of make_golden.CASES. Run in the build container:
 `python tests/golden/make_ray_golden.py`. Pins oracle/port.cpp's restatement and
 the CUDA ray kernel where the reference is not mounted.
@@ -27,7 +28,7 @@ def main():
         if only and name not in only:
             continue
         sc = fn(**kw)
-        ref = orc.Oracle(sc, "reference")
+        ref = orc.Oracle(sc, "reference_defined")
         rng = np.random.default_rng(SEED)
         out = {}
         step = 0

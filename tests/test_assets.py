@@ -150,12 +150,15 @@ def test_obj_loader_triangular_and_errors(host_lib, emu_lib):
 def test_port_matches_compiled_reference_on_hull_pile(port_oracle, ref_oracle):
     sc = scenes.hull_pile(10)
     r = ref_oracle.Oracle(sc, "reference")
+    d = ref_oracle.Oracle(sc, "reference_defined")     # locals defined: every world comparable (oracle/Makefile)
     p = port_oracle.Oracle(sc, "port")
     for st in range(40):
         r.step()
+        d.step()
         p.step()
         det = p.indeterminate() == 0
         assert_state_equal(p.state(), r.state(), det, f"hull pile step {st}")
+        assert_state_equal(p.state(), d.state(), None, f"hull pile step {st} (defined build)")
     assert det.sum() >= 5
 
 
@@ -252,12 +255,15 @@ def test_hull_at_capacity_and_beyond(port_oracle, emu_lib):
 def test_port_matches_compiled_reference_at_hull_capacity(port_oracle, ref_oracle):
     for name, sc in (("32", _capacity_scene(16, 6)), ("64", _barrel_scene(6))):
         r = ref_oracle.Oracle(sc, "reference")
+        d = ref_oracle.Oracle(sc, "reference_defined")
         p = port_oracle.Oracle(sc, "port")
         for st in range(30):
             r.step()
+            d.step()
             p.step()
             det = p.indeterminate() == 0
             assert_state_equal(p.state(), r.state(), det, f"{name}-vertex hulls step {st}")
+            assert_state_equal(p.state(), d.state(), None, f"{name}-vertex hulls step {st} (defined build)")
         assert det.sum() >= 3, name
 
 

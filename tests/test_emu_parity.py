@@ -89,11 +89,8 @@ def test_emu_probe_matches_golden(emu_lib, port_oracle, name):
     rank = np.empty(sc.bodies_per_world, np.int32)
     rank[order[pw].astype(np.int64)] = np.arange(sc.bodies_per_world)
     assert np.array_equal(rank, g["probe_ref_rank"])
-    o = port_oracle.Oracle(sc, "port")
-    o.probe_step(pw)
-    if o.indeterminate()[pw] == 0:
-        for s, c in enumerate(pr["contacts"]):
-            assert contacts_equal(c, g[f"probe_contacts_{s}"]), f"substep {s}"
+    for s, c in enumerate(pr["contacts"]):
+        assert contacts_equal(c, g[f"probe_contacts_{s}"]), f"substep {s}"
 
 
 def test_emu_ragged_and_empty_worlds(port_oracle, emu_lib):
@@ -115,8 +112,6 @@ def test_emu_ragged_and_empty_worlds(port_oracle, emu_lib):
                            sub.ext_force[sl, :n], sub.ext_torque[sl, :n])
         o = port_oracle.Oracle(one, "port")
         o.step(12)
-        if o.indeterminate()[0]:
-            continue
         want = o.state()
         for a, b in zip(got, want):
             assert np.array_equal(bits(a[w, :n]), bits(b[0])), f"world {w}"

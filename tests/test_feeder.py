@@ -25,17 +25,16 @@ def bits(a):
 
 def test_port_feeder_matches_compiled_reference(port_oracle, ref_oracle):
     sc = scenes.tumble(5, seed=2)
-    ref, port = ref_oracle.Oracle(sc, "reference"), port_oracle.Oracle(sc, "port")
+    # the reference build whose manifold slots are defined (oracle/Makefile): every world
+    ref, port = ref_oracle.Oracle(sc, "reference_defined"), port_oracle.Oracle(sc, "port")
     rng = np.random.default_rng(1)
     for steps in (0, 3, 9):
         ref.step(steps)
         port.step(steps)
-        ok = port.indeterminate() == 0
         spec = view_spec(rng, sc.num_worlds, sc.bodies_per_world)
         a, b = ref.feeder(OFFSET, *spec), port.feeder(OFFSET, *spec)
-        assert ok.sum() >= 2
         for x, y in zip(a, b):
-            assert np.array_equal(bits(x[ok]), bits(y[ok]))
+            assert np.array_equal(bits(x), bits(y))
 
 
 def run_feeder_host(e, spec):
@@ -50,10 +49,9 @@ def run_feeder_host(e, spec):
 
 def check(e, o, sc, tr, ids, views, spec):
     N = sc.bodies_per_world
-    ok = o.indeterminate() == 0
     want_tr, want_views = o.feeder(OFFSET, *spec)
-    assert np.array_equal(bits(tr[:, :N][ok]), bits(want_tr[ok]))
-    assert np.array_equal(bits(views[ok]), bits(want_views[ok]))
+    assert np.array_equal(bits(tr[:, :N]), bits(want_tr))
+    assert np.array_equal(bits(views), bits(want_views))
     assert np.array_equal(ids[:, :N], np.asarray(sc.obj_ids, np.int32).reshape(sc.num_worlds, N))
     assert (ids[:, N:] == -1).all() and not tr[:, N:].any()
 

@@ -40,16 +40,14 @@ def test_cuda_matches_reference_golden(cuda_lib, port_oracle, name):
     fn, kw, snaps, pw = CASES[name]
     g = load_golden(name)
     sc = fn(**kw)
-    o = port_oracle.Oracle(sc, "port")   # only to know which worlds hit the reference's UB
     e = phys.PhysExecutor(sc)
     step = 0
     for snap in snaps:
-        while step < snap:
-            e.run(); o.step()
-            step += 1
-        det = o.indeterminate() == 0
+        e.run(snap - step)
+        step = snap
+        # every world: the fixtures are the reference build whose manifold slots are defined (make_golden.py)
         assert_state_equal(e.state(), (g[f"pos_{snap}"], g[f"rot_{snap}"], g[f"vel_{snap}"]),
-                           det, f"{name} step {snap}")
+                           None, f"{name} step {snap}")
     e2 = phys.PhysExecutor(sc, smem_contacts=8)    # exercises the global overflow slots
     pr = e2.probe_step(pw)
     assert np.array_equal(pr["pairs"], g["probe_pairs"])
@@ -60,11 +58,8 @@ def test_cuda_matches_reference_golden(cuda_lib, port_oracle, name):
     rank = np.empty(sc.bodies_per_world, np.int32)
     rank[order[pw].astype(np.int64)] = np.arange(sc.bodies_per_world)
     assert np.array_equal(rank, g["probe_ref_rank"])
-    o2 = port_oracle.Oracle(sc, "port")
-    o2.probe_step(pw)
-    if o2.indeterminate()[pw] == 0:
-        for s, c in enumerate(pr["contacts"]):
-            assert contacts_equal(c, g[f"probe_contacts_{s}"]), f"substep {s}"
+    for s, c in enumerate(pr["contacts"]):
+        assert contacts_equal(c, g[f"probe_contacts_{s}"]), f"substep {s}"
 
 
 def test_cuda_hinges_and_joint_table_updates(cuda_lib, port_oracle):
@@ -110,6 +105,24 @@ def test_cuda_drift_100_steps(cuda_lib, port_oracle):
     assert_state_equal(e.state(), o.state(), None, "100 steps")
 
 
+@pytest.mark.parametrize("name", ["tumble48", "tumble40", "hull_pile"])
+def test_cuda_matches_defined_reference_100_steps(cuda_lib, ref_oracle, name):
+    """Hull-hull scenes, 100 steps, EVERY world against the compiled reference itself: the build whose locals are
+    defined (oracle/_ref/libmadrona_ref_defined.so), so the worlds in which buildFaceContactManifold returns a
+    slot it never wrote (11 of 48 / 16 / 32 here) are compared too, not masked."""
+    if not ref_oracle.available("reference_defined"):
+        pytest.skip("oracle/_ref/libmadrona_ref_defined.so did not travel")
+    sc = {"tumble48": lambda: scenes.tumble(48),
+          "tumble40": lambda: scenes.tumble(16, num_bodies=40, spread=1.0, seed=3),
+          "hull_pile": lambda: scenes.hull_pile(32)}[name]()
+    d = ref_oracle.Oracle(sc, "reference_defined")
+    e = phys.PhysExecutor(sc)
+    for st in range(0, 100, 10):
+        d.step(10, 8)
+        e.run(10)
+        assert_state_equal(e.state(), d.state(), None, f"{name} step {st + 10}")
+
+
 def test_cuda_ragged_and_empty_worlds(cuda_lib, port_oracle):
     full = scenes.tumble(6, num_bodies=15)
     rows = np.array([16, 9, 1, 0, 5, 16], np.int32)
@@ -128,8 +141,6 @@ def test_cuda_ragged_and_empty_worlds(cuda_lib, port_oracle):
                            sub.ext_force[sl, :n], sub.ext_torque[sl, :n])
         o = port_oracle.Oracle(one, "port")
         o.step(12)
-        if o.indeterminate()[0]:
-            continue
         for a, b in zip(got, o.state()):
             assert np.array_equal(bits(a[w, :n]), bits(b[0])), f"world {w}"
     assert np.array_equal(got[0][3], np.ascontiguousarray(full.pos[3], np.float32))

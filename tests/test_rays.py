@@ -26,10 +26,9 @@ def oracle_rays(o, origins, dirs, t_max):
     return tuple(np.stack([r[k] for r in res]) for k in range(3))
 
 
-def golden_walk(name, executor_rays, step_fn, indeterminate):
-    """Replays make_ray_golden's schedule and compares at every snapshot. Worlds in
-    which the reference read an uninitialised manifold slot (`indeterminate()`,
-    oracle_api.h) are left out, as in the step parity tests."""
+def golden_walk(name, executor_rays, step_fn):
+    """Replays make_ray_golden's schedule and compares at every snapshot, every world
+    (the fixtures come from the reference build whose manifold slots are defined)."""
     fn, kw, snaps, _ = CASES[name]
     g = load_golden("rays_" + name)
     step = 0
@@ -37,8 +36,7 @@ def golden_walk(name, executor_rays, step_fn, indeterminate):
         step_fn(snap - step)
         step = snap
         o, d = g[f"origins_{snap}"], g[f"dirs_{snap}"]
-        worlds = np.nonzero(indeterminate() == 0)[0]
-        assert len(worlds) >= 2
+        worlds = np.arange(o.shape[0])
         for tag, tm in (("inf", np.float32(np.inf)), ("t3", np.float32(3.0))):
             want = (g[f"t_{snap}_{tag}"], g[f"normal_{snap}_{tag}"], g[f"row_{snap}_{tag}"])
             assert_rays_equal(executor_rays(o, d, tm), want, worlds, f"{name} step {snap} {tag}")
@@ -48,7 +46,7 @@ def golden_walk(name, executor_rays, step_fn, indeterminate):
 def test_port_rays_match_reference_golden(port_oracle, name):
     fn, kw, _, _ = CASES[name]
     o = port_oracle.Oracle(fn(**kw), "port")
-    golden_walk(name, lambda a, b, tm: oracle_rays(o, a, b, tm), o.step, o.indeterminate)
+    golden_walk(name, lambda a, b, tm: oracle_rays(o, a, b, tm), o.step)
 
 
 def test_golden_ray_generator_is_seeded_like_the_tests():
@@ -59,12 +57,12 @@ def test_golden_ray_generator_is_seeded_like_the_tests():
 @pytest.mark.parametrize("name", sorted(SCENES))
 def test_port_rays_match_compiled_reference(port_oracle, ref_oracle, name):
     sc = SCENES[name]()
-    ref, port = ref_oracle.Oracle(sc, "reference"), port_oracle.Oracle(sc, "port")
+    ref, port = ref_oracle.Oracle(sc, "reference_defined"), port_oracle.Oracle(sc, "port")
     rng = np.random.default_rng(11)
     for steps in (1, 6, 20):
         ref.step(steps)
         port.step(steps)
-        ok = np.nonzero(port.indeterminate() == 0)[0]
+        ok = np.arange(sc.num_worlds)
         o, d = world_rays(rng, 128, ref.read_f32(ref_oracle.COL_POSITION))
         for tm in (np.float32(np.inf), np.float32(2.5)):
             assert_rays_equal(oracle_rays(port, o, d, tm), oracle_rays(ref, o, d, tm), ok, f"{name} +{steps}")
@@ -79,7 +77,7 @@ def test_emu_rays_match_oracle(port_oracle, emu_lib, name):
     for steps in (1, 7, 22):
         o.step(steps)
         e.run(steps)
-        ok = np.nonzero(o.indeterminate() == 0)[0]
+        ok = np.arange(sc.num_worlds)
         og, dr = world_rays(rng, 64, o.read_f32(port_oracle.COL_POSITION))
         for tm in (None, np.float32(2.0)):
             t, n, ent, row = e.trace_rays(og, dr, tm)
@@ -102,7 +100,7 @@ def test_cuda_rays_match_oracle(cuda_lib, port_oracle, name):
     for steps, rays in ((1, 33), (7, 128), (22, 300)):
         o.step(steps)
         e.run(steps)
-        ok = np.nonzero(o.indeterminate() == 0)[0]
+        ok = np.arange(sc.num_worlds)
         og, dr = world_rays(rng, rays, o.read_f32(port_oracle.COL_POSITION))
         for tm in (None, np.float32(2.0)):
             t, n, ent, row = e.trace_rays(og, dr, tm)
@@ -119,16 +117,12 @@ def test_cuda_rays_match_oracle(cuda_lib, port_oracle, name):
 def test_cuda_rays_match_reference_golden(cuda_lib, port_oracle, name):
     fn, kw, _, _ = CASES[name]
     e = phys.PhysExecutor(fn(**kw))
-    o = port_oracle.Oracle(fn(**kw), "port")       # only says which worlds are comparable
 
     def rays(og, d, tm):
         t, n, _, row = e.trace_rays(og, d, tm)
         return t, n, row
 
-    def step(k):
-        e.run(k)
-        o.step(k)
-    golden_walk(name, rays, step, o.indeterminate)
+    golden_walk(name, rays, e.run)
 
 
 @pytest.mark.gpu
