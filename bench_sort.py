@@ -27,6 +27,7 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--lib", default="", help="another build of csrc/table_sort.cu (profiles/exp sweeps)")
     args = ap.parse_args()
     import torch
     from gpu_ecs_madrona_b200 import table_sort
@@ -41,7 +42,8 @@ def main():
         d_in = [torch.from_numpy(np.ascontiguousarray(c)).cuda() for c in cols]
         d_out = [torch.empty_like(c) for c in d_in]
         d_map = torch.full((n,), -1, dtype=torch.int32, device="cuda")
-        s = table_sort.TableSort(n, PHYS_COLS, 1, W)
+        import ctypes
+        s = table_sort.TableSort(n, PHYS_COLS, 1, W, lib=ctypes.CDLL(args.lib) if args.lib else None)
         for _ in range(args.warmup):
             rows = s.run(d_in, d_out, n, d_map)
         ms, launches = [], 0
