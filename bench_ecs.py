@@ -72,9 +72,16 @@ def run_record(name, worlds=0, steps=100, warmup=10, no_cpu=False):
     ex = EcsExecutor(app, W)
     ex.run(warmup)
     ex.step_ms()
-    ex.run_async(steps)
+    ex.run_async(steps)          # ONE call of `steps` steps: a batch, walked inside one launch (mdr_ecs_last_launches)
     ex.sync()
     ms, n = ex.step_ms()
+    launches = ex.last_launches()
+    # the same number of steps as `steps` calls of one step each (one graph launch per step), for comparison
+    for _ in range(steps):
+        ex.run_async(1)
+    ex.sync()
+    ms1, n1 = ex.step_ms()
+    launches1 = n1 * ex.launches_per_step()
     rows = ex.row_counts().mean(axis=0)
     Abytes = algorithmic_bytes(app, rows)
     peak = 6463.0
@@ -97,7 +104,8 @@ def run_record(name, worlds=0, steps=100, warmup=10, no_cpu=False):
     line = {"metric": f"world-steps/sec ({A.APP_NAMES[app]}, device-timed)", "value": W * n / (ms * n * 1e-3),
             "unit": "world-steps/s", "n_gpus": 1, "steps": n, "warmup": warmup, "ms_per_step": ms,
             "config": {"workload": f"{A.APP_NAMES[app]}: {W} worlds, params {ex.params}", "mean_rows": rows.tolist()},
-            "gpu_launches": n * ex.launches_per_step(),
+            "gpu_launches": launches, "steps_per_call": n,
+            "one_step_per_call": {"value": W / (ms1 * 1e-3), "ms_per_step": ms1, "gpu_launches": launches1},
             "e2e": {"value": W * steps / e2e_s, "unit": "world-steps/s", "h2d_bytes_per_step": 0,
                     "d2h_bytes_per_step": int(d2h), "steps": steps},
             "roofline": {"bound": "hbm", "achieved": Abytes * W / (ms * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",

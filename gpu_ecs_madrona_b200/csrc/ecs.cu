@@ -46,7 +46,7 @@ struct AppsBuiltin {
 };
 template <int kMinBlocks>
 __global__ void __launch_bounds__(32 * kWarpsPerBlock, kMinBlocks)
-ecsStepKernel(const EcsDev *__restrict__ E, int first, int last)
+ecsStepKernel(const EcsDev *__restrict__ E, int first, int last, int steps)
 {
     __shared__ WarpShared shared[kWarpsPerBlock];
     __shared__ BlockDescriptors descriptors;
@@ -56,7 +56,12 @@ ecsStepKernel(const EcsDev *__restrict__ E, int first, int last)
     const NodeDev *nodes = loadDescriptors(&descriptors, ctx, E, first, last);
     for (int w = blockIdx.x * kWarpsPerBlock + (threadIdx.x >> 5); w < E->num_worlds; w += warps) {
         loadWorld(ctx, E, ws, w);
-        runNodes(ctx, nodes, last - first, AppsBuiltin());
+        // `steps` walks of the graph back to back (mdr_ecs_step_async(e, n > 1)): no world reads another world,
+        // so a warp may run its world ahead; row counts and id state stay in shared memory between the walks
+        for (int k = 0; k < steps; k++) {
+            if (k) beginStep(ctx);
+            runNodes(ctx, nodes, last - first, AppsBuiltin());
+        }
         storeWorld(ctx);
     }
 }
@@ -271,7 +276,7 @@ __device__ __forceinline__ void gridBarrier(unsigned *bar /*[2]: arrivals, gener
 
 template <int kMinBlocks>
 __global__ void __launch_bounds__(32 * kWarpsPerBlock, kMinBlocks)
-ecsFusedStepKernel(const EcsDev *__restrict__ E, int first, int last, unsigned *bar)
+ecsFusedStepKernel(const EcsDev *__restrict__ E, int first, int last, unsigned *bar, int steps)
 {
     __shared__ WarpShared shared[kWarpsPerBlock];
     __shared__ BlockDescriptors descriptors;
@@ -294,9 +299,13 @@ ecsFusedStepKernel(const EcsDev *__restrict__ E, int first, int last, unsigned *
             copyWordsWarp((uint32_t *)(A.col[x.col] + (size_t)w * A.stride * x.bytes), (const uint32_t *)x.buffer + off * (x.bytes >> 2), total, lane);
         }
         __syncwarp();
-        // 2. TaskGraph::run
+        // 2. TaskGraph::run, `steps` times (a batch: the staged exports are observable only at its end, so
+        //    copy-in happens once before and offsets + copy-out once after; nothing else crosses worlds)
         loadWorld(ctx, E, &shared[warp], w);
-        runNodes(ctx, nodes, last - first, AppsBuiltin());
+        for (int k = 0; k < steps; k++) {
+            if (k) beginStep(ctx);
+            runNodes(ctx, nodes, last - first, AppsBuiltin());
+        }
         storeWorld(ctx);
     }
     // 3. every world's row counts are final
@@ -373,8 +382,11 @@ struct mdr_ecs {
     cudaGraphExec_t graph = nullptr;
     bool exports_dirty = true;
     int blocks = 0;
-    void (*step_kernel)(const EcsDev *, int, int) = nullptr;
-    void (*fused_kernel)(const EcsDev *, int, int, unsigned *) = nullptr;   // the whole step in one launch, when it applies
+    void (*step_kernel)(const EcsDev *, int, int, int) = nullptr;
+    void (*fused_kernel)(const EcsDev *, int, int, unsigned *, int) = nullptr;   // the whole step in one launch, when it applies
+    bool all_resident = false;      // every world fits the fused kernel's resident grid (and MDR_ECS_NO_FUSED is not set)
+    bool batch_ok = true;           // n > 1 steps of one call run inside one launch (MDR_ECS_NO_BATCH=1: n graph launches)
+    int last_call_launches = 0;     // kernels launched by the last mdr_ecs_step_async call
     unsigned *grid_bar = nullptr;
     bool fused_ok = false, fused_in_graph = false;
     mdr_ecs_launch_fn launcher = nullptr;   // megakernel instantiated in the user's translation unit
@@ -888,8 +900,10 @@ static int32_t buildImpl(mdr_ecs *e)
     // at 1024 (the barrier is two more dependent round trips in a step that is all latency): on by default from 2048
     // worlds, MDR_ECS_FUSED=1 / MDR_ECS_NO_FUSED=1 force it either way.
     const char *nf = getenv("MDR_ECS_NO_FUSED"), *ff = getenv("MDR_ECS_FUSED");
-    e->fused_ok = !(nf && *nf == '1') && (W >= 2048 || (ff && *ff == '1')) &&
-                  need <= (long long)fused_per_sm * prop.multiProcessorCount;
+    e->all_resident = need <= (long long)fused_per_sm * prop.multiProcessorCount && !(nf && *nf == '1');
+    e->fused_ok = !(nf && *nf == '1') && (W >= 2048 || (ff && *ff == '1')) && e->all_resident;
+    const char *nb = getenv("MDR_ECS_NO_BATCH");
+    e->batch_ok = !(nb && *nb == '1');
     e->built = true;
     e->exports_dirty = true;
     return MDR_OK;
@@ -1043,6 +1057,32 @@ int32_t mdr_ecs_step_async(mdr_ecs *e, int32_t num_steps)
             if (!e->host.exports[s].fixed) return true;
         return false;
     }();
+    // A batch of n > 1 steps without a host-visible point between them: the n walks of a world's graph run inside
+    // ONE launch (the staged exports are copied in before and out after; the tables, row counts and id state of a
+    // world stay with its warp). Same results as n single steps, bit for bit (tests/test_ecs_gpu.py). Not for graphs
+    // with a physics node (a launch boundary) or a user-instantiated megakernel (its launcher takes one step).
+    bool has_physics_node = false;
+    for (int ni = 0; ni < e->host.num_nodes; ni++) has_physics_node = has_physics_node || e->host.node[ni].kind == kNodePhysics;
+    if (num_steps > 1 && e->batch_ok && !e->launcher && !has_physics_node) {
+        if (!extend) REQ_CUDA(cudaEventRecord(e->ev0, e->stream));
+        const int W = e->host.num_worlds, N = e->host.num_nodes;
+        if (staged && e->all_resident) {
+            e->fused_kernel<<<(W + kWarpsPerBlock - 1) / kWarpsPerBlock, 32 * kWarpsPerBlock, 0, e->stream>>>(e->dev, 0, N, e->grid_bar, num_steps);
+        } else {
+            if (staged) ecsExportCopy<<<(W + 7) / 8, 256, 0, e->stream>>>(e->dev, 0);
+            e->step_kernel<<<e->blocks, 32 * kWarpsPerBlock, 0, e->stream>>>(e->dev, 0, N, num_steps);
+            if (staged) {
+                launchExportOffsets(e->dev, e->host.num_exports, W, e->stream);
+                ecsExportCopy<<<(W + 7) / 8, 256, 0, e->stream>>>(e->dev, 1);
+            }
+        }
+        REQ_CUDA(cudaGetLastError());
+        REQ_CUDA(cudaEventRecord(e->ev1, e->stream));
+        e->timing_open = true;
+        e->pending_steps = (extend ? e->pending_steps : 0) + num_steps;
+        e->last_call_launches = staged && !e->all_resident ? 4 : 1;
+        return MDR_OK;
+    }
     if (!e->graph) {
         // MWCudaExecutor's run graph (src/mw/cuda_exec.cpp:1519-1690):
         // exportCopyIn -> megakernel -> exportBlockSums -> exportCopyOut
@@ -1054,7 +1094,7 @@ int32_t mdr_ecs_step_async(mdr_ecs *e, int32_t num_steps)
         e->fused_in_graph = fused;
         if (fused) {
             const int blocks = (e->host.num_worlds + kWarpsPerBlock - 1) / kWarpsPerBlock;
-            e->fused_kernel<<<blocks, 32 * kWarpsPerBlock, 0, e->stream>>>(e->dev, 0, e->host.num_nodes, e->grid_bar);
+            e->fused_kernel<<<blocks, 32 * kWarpsPerBlock, 0, e->stream>>>(e->dev, 0, e->host.num_nodes, e->grid_bar, 1);
         }
         if (staged && !fused) ecsExportCopy<<<(e->host.num_worlds + 7) / 8, 256, 0, e->stream>>>(e->dev, 0);
         // The megakernel walks maximal runs of in-kernel nodes; a physics node is a launch of the
@@ -1067,7 +1107,7 @@ int32_t mdr_ecs_step_async(mdr_ecs *e, int32_t num_steps)
                 const int32_t r = e->launcher(e->dev, first, last, e->host.num_worlds, (void *)e->stream, e->launcher_user);
                 if (r != MDR_OK) rc_launch = r;
             } else {
-                e->step_kernel<<<e->blocks, 32 * kWarpsPerBlock, 0, e->stream>>>(e->dev, first, last);
+                e->step_kernel<<<e->blocks, 32 * kWarpsPerBlock, 0, e->stream>>>(e->dev, first, last, 1);
             }
         };
         int first = fused ? e->host.num_nodes : 0;
@@ -1093,8 +1133,11 @@ int32_t mdr_ecs_step_async(mdr_ecs *e, int32_t num_steps)
     REQ_CUDA(cudaEventRecord(e->ev1, e->stream));
     e->timing_open = true;
     e->pending_steps = (extend ? e->pending_steps : 0) + num_steps;
+    e->last_call_launches = num_steps * mdr_ecs_launches_per_step(e);
     return MDR_OK;
 }
+
+int32_t mdr_ecs_last_launches(mdr_ecs *e) { return e ? e->last_call_launches : MDR_EINVAL; }
 
 int32_t mdr_ecs_sync(mdr_ecs *e)
 {

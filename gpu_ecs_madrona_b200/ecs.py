@@ -51,7 +51,7 @@ def _lib():
         lib.mdr_ecs_read_column.argtypes = [vp, i32, i32, i32, vp]
         lib.mdr_ecs_row_counts.argtypes = [vp, i32, vp]
         for name in ("mdr_ecs_num_archetypes", "mdr_ecs_id_capacity", "mdr_ecs_build", "mdr_ecs_sync",
-                     "mdr_ecs_launches_per_step"):
+                     "mdr_ecs_launches_per_step", "mdr_ecs_last_launches"):
             getattr(lib, name).argtypes = [vp]
         lib.mdr_ecs_num_columns.argtypes = [vp, i32]
         lib.mdr_ecs_column_bytes.argtypes = [vp, i32, i32]
@@ -239,6 +239,10 @@ class EcsRegistry:
 
     def launches_per_step(self):
         return self.lib.mdr_ecs_launches_per_step(self.h)
+
+    def last_launches(self):
+        """Kernels launched by the last run / run_async call (a call of n > 1 steps is one batch launch)."""
+        return self.lib.mdr_ecs_last_launches(self.h)
 
     def column_map(self, arch):
         """The archetype's perfect-hash column map (ColumnMap columnLookup of the reference): (keys[128], values[128])."""

@@ -688,17 +688,26 @@ __device__ inline void sortArchetype(Context &ctx, int arch, int key_col, bool r
 }
 
 // ------------------------------------------------------ world load / store --
-__device__ inline void loadWorld(Context &ctx, const EcsDev *E, WarpShared *ws, int world)
+// What one walk of the graph starts from besides the world's tables: no pending structural batch, lane turns at
+// zero. A warp that walks SEVERAL steps of its world between one loadWorld and one storeWorld (the batched step
+// kernels of csrc/ecs.cu) calls this before every walk after the first.
+__device__ __forceinline__ void beginStep(Context &ctx)
 {
-    const int lane = laneId();
-    ctx.E = E; ctx.ws = ws; ctx.world = world; ctx.world_id = (uint32_t)(E->first_world + world);
-    if (!ctx.archs) ctx.archs = E->arch;
     ctx.pend = 0u;
     ctx.serial = 0u;
     ctx.created = Entity { 0u, -1 };
     ctx.created_row = -1;
     __syncwarp();
-    if (lane == 0) { ws->tmp_used = E->tmp_used ? E->tmp_used[world] : 0; ws->done = 0u; }
+    if (laneId() == 0) ctx.ws->done = 0u;
+}
+
+__device__ inline void loadWorld(Context &ctx, const EcsDev *E, WarpShared *ws, int world)
+{
+    const int lane = laneId();
+    ctx.E = E; ctx.ws = ws; ctx.world = world; ctx.world_id = (uint32_t)(E->first_world + world);
+    if (!ctx.archs) ctx.archs = E->arch;
+    beginStep(ctx);
+    if (lane == 0) ws->tmp_used = E->tmp_used ? E->tmp_used[world] : 0;
     {
         const int a = lane / kTileCols, c = lane % kTileCols;      // 32 lanes = kTileArch x kTileCols entries
         char *ptr = nullptr;

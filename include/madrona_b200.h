@@ -380,6 +380,12 @@ void *mdr_ecs_stream(mdr_ecs *e);
 void *mdr_ecs_done_event(mdr_ecs *e);
 float mdr_ecs_step_ms(mdr_ecs *e, int32_t *steps);
 int32_t mdr_ecs_launches_per_step(mdr_ecs *e);
+/* Kernels the last mdr_ecs_step_async call launched. A call with num_steps > 1 is a BATCH: nothing on the host can
+ * see the state between its steps, so the num_steps walks of a world's graph run inside one launch (staged exports
+ * copied in once before, offsets + copy-out once after); results are those of num_steps single steps, bit for bit.
+ * Graphs with a physics node or a user-side megakernel keep one graph launch per step. MDR_ECS_NO_BATCH=1 (read at
+ * mdr_ecs_build) turns batches off. */
+int32_t mdr_ecs_last_launches(mdr_ecs *e);
 /* Archetype column map, SURVEY 8 row a2: StaticIntegerMap<128> (include/madrona/hashmap.hpp:26-58, hashmap.inl:
  * 14-74, src/common/hashmap.cpp:17-116), kept per archetype as `ColumnMap columnLookup` (state.hpp:245-293).
  * `mdr_static_map_build` (host) fills both 128-word storage arrays exactly as the reference's constructor does

@@ -322,3 +322,33 @@ def test_one_launch_step_equals_the_four_launch_graph(monkeypatch):
             assert np.array_equal(fused.export(s), plain.export(s)), (steps, s)
     fused.close()
     plain.close()
+
+
+@pytest.mark.parametrize("app,worlds,params", [
+    (A.APP_TASKGRAPH, 70, None),
+    (A.APP_FANOUT, 21, None),
+    (A.APP_FVS, 300, [10, 40]),
+])
+@pytest.mark.parametrize("no_fused", [False, True])
+def test_batched_steps_equal_single_steps(monkeypatch, app, worlds, params, no_fused):
+    """run(n > 1) walks a world's graph n times inside one launch (staged exports copied in once before, offsets and
+    copy-out once after). Against n single-step graph launches (MDR_ECS_NO_BATCH=1): every column, row counts, id
+    maps, staged exports -- with the one-launch kernel and with the four-launch form (MDR_ECS_NO_FUSED=1)."""
+    from gpu_ecs_madrona_b200.ecs import EcsExecutor
+    args = (app, worlds) if params is None else (app, worlds, params)
+    if no_fused:
+        monkeypatch.setenv("MDR_ECS_NO_FUSED", "1")
+    batch = EcsExecutor(*args)
+    monkeypatch.setenv("MDR_ECS_NO_BATCH", "1")
+    single = EcsExecutor(*args)
+    monkeypatch.delenv("MDR_ECS_NO_BATCH")
+    staged = single.launches_per_step() > 1 or batch.launches_per_step() > 1
+    for steps in (5, 1, 33):
+        batch.run(steps)
+        single.run(steps)
+        if steps > 1:
+            assert batch.last_launches() in (1, 4) and batch.last_launches() == (4 if staged and no_fused else 1)
+            assert single.last_launches() == steps * single.launches_per_step()
+        U.assert_same(gpu_snapshot(batch, app), gpu_snapshot(single, app), app, f"after run({steps}) ")
+    batch.close()
+    single.close()
