@@ -45,11 +45,35 @@ physStepKernel(const __grid_constant__ StepParams p, int threads_per_world, int 
     __syncthreads();
     // Every slot of the block walks the same barriers: the trip count depends on
     // the block index only; a slot past the last world idles through them.
+#ifndef MDR_STATIC_WORLDS
+    // World groups handed out by a counter instead of strided over the grid: a block that drew light worlds (or
+    // shares its SM with a block that did) takes more of them, so the launch ends when the work ends, not when the
+    // unluckiest block does: +5.5 % on collisions-64 (profiles/r02_summary.md section 8). The first group of a block
+    // is its own index; the next one is drawn while the current one is stepped; the last block out resets the counter
+    // for the next launch (launches of one executor are ordered on a stream: they share the tables anyway). Which
+    // block steps a world does not change the world's result.
+    uint32_t *const work = p.work;
+    int base = first_world + blockIdx.x * slots;
+    while (base < end_world) {
+        if (threadIdx.x == 0) block_solve.next_base = first_world + (int)(gridDim.x + atomicAdd(work, 1u)) * slots;
+        const int w = base + slot;
+        v.active = w < end_world;
+        stepWorld<kJoints, kHullSlots, Layout>(ctx, v, p, v.active ? w : first_world, &group_level, bs, slot);
+        __syncthreads();
+        base = block_solve.next_base;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0 && atomicAdd(work + 1, 1u) == gridDim.x - 1) {
+        atomicExch(work, 0u);
+        atomicExch(work + 1, 0u);
+    }
+#else
     for (int base = first_world + blockIdx.x * slots; base < end_world; base += gridDim.x * slots) {
         const int w = base + slot;
         v.active = w < end_world;
         stepWorld<kJoints, kHullSlots, Layout>(ctx, v, p, v.active ? w : first_world, &group_level, bs, slot);
     }
+#endif
 }
 
 

@@ -121,6 +121,7 @@ struct StepParams {
     int32_t *world_pairs;         // [W] pairs found in the last step
     int32_t *world_contacts;      // [W] contacts of the last substep
     int32_t *error_flags;         // [1] bit 0: pair list overflow
+    uint32_t *work;               // [2] next world group of the running launch, blocks that have left it
     ProbeDev probe;
     const JointDev *joints;       // [W][joint_stride]; joint_stride 0: the batch has no joints
     const int32_t *joint_count;   // [W]

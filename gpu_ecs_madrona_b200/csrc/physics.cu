@@ -256,6 +256,7 @@ static int32_t createImpl(const mdr_phys_config *cfg, const mdr_object *objs, in
     sp.world_contacts = p->dalloc<int32_t>(W);
     p->d_err = p->dalloc<int32_t>(1);
     sp.error_flags = p->d_err;
+    sp.work = p->dalloc<uint32_t>(2);
     sp.probe.world = -1;
 #ifdef MDR_PHASE_CLOCKS
     sp.phase_clocks = p->dalloc<unsigned long long>(32);
