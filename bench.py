@@ -250,7 +250,8 @@ def run_ours(args):
     ex.run_async(args.steps)
     ex.sync()
     wall = time.perf_counter() - t0
-    kms, launches = ex.kernel_ms()           # CUDA events on the executor's stream around the K launches
+    kms, launches = ex.kernel_ms()           # CUDA events on the executor's stream around the K steps
+    gpu_launches = ex.last_launches()        # one call of K steps = one batch launch of the step kernel
     clocks = sampler.stop()
     assert launches == args.steps
     dev_ms = kms * launches
@@ -260,6 +261,19 @@ def run_ours(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         dev_ms = float(t.item())
     value = world * W * args.steps / (dev_ms * 1e-3)
+    # the same K steps as K calls of one step each (one launch per step, the form a caller that looks at the state
+    # after every step uses); reported beside the batch, not instead of it
+    for _ in range(args.steps):
+        ex.run_async(1)
+    ex.sync()
+    kms1, n1 = ex.kernel_ms()
+    one_ms = kms1 * n1
+    if dist is not None:
+        t = torch.tensor([one_ms], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        one_ms = float(t.item())
+    one_step_per_call = {"value": world * W * n1 / (one_ms * 1e-3), "unit": UNIT, "ms_per_step": one_ms / n1,
+                         "gpu_launches": n1}
 
     # ---- end to end through the public API with host buffers ------------
     # A fresh executor on the same scene, so that the end-to-end figure covers the SAME step range
@@ -376,7 +390,8 @@ def run_ours(args):
                        "parallelism": f"worlds sharded over {world} GPU(s), no per-step communication",
                        "episode_stats_all_gather": episode},
             "mean_contacts_per_world": C, "mean_pairs_per_world": P,      # the regime the value was measured in
-            "gpu_launches": args.steps,
+            "gpu_launches": gpu_launches, "steps_per_launch": args.steps // max(gpu_launches, 1),
+            "one_step_per_call": one_step_per_call,
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d,
                     "d2h_bytes_per_step": d2h, "steps": e2e_steps, "finite": finite,
                     "pcie_gb_per_s_per_rank": (h2d + d2h) * e2e_steps / e2e_s / 1e9,

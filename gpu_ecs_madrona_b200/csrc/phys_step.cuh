@@ -23,7 +23,7 @@ struct BlockSolve {
     int32_t cnt[32];                  // per level (index 31: deeper than kDenseLevels)
     int32_t off[33];
     int32_t dense;
-    int32_t next_base;                // first world of the block's next group (dynamic world assignment, phys_kernel.cuh)
+    uint32_t next_task;               // the block's next task (phys_kernel.cuh)
     uint32_t level_any[2];            // per substep parity: bit lv set when a contact of level lv was emitted
     uint16_t items[kDenseItems];      // world slot << 10 | pair slot
     WorldView views[kDenseSlots];

@@ -121,7 +121,8 @@ struct StepParams {
     int32_t *world_pairs;         // [W] pairs found in the last step
     int32_t *world_contacts;      // [W] contacts of the last substep
     int32_t *error_flags;         // [1] bit 0: pair list overflow
-    uint32_t *work;               // [2] next world group of the running launch, blocks that have left it
+    uint32_t *work;               // [2] next task of the running launch, blocks that have left it
+    uint32_t *group_done;         // [W] batches only: steps (counted since creation) finished by each world group
     ProbeDev probe;
     const JointDev *joints;       // [W][joint_stride]; joint_stride 0: the batch has no joints
     const int32_t *joint_count;   // [W]
@@ -132,7 +133,7 @@ struct StepParams {
 #endif
 };
 
-enum { MDR_ERR_PAIR_OVERFLOW = 1, MDR_ERR_BAD_OBJECT = 2 };
+enum { MDR_ERR_PAIR_OVERFLOW = 1, MDR_ERR_BAD_OBJECT = 2, MDR_ERR_STALL = 4 };
 
 // Caps of the hull-hull path: 32 vertices / faces per slot of the warp SAT (phys_sat_warp.cuh), two slots in the
 // big-hull kernel variant; also the per-thread arrays of the host emulation.

@@ -222,6 +222,28 @@ MDR_HD void fetchWords(const BlockCtx &c, float *dst, const float *src, int word
     copyWords(c, dst, src, words);
 #endif
 }
+// The same for the columns the step itself writes (poses, velocities, slot boxes, hints): read at L2 (.cg). Inside a
+// batch of steps in one launch (phys_kernel.cuh) the previous step of this world may have run on another SM, and an
+// L1 line this SM kept from an even earlier step would be stale; L2 is the point of coherence. 16-byte copies when
+// the tile starts on a 16-byte boundary (a row stride that is a multiple of 4 rows: every tile of the library's own
+// tables), a quarter of the copy instructions; the last few words, and unaligned tiles, through registers.
+MDR_HD void fetchWordsL2(const BlockCtx &c, float *dst, const float *src, int words)
+{
+#if defined(__CUDA_ARCH__)
+    int done = 0;
+    if ((reinterpret_cast<uintptr_t>(src) & 15u) == 0) {
+        const int chunks = words >> 2;
+        for (int i = c.tid(); i < chunks; i += c.nthreads()) {
+            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(dst + 4 * i)),
+                         "l"(src + 4 * i) : "memory");
+        }
+        done = chunks << 2;
+    }
+    for (int i = done + c.tid(); i < words; i += c.nthreads()) dst[i] = __ldcg(src + i);
+#else
+    copyWords(c, dst, src, words);
+#endif
+}
 MDR_HD void fetchWait()
 {
 #if defined(__CUDA_ARCH__)
@@ -272,14 +294,14 @@ MDR_HD void loadWorld(const BlockCtx &c, WorldView &v, const StepParams &p, int 
     const PhysTables &t = p.t;
     const size_t r0 = (size_t)w * t.stride;
     const int n = v.n;
-    fetchWords(c, v.pos, t.pos + 3 * r0, 3 * n);
-    fetchWords(c, v.rot, t.rot + 4 * r0, 4 * n);
-    fetchWords(c, v.vel, t.vel + 6 * r0, 6 * n);
     fetchWords(c, v.scale, t.scale + 3 * r0, 3 * n);
-    fetchWords(c, v.slot, t.slot_box + 6 * r0, 6 * n);
+    fetchWordsL2(c, v.pos, t.pos + 3 * r0, 3 * n);
+    fetchWordsL2(c, v.rot, t.rot + 4 * r0, 4 * n);
+    fetchWordsL2(c, v.vel, t.vel + 6 * r0, 6 * n);
+    fetchWordsL2(c, v.slot, t.slot_box + 6 * r0, 6 * n);
     if (p.sat_hint) {
         const int hw = (p.max_pairs + 3) / 4;
-        fetchWords(c, reinterpret_cast<float *>(v.hint), reinterpret_cast<const float *>(p.sat_hint + (size_t)w * hw * 4), hw);
+        fetchWordsL2(c, reinterpret_cast<float *>(v.hint), reinterpret_cast<const float *>(p.sat_hint + (size_t)w * hw * 4), hw);
     }
     for (int i = c.tid(); i < n; i += c.nthreads()) {
         // four independent loads, then the object table (cached)

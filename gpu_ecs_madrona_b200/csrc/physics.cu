@@ -94,7 +94,10 @@ struct mdr_phys {
     char *ray_buf = nullptr;
     size_t ray_buf_bytes = 0;
     bool timing_open = false;
-    int pending_launches = 0;
+    int pending_launches = 0;                // steps (or world ranges of step_io) between ev0 and ev1
+    int last_call_launches = 0;              // step kernels the last mdr_phys_step_async call launched
+    bool batch_ok = true;                    // n > 1 steps of one call run as one launch (MDR_PHYS_NO_BATCH=1: n launches)
+    uint32_t batch_step_base = 0;            // steps done inside batches so far: the epoch of StepParams::group_done
     double timed_ms = 0.0;
     int timed_launches = 0;
     bool external_tables = false;            // columns and row counts belong to an ECS archetype
@@ -257,6 +260,7 @@ static int32_t createImpl(const mdr_phys_config *cfg, const mdr_object *objs, in
     p->d_err = p->dalloc<int32_t>(1);
     sp.error_flags = p->d_err;
     sp.work = p->dalloc<uint32_t>(2);
+    sp.group_done = p->dalloc<uint32_t>(W);
     sp.probe.world = -1;
 #ifdef MDR_PHASE_CLOCKS
     sp.phase_clocks = p->dalloc<unsigned long long>(32);
@@ -272,6 +276,7 @@ static int32_t createImpl(const mdr_phys_config *cfg, const mdr_object *objs, in
     int wpb = envInt("MDR_WORLDS_PER_BLOCK", cfg->worlds_per_block > 0 ? cfg->worlds_per_block : 4);
     int want_min_blocks = envInt("MDR_MIN_BLOCKS", 0);
     p->lockstep = envInt("MDR_LOCKSTEP", 1);
+    p->batch_ok = !envInt("MDR_PHYS_NO_BATCH", 0);
     if (!p->lockstep && wpb > 15) wpb = 15;     // one named barrier per world slot
     if (tpw < 32 || tpw % 32 || wpb < 1 || tpw * wpb > 1024) {
         fprintf(stderr, "madrona_b200: threads per world must be a multiple of 32 and threads x worlds per block <= 1024\n");
@@ -353,7 +358,7 @@ int32_t mdrPhysEnqueueStep(mdr_phys *p, cudaStream_t stream)
     const int W = p->cfg.num_worlds;
     launchRebuild(p->params, W, stream);
     p->kernel<<<p->blocks, p->threads, p->smem_bytes, stream>>>(
-        p->params, p->threads_per_world, (int)p->slot_bytes, p->overflow_per_slot, p->lockstep, 0, W);
+        p->params, p->threads_per_world, (int)p->slot_bytes, p->overflow_per_slot, p->lockstep, 0, W, 1, 0u);
     return cudaGetLastError() == cudaSuccess ? MDR_OK : MDR_ESTATE;
 }
 
@@ -673,10 +678,21 @@ int32_t mdr_phys_step_async(mdr_phys *p, int32_t num_steps)
         p->maybe_rebuild = false;
     }
     if (!extend) REQ_CUDA(cudaEventRecord(p->ev0, p->stream));
-    for (int s = 0; s < num_steps; s++) {
+    // A call of n > 1 steps is a batch nobody observes in between: ONE launch walks (step, world group) tasks in
+    // step order, a group's step waiting for its previous one (phys_kernel.cuh). MDR_PHYS_NO_BATCH=1: n launches.
+    if (num_steps > 1 && p->batch_ok) {
         p->kernel<<<p->blocks, p->threads, p->smem_bytes, p->stream>>>(
             p->params, p->threads_per_world, (int)p->slot_bytes, p->overflow_per_slot, p->lockstep,
-            0, p->cfg.num_worlds);
+            0, p->cfg.num_worlds, num_steps, p->batch_step_base);
+        p->batch_step_base += (uint32_t)num_steps;
+        p->last_call_launches = 1;
+    } else {
+        for (int s = 0; s < num_steps; s++) {
+            p->kernel<<<p->blocks, p->threads, p->smem_bytes, p->stream>>>(
+                p->params, p->threads_per_world, (int)p->slot_bytes, p->overflow_per_slot, p->lockstep,
+                0, p->cfg.num_worlds, 1, 0u);
+        }
+        p->last_call_launches = num_steps;
     }
     REQ_CUDA(cudaGetLastError());
     REQ_CUDA(cudaEventRecord(p->ev1, p->stream));
@@ -767,7 +783,7 @@ int32_t mdr_phys_step_io_async(mdr_phys *p, int32_t num_in, const int32_t *in_co
         long long grid = ((long long)(end - first) + p->worlds_per_block - 1) / p->worlds_per_block;
         if (grid > p->blocks) grid = p->blocks;
         p->kernel<<<(int)grid, p->threads, p->smem_bytes, p->stream>>>(
-            p->params, p->threads_per_world, (int)p->slot_bytes, p->overflow_per_slot, p->lockstep, first, end);
+            p->params, p->threads_per_world, (int)p->slot_bytes, p->overflow_per_slot, p->lockstep, first, end, 1, 0u);
         REQ_CUDA(cudaGetLastError());
         REQ_CUDA(cudaEventRecord(p->io_events[2 * r + 1], p->stream));
         REQ_CUDA(cudaStreamWaitEvent(p->io_out, p->io_events[2 * r + 1], 0));
@@ -796,6 +812,7 @@ int32_t mdr_phys_sync(mdr_phys *p)
     int32_t err = 0;
     REQ_CUDA(cudaMemcpy(&err, p->d_err, 4, cudaMemcpyDeviceToHost));
     if (err) REQ_CUDA(cudaMemset(p->d_err, 0, 4));
+    if (err & MDR_ERR_STALL) return MDR_ESTATE;            // a batch task gave up waiting for its world's previous step
     if (err & MDR_ERR_BAD_OBJECT) return MDR_EINVAL;       // an ObjectID outside the object table reached the step
     if (err & MDR_ERR_PAIR_OVERFLOW) return MDR_EOVERFLOW;
     return MDR_OK;
@@ -1026,6 +1043,8 @@ int32_t mdr_phys_launch_info(mdr_phys *p, int32_t info[6])
     info[4] = p->threads_per_world; info[5] = p->worlds_per_block;
     return MDR_OK;
 }
+
+int32_t mdr_phys_last_launches(mdr_phys *p) { return p ? p->last_call_launches : MDR_EINVAL; }
 
 float mdr_phys_kernel_ms(mdr_phys *p, int32_t *launches)
 {

@@ -103,6 +103,8 @@ def bind(lib):
         lib.mdr_phys_launch_info.argtypes = [vp, vp]
         lib.mdr_phys_kernel_ms.argtypes = [vp, vp]
         lib.mdr_phys_kernel_ms.restype = C.c_float
+        if hasattr(lib, "mdr_phys_last_launches"):
+            lib.mdr_phys_last_launches.argtypes = [vp]
         lib.mdr_phys_row_stride.argtypes = [vp]
         lib.mdr_phys_write_column_raw_async.argtypes = [vp, i32, vp]
         lib.mdr_phys_read_column_raw_async.argtypes = [vp, i32, vp]
@@ -407,6 +409,11 @@ class PhysExecutor:
                     worlds_per_block=int(info[5]))
 
     def kernel_ms(self):
+        """(ms per step, steps) timed on the device since the last call."""
         n = C.c_int32(0)
         ms = self.lib.mdr_phys_kernel_ms(self.h, C.byref(n))
         return float(ms), int(n.value)
+
+    def last_launches(self):
+        """Step kernels launched by the last run / run_async call (a call of n > 1 steps is one batch launch)."""
+        return int(self.lib.mdr_phys_last_launches(self.h))

@@ -267,9 +267,14 @@ int32_t mdr_stream_wait_event(void *stream, void *event);
  * [2] dynamic shared memory bytes per block, [3] resident blocks per SM,
  * [4] threads per world, [5] worlds per block. */
 int32_t mdr_phys_launch_info(mdr_phys *p, int32_t info[6]);
-/* Average device time of the step kernel, in ms, over the launches since the
- * last call (CUDA events on the executor's stream); <0 if none were timed. */
+/* Average device time of a step, in ms, over the steps since the last call
+ * (CUDA events on the executor's stream); <0 if none were timed. `launches`
+ * receives that number of steps (world ranges for mdr_phys_step_io_async). */
 float mdr_phys_kernel_ms(mdr_phys *p, int32_t *launches);
+/* Step kernels the last mdr_phys_step_async call launched. A call of n > 1 steps is a BATCH: the host cannot see the
+ * state between its steps, so one launch runs all n (a world's step s starts when its step s - 1 is done, wherever
+ * that ran); results are those of n single steps, bit for bit. MDR_PHYS_NO_BATCH=1 (read at creation): n launches. */
+int32_t mdr_phys_last_launches(mdr_phys *p);
 
 /* ---- ECS state layer + task graph -------------------------------------------
  * Stands in for the registration / graph-building / executor surface a world

@@ -123,6 +123,31 @@ def test_cuda_matches_defined_reference_100_steps(cuda_lib, ref_oracle, name):
         assert_state_equal(e.state(), d.state(), None, f"{name} step {st + 10}")
 
 
+@pytest.mark.parametrize("name", ["collisions64", "tumble24", "jointed", "few_worlds"])
+def test_cuda_batched_steps_equal_single_steps(cuda_lib, monkeypatch, name):
+    """run(n > 1) is ONE launch that walks (step, world group) tasks, a group's step waiting for its previous one
+    wherever that ran (phys_kernel.cuh). Against n launches of one step (MDR_PHYS_NO_BATCH=1): every column."""
+    make = {"collisions64": lambda: scenes.collisions64(1500), "tumble24": lambda: scenes.tumble(700),
+            "jointed": lambda: scenes.jointed(333), "few_worlds": lambda: scenes.collisions64(3)}[name]
+    batch = phys.PhysExecutor(make())
+    monkeypatch.setenv("MDR_PHYS_NO_BATCH", "1")
+    single = phys.PhysExecutor(make())
+    monkeypatch.delenv("MDR_PHYS_NO_BATCH")
+    for steps in (7, 1, 40):
+        batch.run(steps)
+        single.run(steps)
+        assert batch.last_launches() == 1 and single.last_launches() == steps
+        for col in (phys.COL_POSITION, phys.COL_ROTATION, phys.COL_VELOCITY, phys.COL_SUBSTEP_PREV,
+                    phys.COL_PRESOLVE_POS, phys.COL_PRESOLVE_VEL):
+            assert np.array_equal(batch.read(col), single.read(col)), (steps, col)
+        for a, b in zip(batch.read_bvh(), single.read_bvh()):
+            assert np.array_equal(a.view(np.uint8), b.view(np.uint8)), steps
+        for a, b in zip(batch.stats(), single.stats()):
+            assert np.array_equal(a, b), steps
+    batch.close()
+    single.close()
+
+
 def test_cuda_ragged_and_empty_worlds(cuda_lib, port_oracle):
     full = scenes.tumble(6, num_bodies=15)
     rows = np.array([16, 9, 1, 0, 5, 16], np.int32)
