@@ -370,7 +370,8 @@ def run_ours(args):
         if os.path.exists(tpath):
             try:
                 tj = json.load(open(tpath))
-                traffic, traffic_src = tj.get("dram_bytes_per_launch"), "static: " + tj.get("source", "profiles/traffic.json")
+                # per STEP: the timed region is one launch of `steps` steps (gpu_launches), the capture one of 12
+                traffic, traffic_src = tj.get("dram_bytes_per_step"), "static: " + tj.get("source", "profiles/traffic.json")
             except Exception:
                 traffic = None
         base, _ = cpu_baseline(args.steps, args.warmup, preroll=args.preroll) if not args.no_cpu else ({}, 0)
@@ -399,7 +400,9 @@ def run_ours(args):
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
                          "algorithmic_bytes_per_world_step": A, "kernel": "physStepKernel",
-                         "kernel_ms": kms},
+                         "kernel_ms": kms,
+                         "per": "step: achieved = A x worlds / device ms per step, traffic = DRAM bytes per step; the timed "
+                                "launch holds steps_per_launch steps, so per launch both scale by that number"},
             "cpu_baseline": base,
             "clocks": clocks,
         }
