@@ -424,8 +424,9 @@ def main():
     ap.add_argument("--worlds-per-block", type=int, default=0)
     ap.add_argument("--smem-contacts", type=int, default=0, help="contact slots in shared memory (0: default)")
     ap.add_argument("--max-contacts", type=int, default=640, help="candidate-pair capacity per world (SURVEY 8d: 640)")
-    ap.add_argument("--io-chunks", type=int, default=6,
-                    help="world ranges the end-to-end step is pipelined over (1: copy, step, copy in sequence)")
+    ap.add_argument("--io-chunks", type=int, default=14,
+                    help="world ranges the end-to-end step is pipelined over (1: copy, step, copy in sequence; "
+                         "14 = one range per resident wave of 16384 worlds: the shortest exposed copy-out)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--preroll", type=int, default=PREROLL,
                     help="untimed steps before the warm-up, so that every --steps / --warmup pair times the settled regime")

@@ -88,7 +88,7 @@ struct mdr_phys {
     cudaStream_t stream = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     // mdr_phys_step_io: copy-in / copy-out streams and per-chunk events
-    cudaStream_t io_in = nullptr, io_out = nullptr;
+    cudaStream_t io_in = nullptr, io_out = nullptr, stream2 = nullptr;   // stream2: every other world range of step_io
     std::vector<cudaEvent_t> io_events;
     // mdr_phys_trace_rays: device staging of the host-side ray buffers
     char *ray_buf = nullptr;
@@ -96,6 +96,10 @@ struct mdr_phys {
     bool timing_open = false;
     int pending_launches = 0;                // steps (or world ranges of step_io) between ev0 and ev1
     int last_call_launches = 0;              // step kernels the last mdr_phys_step_async call launched
+    bool io_trace_on = false;                // MDR_PHYS_IO_TRACE=1
+    std::vector<cudaEvent_t> io_trace;
+    int io_trace_ranges = 0;
+    bool io_two_lanes = true;                // step_io: world ranges alternate between two streams (MDR_PHYS_IO_ONE_LANE=1: one)
     bool batch_ok = true;                    // n > 1 steps of one call run as one launch (MDR_PHYS_NO_BATCH=1: n launches)
     uint32_t batch_step_base = 0;            // steps done inside batches so far: the epoch of StepParams::group_done
     double timed_ms = 0.0;
@@ -259,7 +263,7 @@ static int32_t createImpl(const mdr_phys_config *cfg, const mdr_object *objs, in
     sp.world_contacts = p->dalloc<int32_t>(W);
     p->d_err = p->dalloc<int32_t>(1);
     sp.error_flags = p->d_err;
-    sp.work = p->dalloc<uint32_t>(2);
+    sp.work = p->dalloc<uint32_t>(4);
     sp.group_done = p->dalloc<uint32_t>(W);
     sp.probe.world = -1;
 #ifdef MDR_PHASE_CLOCKS
@@ -277,6 +281,8 @@ static int32_t createImpl(const mdr_phys_config *cfg, const mdr_object *objs, in
     int want_min_blocks = envInt("MDR_MIN_BLOCKS", 0);
     p->lockstep = envInt("MDR_LOCKSTEP", 1);
     p->batch_ok = !envInt("MDR_PHYS_NO_BATCH", 0);
+    p->io_two_lanes = !envInt("MDR_PHYS_IO_ONE_LANE", 0);
+    p->io_trace_on = envInt("MDR_PHYS_IO_TRACE", 0) != 0;
     if (!p->lockstep && wpb > 15) wpb = 15;     // one named barrier per world slot
     if (tpw < 32 || tpw % 32 || wpb < 1 || tpw * wpb > 1024) {
         fprintf(stderr, "madrona_b200: threads per world must be a multiple of 32 and threads x worlds per block <= 1024\n");
@@ -334,7 +340,8 @@ static int32_t createImpl(const mdr_phys_config *cfg, const mdr_object *objs, in
     if (grid > need) grid = need;
     p->blocks = (int)grid;
     p->overflow_per_slot = sp.max_pairs - sp.smem_contacts;
-    sp.overflow = p->dalloc<SolverContact>((size_t)p->blocks * wpb * (p->overflow_per_slot + 1), false);
+    // two sets: the world ranges of mdr_phys_step_io_async run on two streams, side by side at their ends
+    sp.overflow = p->dalloc<SolverContact>(2 * (size_t)p->blocks * wpb * (p->overflow_per_slot + 1), false);
     if (p->alloc_failed) {
         fprintf(stderr, "madrona_b200: %d worlds x %d bodies (%d contact slots) do not fit the device memory\n",
                 W, cfg->max_bodies_per_world, sp.max_pairs);
@@ -358,7 +365,7 @@ int32_t mdrPhysEnqueueStep(mdr_phys *p, cudaStream_t stream)
     const int W = p->cfg.num_worlds;
     launchRebuild(p->params, W, stream);
     p->kernel<<<p->blocks, p->threads, p->smem_bytes, stream>>>(
-        p->params, p->threads_per_world, (int)p->slot_bytes, p->overflow_per_slot, p->lockstep, 0, W, 1, 0u);
+        p->params, p->threads_per_world, (int)p->slot_bytes, p->overflow_per_slot, p->lockstep, 0, W, 1, 0u, 0);
     return cudaGetLastError() == cudaSuccess ? MDR_OK : MDR_ESTATE;
 }
 
@@ -391,7 +398,9 @@ void mdr_phys_destroy(mdr_phys *p)
     if (p->d_joint_count) cudaFree(p->d_joint_count);
     if (p->io_in) { cudaStreamSynchronize(p->io_in); cudaStreamDestroy(p->io_in); }
     if (p->io_out) { cudaStreamSynchronize(p->io_out); cudaStreamDestroy(p->io_out); }
+    if (p->stream2) { cudaStreamSynchronize(p->stream2); cudaStreamDestroy(p->stream2); }
     for (cudaEvent_t e : p->io_events) cudaEventDestroy(e);
+    for (cudaEvent_t e : p->io_trace) cudaEventDestroy(e);
     if (p->ev0) cudaEventDestroy(p->ev0);
     if (p->ev1) cudaEventDestroy(p->ev1);
     for (void *a : p->allocs) cudaFree(a);
@@ -683,14 +692,14 @@ int32_t mdr_phys_step_async(mdr_phys *p, int32_t num_steps)
     if (num_steps > 1 && p->batch_ok) {
         p->kernel<<<p->blocks, p->threads, p->smem_bytes, p->stream>>>(
             p->params, p->threads_per_world, (int)p->slot_bytes, p->overflow_per_slot, p->lockstep,
-            0, p->cfg.num_worlds, num_steps, p->batch_step_base);
+            0, p->cfg.num_worlds, num_steps, p->batch_step_base, 0);
         p->batch_step_base += (uint32_t)num_steps;
         p->last_call_launches = 1;
     } else {
         for (int s = 0; s < num_steps; s++) {
             p->kernel<<<p->blocks, p->threads, p->smem_bytes, p->stream>>>(
                 p->params, p->threads_per_world, (int)p->slot_bytes, p->overflow_per_slot, p->lockstep,
-                0, p->cfg.num_worlds, 1, 0u);
+                0, p->cfg.num_worlds, 1, 0u, 0);
         }
         p->last_call_launches = num_steps;
     }
@@ -742,22 +751,36 @@ int32_t mdr_phys_step_io_async(mdr_phys *p, int32_t num_in, const int32_t *in_co
     if (!p->io_in) {
         REQ_CUDA(cudaStreamCreateWithFlags(&p->io_in, cudaStreamNonBlocking));
         REQ_CUDA(cudaStreamCreateWithFlags(&p->io_out, cudaStreamNonBlocking));
+        REQ_CUDA(cudaStreamCreateWithFlags(&p->stream2, cudaStreamNonBlocking));
     }
-    while ((int)p->io_events.size() < 2 * ranges + 2) {
+    while ((int)p->io_events.size() < 2 * ranges + 5) {
         cudaEvent_t e;
         REQ_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
         p->io_events.push_back(e);
+    }
+    // A flagged BVH rebuild reads poses of EVERY world: on such a step (a reset) all inputs go in first and
+    // the rebuild follows them; the per-range overlap of copy-in and step is given up for that one step.
+    const bool inputs_first = p->maybe_rebuild;
+    REQ_CUDA(cudaEventRecord(p->ev0, p->stream));
+    // MDR_PHYS_IO_TRACE=1: device timestamps of every range -- copy-in landed, kernel
+    // done, copy-out done -- printed by the next mdr_phys_sync (profiles/io_probe.py)
+    const bool trace = p->io_trace_on;
+    if (trace) {
+        while ((int)p->io_trace.size() < 3 * ranges + 1) {
+            cudaEvent_t e;
+            REQ_CUDA(cudaEventCreate(&e));
+            p->io_trace.push_back(e);
+        }
+        p->io_trace_ranges = ranges;
+        REQ_CUDA(cudaEventRecord(p->io_trace[0], p->stream));
     }
     // the side streams start after everything already queued on the executor's stream
     cudaEvent_t start = p->io_events[2 * ranges], done = p->io_events[2 * ranges + 1];
     REQ_CUDA(cudaEventRecord(start, p->stream));
     REQ_CUDA(cudaStreamWaitEvent(p->io_in, start, 0));
     REQ_CUDA(cudaStreamWaitEvent(p->io_out, start, 0));
-    REQ_CUDA(cudaEventRecord(p->ev0, p->stream));
+    REQ_CUDA(cudaStreamWaitEvent(p->stream2, start, 0));
     const size_t stride = p->params.t.stride;
-    // A flagged BVH rebuild reads poses of EVERY world: on such a step (a reset) all inputs go in first and
-    // the rebuild follows them; the per-range overlap of copy-in and step is given up for that one step.
-    const bool inputs_first = p->maybe_rebuild;
     if (inputs_first) {
         for (int i = 0; i < num_in; i++) {
             const size_t bytes = (size_t)kColBytes[in_cols[i]] * stride * W;
@@ -768,7 +791,13 @@ int32_t mdr_phys_step_io_async(mdr_phys *p, int32_t num_in, const int32_t *in_co
         launchRebuild(p->params, W, p->stream);
         REQ_CUDA(cudaGetLastError());
         p->maybe_rebuild = false;
+        REQ_CUDA(cudaEventRecord(p->io_events[2 * ranges + 2], p->stream));
+        REQ_CUDA(cudaStreamWaitEvent(p->stream2, p->io_events[2 * ranges + 2], 0));
     }
+    // The ranges alternate between the executor's stream and a second one: a launch ends with blocks finishing within
+    // one group time of each other, and the next range's blocks (other worlds, nothing shared but the read-only
+    // tables) move into the freed SMs instead of waiting for the stragglers -- six launch tails were a fifth of the
+    // end-to-end step. Each of the two lanes has its own task counter and overflow contact slots (block_base).
     for (int r = 0; r < ranges; r++) {
         const int first = range_first[r], end = range_first[r + 1];
         if (end <= first) continue;
@@ -778,14 +807,19 @@ int32_t mdr_phys_step_io_async(mdr_phys *p, int32_t num_in, const int32_t *in_co
                                      (const char *)in_host[i] + row * first, row * (end - first),
                                      cudaMemcpyHostToDevice, p->io_in));
         }
+        const int lane = p->io_two_lanes ? (r & 1) : 0;
+        cudaStream_t ks = lane ? p->stream2 : p->stream;
         REQ_CUDA(cudaEventRecord(p->io_events[2 * r], p->io_in));
-        REQ_CUDA(cudaStreamWaitEvent(p->stream, p->io_events[2 * r], 0));
+        REQ_CUDA(cudaStreamWaitEvent(ks, p->io_events[2 * r], 0));
         long long grid = ((long long)(end - first) + p->worlds_per_block - 1) / p->worlds_per_block;
         if (grid > p->blocks) grid = p->blocks;
-        p->kernel<<<(int)grid, p->threads, p->smem_bytes, p->stream>>>(
-            p->params, p->threads_per_world, (int)p->slot_bytes, p->overflow_per_slot, p->lockstep, first, end, 1, 0u);
+        p->kernel<<<(int)grid, p->threads, p->smem_bytes, ks>>>(
+            p->params, p->threads_per_world, (int)p->slot_bytes, p->overflow_per_slot, p->lockstep, first, end, 1, 0u,
+            lane ? p->blocks : 0);
         REQ_CUDA(cudaGetLastError());
-        REQ_CUDA(cudaEventRecord(p->io_events[2 * r + 1], p->stream));
+        REQ_CUDA(cudaEventRecord(p->io_events[2 * r + 1], ks));
+        if (trace) REQ_CUDA(cudaEventRecord(p->io_trace[1 + 3 * r], p->io_in));
+        if (trace) REQ_CUDA(cudaEventRecord(p->io_trace[2 + 3 * r], ks));
         REQ_CUDA(cudaStreamWaitEvent(p->io_out, p->io_events[2 * r + 1], 0));
         for (int i = 0; i < num_out; i++) {
             const size_t row = (size_t)kColBytes[out_cols[i]] * stride;
@@ -793,10 +827,16 @@ int32_t mdr_phys_step_io_async(mdr_phys *p, int32_t num_in, const int32_t *in_co
                                      (const char *)*colSlot(p->params.t, out_cols[i]) + row * first,
                                      row * (end - first), cudaMemcpyDeviceToHost, p->io_out));
         }
+        if (trace) REQ_CUDA(cudaEventRecord(p->io_trace[3 + 3 * r], p->io_out));
     }
-    // mdr_phys_sync (the executor's stream) also covers the last copy-out
+    // mdr_phys_sync (the executor's stream) also covers the last copy-out; the copy-in stream joins through the
+    // kernels that waited for it, the second kernel stream through the copy-outs that waited for its kernels
     REQ_CUDA(cudaEventRecord(done, p->io_out));
     REQ_CUDA(cudaStreamWaitEvent(p->stream, done, 0));
+    REQ_CUDA(cudaEventRecord(p->io_events[2 * ranges + 3], p->io_in));       // every side stream joins the executor's
+    REQ_CUDA(cudaStreamWaitEvent(p->stream, p->io_events[2 * ranges + 3], 0));
+    REQ_CUDA(cudaEventRecord(p->io_events[2 * ranges + 4], p->stream2));
+    REQ_CUDA(cudaStreamWaitEvent(p->stream, p->io_events[2 * ranges + 4], 0));
     REQ_CUDA(cudaEventRecord(p->ev1, p->stream));
     p->timing_open = true;
     p->pending_launches = ranges;
@@ -809,6 +849,16 @@ int32_t mdr_phys_sync(mdr_phys *p)
     REQ_CUDA(cudaSetDevice(p->cfg.gpu_id));
     REQ_CUDA(cudaStreamSynchronize(p->stream));
     closeTiming(p);
+    if (p->io_trace_ranges > 0) {
+        fprintf(stderr, "[mdr io trace] range: copy-in landed / kernel done / copy-out done (ms after the call)\n");
+        for (int r = 0; r < p->io_trace_ranges; r++) {
+            float t[3] = { 0.f, 0.f, 0.f };
+            for (int k = 0; k < 3; k++) cudaEventElapsedTime(&t[k], p->io_trace[0], p->io_trace[1 + 3 * r + k]);
+            fprintf(stderr, "[mdr io trace] %2d: %.3f / %.3f / %.3f\n", r, t[0], t[1], t[2]);
+        }
+        cudaGetLastError();
+        p->io_trace_ranges = 0;
+    }
     int32_t err = 0;
     REQ_CUDA(cudaMemcpy(&err, p->d_err, 4, cudaMemcpyDeviceToHost));
     if (err) REQ_CUDA(cudaMemset(p->d_err, 0, 4));
