@@ -15,7 +15,7 @@ template <int kMaxThreads, int kMinBlocks, bool kJoints, int kHullSlots = 1, typ
 __global__ void __launch_bounds__(kMaxThreads, kMinBlocks)
 physStepKernel(const __grid_constant__ StepParams p, int threads_per_world, int slot_bytes,
                int overflow_per_slot, int lockstep, int first_world, int end_world, int steps, uint32_t step_base,
-               int block_base)
+               int block_base, int lane)
 {
     __shared__ int group_level;
     __shared__ BlockSolve block_solve;
@@ -37,8 +37,8 @@ physStepKernel(const __grid_constant__ StepParams p, int threads_per_world, int 
     } else {
         carveWorld(v, mdr_smem + (size_t)slot * slot_bytes, p.t.stride, p.max_pairs, p.smem_contacts);
     }
-    // block_base: 0, or the grid capacity for a launch that may run BESIDE another one of this executor (the world
-    // ranges of mdr_phys_step_io_async alternate between two streams): its own overflow slots and task counter
+    // lane, block_base = lane x grid capacity: a launch that may run BESIDE others of this executor (the world ranges
+    // of mdr_phys_step_io_async rotate over a few streams) has its own overflow slots and task counter
     v.overflow = p.overflow + ((size_t)(block_base + blockIdx.x) * slots + slot) * overflow_per_slot;
     // dense solver lanes need block-wide barriers, pair slots in 10 bits and a view per slot
     BlockSolve *bs = kFixed ? &block_solve
@@ -59,7 +59,7 @@ physStepKernel(const __grid_constant__ StepParams p, int threads_per_world, int 
     // of all groups, so it has long finished and the wait is one load. The idle tail of a launch (blocks finishing
     // within one group time of each other) is then paid once per batch instead of once per step. Deadlock-free:
     // tasks are drawn in increasing order by resident blocks, and a task waits only for a smaller one.
-    uint32_t *const work = p.work + (block_base ? 2 : 0);
+    uint32_t *const work = p.work + 2 * lane;
     const int groups = (end_world - first_world + slots - 1) / slots;
     const uint32_t total = (uint32_t)groups * (uint32_t)steps;
     uint32_t task = blockIdx.x;
@@ -93,7 +93,7 @@ physStepKernel(const __grid_constant__ StepParams p, int threads_per_world, int 
 }
 
 
-typedef void (*StepKernel)(const StepParams, int, int, int, int, int, int, int, uint32_t, int);
+typedef void (*StepKernel)(const StepParams, int, int, int, int, int, int, int, uint32_t, int, int);
 // {max block threads, min resident blocks}; fn_joints is the same kernel with the joint
 // solve compiled in (mdr_phys_set_joints), so that batches without joints do not carry it.
 struct KernelVariant {

@@ -121,7 +121,7 @@ struct StepParams {
     int32_t *world_pairs;         // [W] pairs found in the last step
     int32_t *world_contacts;      // [W] contacts of the last substep
     int32_t *error_flags;         // [1] bit 0: pair list overflow
-    uint32_t *work;               // [2][2] per concurrent launch: next task of the running launch, blocks that have left it
+    uint32_t *work;               // [kMaxLanes][2] per concurrent launch: next task of the running launch, blocks that have left it
     uint32_t *group_done;         // [W] batches only: steps (counted since creation) finished by each world group
     ProbeDev probe;
     const JointDev *joints;       // [W][joint_stride]; joint_stride 0: the batch has no joints
@@ -133,6 +133,7 @@ struct StepParams {
 #endif
 };
 
+constexpr int kMaxLanes = 4;       // launches of one executor that may run side by side (step_io world ranges)
 enum { MDR_ERR_PAIR_OVERFLOW = 1, MDR_ERR_BAD_OBJECT = 2, MDR_ERR_STALL = 4 };
 
 // Caps of the hull-hull path: 32 vertices / faces per slot of the warp SAT (phys_sat_warp.cuh), two slots in the

@@ -88,7 +88,9 @@ struct mdr_phys {
     cudaStream_t stream = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     // mdr_phys_step_io: copy-in / copy-out streams and per-chunk events
-    cudaStream_t io_in = nullptr, io_out = nullptr, stream2 = nullptr;   // stream2: every other world range of step_io
+    cudaStream_t io_in = nullptr, io_out = nullptr;
+    cudaStream_t lane_stream[kMaxLanes] = {};      // [0] = stream; the world ranges of step_io rotate over io_lanes of them
+    int io_lanes = 3;
     std::vector<cudaEvent_t> io_events;
     // mdr_phys_trace_rays: device staging of the host-side ray buffers
     char *ray_buf = nullptr;
@@ -99,7 +101,6 @@ struct mdr_phys {
     bool io_trace_on = false;                // MDR_PHYS_IO_TRACE=1
     std::vector<cudaEvent_t> io_trace;
     int io_trace_ranges = 0;
-    bool io_two_lanes = true;                // step_io: world ranges alternate between two streams (MDR_PHYS_IO_ONE_LANE=1: one)
     bool batch_ok = true;                    // n > 1 steps of one call run as one launch (MDR_PHYS_NO_BATCH=1: n launches)
     uint32_t batch_step_base = 0;            // steps done inside batches so far: the epoch of StepParams::group_done
     double timed_ms = 0.0;
@@ -263,7 +264,7 @@ static int32_t createImpl(const mdr_phys_config *cfg, const mdr_object *objs, in
     sp.world_contacts = p->dalloc<int32_t>(W);
     p->d_err = p->dalloc<int32_t>(1);
     sp.error_flags = p->d_err;
-    sp.work = p->dalloc<uint32_t>(4);
+    sp.work = p->dalloc<uint32_t>(2 * kMaxLanes);
     sp.group_done = p->dalloc<uint32_t>(W);
     sp.probe.world = -1;
 #ifdef MDR_PHASE_CLOCKS
@@ -281,7 +282,9 @@ static int32_t createImpl(const mdr_phys_config *cfg, const mdr_object *objs, in
     int want_min_blocks = envInt("MDR_MIN_BLOCKS", 0);
     p->lockstep = envInt("MDR_LOCKSTEP", 1);
     p->batch_ok = !envInt("MDR_PHYS_NO_BATCH", 0);
-    p->io_two_lanes = !envInt("MDR_PHYS_IO_ONE_LANE", 0);
+    p->io_lanes = envInt("MDR_PHYS_IO_LANES", 3);
+    if (p->io_lanes < 1) p->io_lanes = 1;
+    if (p->io_lanes > kMaxLanes) p->io_lanes = kMaxLanes;
     p->io_trace_on = envInt("MDR_PHYS_IO_TRACE", 0) != 0;
     if (!p->lockstep && wpb > 15) wpb = 15;     // one named barrier per world slot
     if (tpw < 32 || tpw % 32 || wpb < 1 || tpw * wpb > 1024) {
@@ -340,8 +343,8 @@ static int32_t createImpl(const mdr_phys_config *cfg, const mdr_object *objs, in
     if (grid > need) grid = need;
     p->blocks = (int)grid;
     p->overflow_per_slot = sp.max_pairs - sp.smem_contacts;
-    // two sets: the world ranges of mdr_phys_step_io_async run on two streams, side by side at their ends
-    sp.overflow = p->dalloc<SolverContact>(2 * (size_t)p->blocks * wpb * (p->overflow_per_slot + 1), false);
+    // one set per lane: the world ranges of mdr_phys_step_io_async run on a few streams, side by side at their ends
+    sp.overflow = p->dalloc<SolverContact>((size_t)p->io_lanes * p->blocks * wpb * (p->overflow_per_slot + 1), false);
     if (p->alloc_failed) {
         fprintf(stderr, "madrona_b200: %d worlds x %d bodies (%d contact slots) do not fit the device memory\n",
                 W, cfg->max_bodies_per_world, sp.max_pairs);
@@ -365,7 +368,7 @@ int32_t mdrPhysEnqueueStep(mdr_phys *p, cudaStream_t stream)
     const int W = p->cfg.num_worlds;
     launchRebuild(p->params, W, stream);
     p->kernel<<<p->blocks, p->threads, p->smem_bytes, stream>>>(
-        p->params, p->threads_per_world, (int)p->slot_bytes, p->overflow_per_slot, p->lockstep, 0, W, 1, 0u, 0);
+        p->params, p->threads_per_world, (int)p->slot_bytes, p->overflow_per_slot, p->lockstep, 0, W, 1, 0u, 0, 0);
     return cudaGetLastError() == cudaSuccess ? MDR_OK : MDR_ESTATE;
 }
 
@@ -398,7 +401,7 @@ void mdr_phys_destroy(mdr_phys *p)
     if (p->d_joint_count) cudaFree(p->d_joint_count);
     if (p->io_in) { cudaStreamSynchronize(p->io_in); cudaStreamDestroy(p->io_in); }
     if (p->io_out) { cudaStreamSynchronize(p->io_out); cudaStreamDestroy(p->io_out); }
-    if (p->stream2) { cudaStreamSynchronize(p->stream2); cudaStreamDestroy(p->stream2); }
+    for (int l = 1; l < kMaxLanes; l++) if (p->lane_stream[l]) { cudaStreamSynchronize(p->lane_stream[l]); cudaStreamDestroy(p->lane_stream[l]); }
     for (cudaEvent_t e : p->io_events) cudaEventDestroy(e);
     for (cudaEvent_t e : p->io_trace) cudaEventDestroy(e);
     if (p->ev0) cudaEventDestroy(p->ev0);
@@ -692,14 +695,14 @@ int32_t mdr_phys_step_async(mdr_phys *p, int32_t num_steps)
     if (num_steps > 1 && p->batch_ok) {
         p->kernel<<<p->blocks, p->threads, p->smem_bytes, p->stream>>>(
             p->params, p->threads_per_world, (int)p->slot_bytes, p->overflow_per_slot, p->lockstep,
-            0, p->cfg.num_worlds, num_steps, p->batch_step_base, 0);
+            0, p->cfg.num_worlds, num_steps, p->batch_step_base, 0, 0);
         p->batch_step_base += (uint32_t)num_steps;
         p->last_call_launches = 1;
     } else {
         for (int s = 0; s < num_steps; s++) {
             p->kernel<<<p->blocks, p->threads, p->smem_bytes, p->stream>>>(
                 p->params, p->threads_per_world, (int)p->slot_bytes, p->overflow_per_slot, p->lockstep,
-                0, p->cfg.num_worlds, 1, 0u, 0);
+                0, p->cfg.num_worlds, 1, 0u, 0, 0);
         }
         p->last_call_launches = num_steps;
     }
@@ -751,9 +754,10 @@ int32_t mdr_phys_step_io_async(mdr_phys *p, int32_t num_in, const int32_t *in_co
     if (!p->io_in) {
         REQ_CUDA(cudaStreamCreateWithFlags(&p->io_in, cudaStreamNonBlocking));
         REQ_CUDA(cudaStreamCreateWithFlags(&p->io_out, cudaStreamNonBlocking));
-        REQ_CUDA(cudaStreamCreateWithFlags(&p->stream2, cudaStreamNonBlocking));
+        p->lane_stream[0] = p->stream;
+        for (int l = 1; l < p->io_lanes; l++) REQ_CUDA(cudaStreamCreateWithFlags(&p->lane_stream[l], cudaStreamNonBlocking));
     }
-    while ((int)p->io_events.size() < 2 * ranges + 5) {
+    while ((int)p->io_events.size() < 2 * ranges + 4 + kMaxLanes) {
         cudaEvent_t e;
         REQ_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
         p->io_events.push_back(e);
@@ -779,7 +783,7 @@ int32_t mdr_phys_step_io_async(mdr_phys *p, int32_t num_in, const int32_t *in_co
     REQ_CUDA(cudaEventRecord(start, p->stream));
     REQ_CUDA(cudaStreamWaitEvent(p->io_in, start, 0));
     REQ_CUDA(cudaStreamWaitEvent(p->io_out, start, 0));
-    REQ_CUDA(cudaStreamWaitEvent(p->stream2, start, 0));
+    for (int l = 1; l < p->io_lanes; l++) REQ_CUDA(cudaStreamWaitEvent(p->lane_stream[l], start, 0));
     const size_t stride = p->params.t.stride;
     if (inputs_first) {
         for (int i = 0; i < num_in; i++) {
@@ -792,12 +796,12 @@ int32_t mdr_phys_step_io_async(mdr_phys *p, int32_t num_in, const int32_t *in_co
         REQ_CUDA(cudaGetLastError());
         p->maybe_rebuild = false;
         REQ_CUDA(cudaEventRecord(p->io_events[2 * ranges + 2], p->stream));
-        REQ_CUDA(cudaStreamWaitEvent(p->stream2, p->io_events[2 * ranges + 2], 0));
+        for (int l = 1; l < p->io_lanes; l++) REQ_CUDA(cudaStreamWaitEvent(p->lane_stream[l], p->io_events[2 * ranges + 2], 0));
     }
-    // The ranges alternate between the executor's stream and a second one: a launch ends with blocks finishing within
-    // one group time of each other, and the next range's blocks (other worlds, nothing shared but the read-only
+    // The ranges rotate over io_lanes streams (the executor's own first): a launch ends with blocks finishing within
+    // one group time of each other, and the next ranges' blocks (other worlds, nothing shared but the read-only
     // tables) move into the freed SMs instead of waiting for the stragglers -- six launch tails were a fifth of the
-    // end-to-end step. Each of the two lanes has its own task counter and overflow contact slots (block_base).
+    // end-to-end step. Each lane has its own task counter and overflow contact slots (lane, block_base).
     for (int r = 0; r < ranges; r++) {
         const int first = range_first[r], end = range_first[r + 1];
         if (end <= first) continue;
@@ -807,15 +811,15 @@ int32_t mdr_phys_step_io_async(mdr_phys *p, int32_t num_in, const int32_t *in_co
                                      (const char *)in_host[i] + row * first, row * (end - first),
                                      cudaMemcpyHostToDevice, p->io_in));
         }
-        const int lane = p->io_two_lanes ? (r & 1) : 0;
-        cudaStream_t ks = lane ? p->stream2 : p->stream;
+        const int lane = r % p->io_lanes;
+        cudaStream_t ks = p->lane_stream[lane];
         REQ_CUDA(cudaEventRecord(p->io_events[2 * r], p->io_in));
         REQ_CUDA(cudaStreamWaitEvent(ks, p->io_events[2 * r], 0));
         long long grid = ((long long)(end - first) + p->worlds_per_block - 1) / p->worlds_per_block;
         if (grid > p->blocks) grid = p->blocks;
         p->kernel<<<(int)grid, p->threads, p->smem_bytes, ks>>>(
             p->params, p->threads_per_world, (int)p->slot_bytes, p->overflow_per_slot, p->lockstep, first, end, 1, 0u,
-            lane ? p->blocks : 0);
+            lane * p->blocks, lane);
         REQ_CUDA(cudaGetLastError());
         REQ_CUDA(cudaEventRecord(p->io_events[2 * r + 1], ks));
         if (trace) REQ_CUDA(cudaEventRecord(p->io_trace[1 + 3 * r], p->io_in));
@@ -835,8 +839,10 @@ int32_t mdr_phys_step_io_async(mdr_phys *p, int32_t num_in, const int32_t *in_co
     REQ_CUDA(cudaStreamWaitEvent(p->stream, done, 0));
     REQ_CUDA(cudaEventRecord(p->io_events[2 * ranges + 3], p->io_in));       // every side stream joins the executor's
     REQ_CUDA(cudaStreamWaitEvent(p->stream, p->io_events[2 * ranges + 3], 0));
-    REQ_CUDA(cudaEventRecord(p->io_events[2 * ranges + 4], p->stream2));
-    REQ_CUDA(cudaStreamWaitEvent(p->stream, p->io_events[2 * ranges + 4], 0));
+    for (int l = 1; l < p->io_lanes; l++) {
+        REQ_CUDA(cudaEventRecord(p->io_events[2 * ranges + 3 + l], p->lane_stream[l]));
+        REQ_CUDA(cudaStreamWaitEvent(p->stream, p->io_events[2 * ranges + 3 + l], 0));
+    }
     REQ_CUDA(cudaEventRecord(p->ev1, p->stream));
     p->timing_open = true;
     p->pending_launches = ranges;
