@@ -114,7 +114,9 @@ struct mdr_phys {
     int threads_per_world = 0, worlds_per_block = 0, lockstep = 1;
     size_t smem_bytes = 0, slot_bytes = 0;
     bool maybe_rebuild = true;
-    int32_t *d_err = nullptr;
+    int32_t *d_err = nullptr;                // device view of h_err
+    volatile int32_t *h_err = nullptr;       // the step's error word: page-locked host memory mapped into the device, so
+                                             // that mdr_phys_sync reads it without a blocking 4-byte copy every step
     ProbeDev d_probe;   // device buffers of the probe
     int probe_pairs_cap = 0;
     JointDev *d_joints = nullptr;       // mdr_phys_set_joints
@@ -262,7 +264,18 @@ static int32_t createImpl(const mdr_phys_config *cfg, const mdr_object *objs, in
     sp.sat_hint = p->dalloc<uint8_t>((size_t)W * ((sp.max_pairs + 3) / 4 * 4));
     sp.world_pairs = p->dalloc<int32_t>(W);
     sp.world_contacts = p->dalloc<int32_t>(W);
-    p->d_err = p->dalloc<int32_t>(1);
+    {
+        void *h = nullptr, *d = nullptr;
+        if (cudaHostAlloc(&h, 64, cudaHostAllocMapped) != cudaSuccess || cudaHostGetDevicePointer(&d, h, 0) != cudaSuccess) {
+            cudaGetLastError();
+            if (h) cudaFreeHost(h);
+            p->alloc_failed = true;
+        } else {
+            memset(h, 0, 64);
+            p->h_err = (volatile int32_t *)h;
+            p->d_err = (int32_t *)d;
+        }
+    }
     sp.error_flags = p->d_err;
     sp.work = p->dalloc<uint32_t>(2 * kMaxLanes);
     sp.group_done = p->dalloc<uint32_t>(W);
@@ -407,6 +420,7 @@ void mdr_phys_destroy(mdr_phys *p)
     if (p->ev0) cudaEventDestroy(p->ev0);
     if (p->ev1) cudaEventDestroy(p->ev1);
     for (void *a : p->allocs) cudaFree(a);
+    if (p->h_err) cudaFreeHost((void *)p->h_err);
     delete p;
 }
 
@@ -866,8 +880,8 @@ int32_t mdr_phys_sync(mdr_phys *p)
         p->io_trace_ranges = 0;
     }
     int32_t err = 0;
-    REQ_CUDA(cudaMemcpy(&err, p->d_err, 4, cudaMemcpyDeviceToHost));
-    if (err) REQ_CUDA(cudaMemset(p->d_err, 0, 4));
+    err = p->h_err ? *p->h_err : 0;          // the stream is idle: every atomicOr of the step has landed
+    if (err) *p->h_err = 0;
     if (err & MDR_ERR_STALL) return MDR_ESTATE;            // a batch task gave up waiting for its world's previous step
     if (err & MDR_ERR_BAD_OBJECT) return MDR_EINVAL;       // an ObjectID outside the object table reached the step
     if (err & MDR_ERR_PAIR_OVERFLOW) return MDR_EOVERFLOW;
