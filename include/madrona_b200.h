@@ -183,7 +183,12 @@ int32_t mdr_phys_sync(mdr_phys *p);
  * call: the worlds are cut into `chunks` ranges and the copy-in of range k+1 and
  * the copy-out of range k-1 overlap the step of range k. Host buffers are whole
  * columns in the raw layout (num_worlds x row_stride elements), page-locked
- * (mdr_host_alloc) for the copies to overlap. Enqueues only; mdr_phys_sync waits. */
+ * (mdr_host_alloc) for the copies to overlap. Enqueues only; mdr_phys_sync waits.
+ * A range is a whole number of resident waves of worlds (chunks is clamped to
+ * the number of waves; one range per wave exposes the least copy-out). The
+ * ranges' launches rotate over MDR_PHYS_IO_LANES streams (default 3, at most 4),
+ * so that the next range's blocks fill the SMs a finishing launch frees.
+ * MDR_PHYS_IO_TRACE=1 prints the device timeline of every call at the next sync. */
 int32_t mdr_phys_step_io_async(mdr_phys *p, int32_t num_in, const int32_t *in_cols, const void *const *in_host,
                                int32_t num_out, const int32_t *out_cols, void *const *out_host, int32_t chunks);
 void *mdr_phys_stream(mdr_phys *p);           /* cudaStream_t */
