@@ -91,6 +91,12 @@ inline bool buildHalfEdgeMesh(HostAssets &out, ObjDev &o, const float *verts, in
         face++;
     }
     o.num_faces = (int32_t)face;
+    o.face_pairs = (face % 2u) == 0u && face > 0u;
+    for (uint32_t f = 0; f + 1 < face && o.face_pairs; f += 2) {
+        const float *a = &out.planes[4 * ((size_t)o.face_off + f)], *b = a + 4;
+        // numerically opposite (a zero may have either sign: it cannot change a comparison downstream)
+        if (!(a[0] == -b[0] && a[1] == -b[1] && a[2] == -b[2])) o.face_pairs = 0;
+    }
     o.num_hedges = (int32_t)hedges.size();
     o.num_edges = (int32_t)out.edges.size() - o.edge_off;
     if (2 * o.num_edges != o.num_hedges) { out.error = "open mesh: an edge has no twin"; return false; }

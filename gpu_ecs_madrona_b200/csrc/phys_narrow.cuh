@@ -405,9 +405,22 @@ MDR_HD bool hullPlaneContact(Manifold &m, const BodyXf &x, const StepParams &p, 
     const int nf = MDR_LDG(&o->num_faces);
     float best = FLT_MAX;
     int inc_face = -1;
-    for (int f = 0; f < nf; f++) {
-        float d = dot(worldNormal(x, src_p, f), plane.n);
-        if (d < best) { best = d; inc_face = f; }
+    if (MDR_LDG(&o->face_pairs)) {
+        // Faces 2k, 2k + 1 with opposite local normals (phys_assets.hpp): every step of worldNormal and of the dot
+        // product -- products, sums, the square root of a sum of squares, the division -- commutes with negation
+        // under round-to-nearest, so the second face's value is the first one's negated, bit for bit (up to the sign
+        // of a zero, which no comparison sees). Same scan order, half the transforms.
+        for (int f = 0; f < nf; f += 2) {
+            const float d = dot(worldNormal(x, src_p, f), plane.n);
+            if (d < best) { best = d; inc_face = f; }
+            const float d2 = -d;
+            if (d2 < best) { best = d2; inc_face = f + 1; }
+        }
+    } else {
+        for (int f = 0; f < nf; f++) {
+            float d = dot(worldNormal(x, src_p, f), plane.n);
+            if (d < best) { best = d; inc_face = f; }
+        }
     }
     if (inc_face < 0) return false;
     // Up to four points stay in registers (every quad face); a fifth sends the

@@ -304,8 +304,12 @@ MDR_HD V3 relVelAt(V3 v1, V3 o1, V3 r1w, V3 v2, V3 o2, V3 r2w)
 }
 
 // solveVelocitiesForContact, physics.cpp:865-993 (+ :752-863).
+// The world arm of a point, rotate(q, r), is the same in all three sweeps (the velocity solve does not move poses).
+// When the other side is a stable static, that side's slot in the contact (its world point, last read by the
+// positional solve; the narrowphase rewrites the contact next substep) is free: the first sweep leaves the arm
+// there and the other two read it back -- the same value, 3 loads instead of 30 instructions.
 template <bool kS1, bool kS2>
-MDR_HD void solveContactVelocitiesT(WorldView &v, const StepParams &p, const SolverContact *ct)
+MDR_HD void solveContactVelocitiesT(WorldView &v, const StepParams &p, SolverContact *ct)
 {
     const float h = p.h;
     const uint32_t hdr = ct->hdr;
@@ -327,8 +331,16 @@ MDR_HD void solveContactVelocitiesT(WorldView &v, const StepParams &p, const Sol
         for (int i = 0; i < npts; i++) {
             const V3 r1 = ldArm(ct->r1, i), r2 = ldArm(ct->r2, i);
             V3 r1w = zero, r2w = zero;
-            if (!s1) r1w = rotate(q1, r1);
-            if (!s2) r2w = rotate(q2, r2);
+            if (!s1 && s2) {
+                if (pass == 0) { r1w = rotate(q1, r1); ct->r2[i][0] = r1w.x; ct->r2[i][1] = r1w.y; ct->r2[i][2] = r1w.z; }
+                else r1w = r2;
+            } else if (!s2 && s1) {
+                if (pass == 0) { r2w = rotate(q2, r2); ct->r1[i][0] = r2w.x; ct->r1[i][1] = r2w.y; ct->r1[i][2] = r2w.z; }
+                else r2w = r1;
+            } else {
+                if (!s1) r1w = rotate(q1, r1);
+                if (!s2) r2w = rotate(q2, r2);
+            }
             V3 vr = relVelAt<kS1, kS2>(v1, o1, r1w, v2, o2, r2w);
             float vn = dot(nrm, vr);
             V3 dir, ta1 = zero, ta2 = zero;
@@ -364,7 +376,7 @@ MDR_HD void solveContactVelocitiesT(WorldView &v, const StepParams &p, const Sol
     if (!s2) stVel(v.vel, b, v2, o2);
 }
 
-MDR_HD void solveContactVelocities(WorldView &v, const StepParams &p, const SolverContact *ct)
+MDR_HD void solveContactVelocities(WorldView &v, const StepParams &p, SolverContact *ct)
 {
     const uint32_t hdr = ct->hdr;
     if ((hdr >> 24) & 1) solveContactVelocitiesT<true, false>(v, p, ct);

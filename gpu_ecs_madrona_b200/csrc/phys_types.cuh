@@ -24,6 +24,8 @@ struct ObjDev {
     int32_t face_off, num_faces;     // planes[] and polys[] share the face index
     int32_t hedge_off, num_hedges;
     int32_t edge_off, num_edges;
+    int32_t face_pairs;      // 1: faces 2k and 2k + 1 have exactly opposite local normals (boxes, prisms): the world
+                             // normal of one is the negation of the other's, bit for bit (see hullPlaneContact)
 };
 
 struct HEdgeDev { uint32_t next, twin, root, poly; };
