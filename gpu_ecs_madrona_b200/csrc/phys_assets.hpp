@@ -121,6 +121,7 @@ inline bool buildAssets(HostAssets &out, const mdr_object *objs, int num_objs,
         o.type = s.type;
         for (int k = 0; k < 3; k++) {
             o.inv_inertia[k] = s.inv_inertia[k];
+            o.inertia[k] = s.inv_inertia[k] == 0 ? 0.0f : 1.0f / s.inv_inertia[k];
             o.aabb[k] = s.aabb_min[k];
             o.aabb[3 + k] = s.aabb_max[k];
         }

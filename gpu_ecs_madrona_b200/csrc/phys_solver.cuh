@@ -64,9 +64,8 @@ MDR_HD void substepBodies(const BlockCtx &c, WorldView &v, const StepParams &p, 
         if (MDR_LDG(p.t.resp + r0 + i) == 0u) vl = vl + h * g;
         vl = vl + (h * inv_m) * ext_f;
         x = x + h * vl;
-        V3 I = mk3(inv_I.x == 0 ? 0.0f : 1.0f / inv_I.x,
-                   inv_I.y == 0 ? 0.0f : 1.0f / inv_I.y,
-                   inv_I.z == 0 ? 0.0f : 1.0f / inv_I.z);
+        // inv_I == 0 ? 0 : 1 / inv_I per axis (physics.cpp:134-138), divided once per object on the host (ObjDev)
+        V3 I = mk3(MDR_LDG(&o->inertia[0]), MDR_LDG(&o->inertia[1]), MDR_LDG(&o->inertia[2]));
         Q4 to_local = qinv(q);
         V3 tau_local = rotate(to_local, ext_t);
         V3 omega_local = rotate(to_local, omega);
@@ -329,6 +328,14 @@ MDR_HD void solveContactVelocitiesT(WorldView &v, const StepParams &p, SolverCon
     // restitution: two sweeps over the points, then dynamic friction: one sweep
     for (int pass = 0; pass < 3; pass++) {
         for (int i = 0; i < npts; i++) {
+            // dynamic friction of a point that took no normal impulse: the magnitude is zero and the reference leaves
+            // the point alone after computing a tangential velocity it then does not use (physics.cpp:775-787);
+            // here the test comes first (a NaN magnitude is != 0 on both sides and goes on)
+            float fric = 0.f;
+            if (pass == 2) {
+                fric = mu_d * fabsf(ct->lambda[i]) / h;
+                if (fric == 0.f) continue;
+            }
             const V3 r1 = ldArm(ct->r1, i), r2 = ldArm(ct->r2, i);
             V3 r1w = zero, r2w = zero;
             if (!s1 && s2) {
@@ -354,7 +361,6 @@ MDR_HD void solveContactVelocitiesT(WorldView &v, const StepParams &p, SolverCon
                 if (!s1) ta1 = cross(r1, n1);
                 if (!s2) ta2 = cross(r2, n2);
             } else {
-                float fric = mu_d * fabsf(ct->lambda[i]) / h;
                 V3 vt = vr - nrm * vn;
                 float vt_len = len(vt);
                 if (!(vt_len != 0 && fric != 0.f)) continue;

@@ -24,6 +24,9 @@ struct ObjDev {
     int32_t face_off, num_faces;     // planes[] and polys[] share the face index
     int32_t hedge_off, num_hedges;
     int32_t edge_off, num_edges;
+    float inertia[3];        // 1 / inv_inertia (0 where that is 0): substepRigidBodies divides per body and substep
+                             // (physics.cpp:134-138); the quotient is a property of the object, IEEE division on the
+                             // host gives the same bits
     int32_t face_pairs;      // 1: faces 2k and 2k + 1 have exactly opposite local normals (boxes, prisms): the world
                              // normal of one is the negation of the other's, bit for bit (see hullPlaneContact)
 };
