@@ -98,8 +98,7 @@ def run_record(name, worlds=0, steps=100, warmup=10, no_cpu=False):
     bufs = [ex.pinned_export_buffer(s) for s in range(slots)]     # page-locked, allocated once
     t0 = time.perf_counter()
     for _ in range(steps):
-        ex.run(1)
-        d2h = sum(ex.export_into(s, bufs[s]) for s in range(slots))
+        d2h = sum(ex.step_read(list(range(slots)), bufs))       # one step + every exported column in host memory
     e2e_s = time.perf_counter() - t0
     line = {"metric": f"world-steps/sec ({A.APP_NAMES[app]}, device-timed)", "value": W * n / (ms * n * 1e-3),
             "unit": "world-steps/s", "n_gpus": 1, "steps": n, "warmup": warmup, "ms_per_step": ms,

@@ -387,6 +387,8 @@ struct mdr_ecs {
     bool all_resident = false;      // every world fits the fused kernel's resident grid (and MDR_ECS_NO_FUSED is not set)
     bool batch_ok = true;           // n > 1 steps of one call run inside one launch (MDR_ECS_NO_BATCH=1: n graph launches)
     int last_call_launches = 0;     // kernels launched by the last mdr_ecs_step_async call
+    volatile int32_t *h_error = nullptr;   // host view of EcsDev::error (mapped page-locked memory)
+    int64_t *h_totals = nullptr;    // page-locked: row totals of the staged exports, read back by mdr_ecs_step_read
     unsigned *grid_bar = nullptr;
     bool fused_ok = false, fused_in_graph = false;
     mdr_ecs_launch_fn launcher = nullptr;   // megakernel instantiated in the user's translation unit
@@ -476,10 +478,10 @@ void runScript(mdr_ecs *e, const mdr_script_op *d_ops, const int32_t *d_offsets,
 
 int32_t checkError(mdr_ecs *e)
 {
-    int32_t err = 0;
-    REQ_CUDA(cudaMemcpy(&err, e->host.error, 4, cudaMemcpyDeviceToHost));
+    REQ_CUDA(cudaStreamSynchronize(e->stream));      // callers have waited already: returns at once
+    const int32_t err = e->h_error ? *e->h_error : 0;
     if (err) {
-        REQ_CUDA(cudaMemset(e->host.error, 0, 4));
+        *e->h_error = 0;
         return MDR_EOVERFLOW;
     }
     return MDR_OK;
@@ -521,6 +523,8 @@ void mdr_ecs_destroy(mdr_ecs *e)
     if (e->ev0) cudaEventDestroy(e->ev0);
     if (e->ev1) cudaEventDestroy(e->ev1);
     for (void *a : e->allocs) cudaFree(a);
+    if (e->h_totals) cudaFreeHost(e->h_totals);
+    if (e->h_error) cudaFreeHost((void *)e->h_error);
     delete e;
 }
 
@@ -714,6 +718,7 @@ int32_t mdr_ecs_build(mdr_ecs *e)
             fprintf(stderr, "madrona_b200: %d worlds of this registry do not fit the device memory\n", e->cfg.num_worlds);
         for (void *a : e->allocs) cudaFree(a);
         e->allocs.clear();
+        if (e->h_error) { cudaFreeHost((void *)e->h_error); e->h_error = nullptr; }
         e->alloc_failed = false;
         e->built = false;
         e->dev = nullptr;
@@ -759,7 +764,19 @@ static int32_t buildImpl(mdr_ecs *e)
                                         : (int32_t)((total_rows + 63) / 64 * 64 + 64 * (4 + (num_singletons ? 1 : 0)));
     H.id_nodes = e->dalloc<IdNode>((size_t)W * H.id_cap);
     H.id_state = e->dalloc<IdState>(W);
-    H.error = e->dalloc<int32_t>(1);
+    {   // the error word lives in page-locked host memory mapped into the device: checkError reads it after a
+        // stream wait without a blocking 4-byte copy per step
+        void *h = nullptr, *d = nullptr;
+        if (cudaHostAlloc(&h, 64, cudaHostAllocMapped) != cudaSuccess || cudaHostGetDevicePointer(&d, h, 0) != cudaSuccess) {
+            cudaGetLastError();
+            if (h) cudaFreeHost(h);
+            e->alloc_failed = true;
+        } else {
+            memset(h, 0, 64);
+            e->h_error = (volatile int32_t *)h;
+        }
+        H.error = (int32_t *)d;
+    }
     H.tmp_bytes = e->tmp_bytes;
     if (H.tmp_bytes > 0) {
         H.tmp_arena = e->dalloc<char>((size_t)W * H.tmp_bytes, false);
@@ -1274,6 +1291,52 @@ int64_t mdr_ecs_read_exported(mdr_ecs *e, int32_t slot, void *host, int64_t max_
     REQ_CUDA(cudaStreamSynchronize(e->stream));
     if (bytes) REQ_CUDA(cudaMemcpy(host, e->host.exports[slot].buffer, (size_t)bytes, cudaMemcpyDeviceToHost));
     return bytes;
+}
+
+// One step and its exported columns in host memory with two host synchronisations instead of one per call and
+// column (mdr_ecs_step + mdr_ecs_export_rows + mdr_ecs_read_exported per slot: six blocking round trips for two
+// slots, ~100 us -- more than a 1024-world step takes on the device). The step, the row totals of the staged
+// exports (8 bytes each, to page-locked memory) and the fixed-size columns are enqueued together; after the first
+// wait the staged columns are copied at their now known sizes.
+int32_t mdr_ecs_step_read(mdr_ecs *e, int32_t num_slots, const int32_t *slots, void *const *host,
+                          const int64_t *max_bytes, int64_t *out_bytes)
+{
+    if (!e || num_slots < 0 || num_slots > kMaxExports || (num_slots && (!slots || !host || !max_bytes || !out_bytes)))
+        return MDR_EINVAL;
+    if (!e->built) return MDR_ESTATE;
+    for (int k = 0; k < num_slots; k++)
+        if (slots[k] < 0 || slots[k] >= e->host.num_exports || !host[k]) return MDR_EINVAL;
+    REQ_CUDA(cudaSetDevice(e->cfg.gpu_id));
+    if (!e->h_totals) REQ_CUDA(cudaHostAlloc((void **)&e->h_totals, sizeof(int64_t) * kMaxExports, cudaHostAllocDefault));
+    int32_t rc = mdr_ecs_step_async(e, 1);
+    if (rc != MDR_OK) return rc;
+    const int W = e->host.num_worlds;
+    bool staged = false;
+    for (int k = 0; k < num_slots; k++) {
+        const ExportDev &X = e->host.exports[slots[k]];
+        if (X.fixed) {
+            out_bytes[k] = (int64_t)W * e->host.arch[X.arch].stride * X.bytes;
+            if (out_bytes[k] > max_bytes[k]) rc = MDR_ECAPACITY;
+            else if (out_bytes[k]) REQ_CUDA(cudaMemcpyAsync(host[k], X.buffer, (size_t)out_bytes[k], cudaMemcpyDeviceToHost, e->stream));
+        } else {
+            staged = true;
+            REQ_CUDA(cudaMemcpyAsync(e->h_totals + k, X.offsets + W, 8, cudaMemcpyDeviceToHost, e->stream));
+        }
+    }
+    REQ_CUDA(cudaStreamSynchronize(e->stream));
+    if (staged) {
+        for (int k = 0; k < num_slots; k++) {
+            const ExportDev &X = e->host.exports[slots[k]];
+            if (X.fixed) continue;
+            out_bytes[k] = e->h_totals[k] * X.bytes;
+            if (out_bytes[k] > max_bytes[k]) rc = MDR_ECAPACITY;
+            else if (out_bytes[k]) REQ_CUDA(cudaMemcpyAsync(host[k], X.buffer, (size_t)out_bytes[k], cudaMemcpyDeviceToHost, e->stream));
+        }
+        REQ_CUDA(cudaStreamSynchronize(e->stream));
+    }
+    closeTiming(e);
+    const int32_t err = checkError(e);
+    return rc != MDR_OK ? rc : err;
 }
 
 int32_t mdr_ecs_export_bytes_per_row(mdr_ecs *e, int32_t slot)

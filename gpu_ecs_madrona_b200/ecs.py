@@ -300,6 +300,19 @@ class EcsRegistry:
         _check(n, "read_exported")
         return int(n)
 
+    def step_read(self, slots, hosts):
+        """One step, then exported columns `slots` into the (pinned) host arrays `hosts`, in one call with two host
+        synchronisations (mdr_ecs_step_read); returns the bytes copied per slot."""
+        n = len(slots)
+        lib = self.lib
+        lib.mdr_ecs_step_read.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        sl = (C.c_int32 * n)(*slots)
+        ptrs = (C.c_void_p * n)(*[h.ctypes.data for h in hosts])
+        mx = (C.c_int64 * n)(*[h.nbytes for h in hosts])
+        out = (C.c_int64 * n)()
+        _check(lib.mdr_ecs_step_read(self.h, n, sl, ptrs, mx, out), "step_read")
+        return [int(v) for v in out]
+
     def export(self, slot):
         """Host copy of an exported column (u8)."""
         ptr, rows, nb = self.get_exported(slot)

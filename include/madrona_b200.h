@@ -416,6 +416,11 @@ int64_t mdr_ecs_export_rows(mdr_ecs *e, int32_t slot);
 int32_t mdr_ecs_export_bytes_per_row(mdr_ecs *e, int32_t slot);
 /* Host copy of an exported column; returns the bytes copied. */
 int64_t mdr_ecs_read_exported(mdr_ecs *e, int32_t slot, void *host, int64_t max_bytes);
+/* run() + the exported columns `slots` in host memory (page-locked for full speed) as one call: the trainer's loop
+ * around MWCudaExecutor::run() + Tensor reads (src/mw/cuda_exec.cpp:1777-1794). out_bytes[k] = bytes written to
+ * host[k] (rows x bytes per row); MDR_ECAPACITY if a buffer is too small (that column is not copied). Blocking. */
+int32_t mdr_ecs_step_read(mdr_ecs *e, int32_t num_slots, const int32_t *slots, void *const *host,
+                          const int64_t *max_bytes, int64_t *out_bytes);
 /* registerTypes + setupTasks + world constructors of a built-in world
  * (MDR_APP_* of madrona_b200_apps.h). */
 int32_t mdr_app_setup(mdr_ecs *e, int32_t app, const int32_t *params, int32_t nparams);

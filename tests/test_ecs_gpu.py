@@ -352,3 +352,22 @@ def test_batched_steps_equal_single_steps(monkeypatch, app, worlds, params, no_f
         U.assert_same(gpu_snapshot(batch, app), gpu_snapshot(single, app), app, f"after run({steps}) ")
     batch.close()
     single.close()
+
+
+@pytest.mark.parametrize("app,worlds", [(A.APP_TASKGRAPH, 50), (A.APP_FVS, 40)])
+def test_step_read_equals_step_plus_exports(app, worlds):
+    """mdr_ecs_step_read (one step and the exported columns in host memory, two synchronisations) against
+    run(1) + export(slot): the same bytes, step after step."""
+    from gpu_ecs_madrona_b200.ecs import EcsExecutor
+    a, b = EcsExecutor(app, worlds), EcsExecutor(app, worlds)
+    n = U.NUM_EXPORTS[app]
+    bufs = [a.pinned_export_buffer(s) for s in range(n)]
+    for step in range(12):
+        got = a.step_read(list(range(n)), bufs)
+        b.run(1)
+        for s in range(n):
+            want = b.export(s)
+            assert got[s] == len(want), (step, s)
+            assert np.array_equal(bufs[s].reshape(-1).view(np.uint8)[:got[s]], want), (step, s)
+    a.close()
+    b.close()
