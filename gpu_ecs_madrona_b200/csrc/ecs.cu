@@ -276,7 +276,7 @@ __device__ __forceinline__ void gridBarrier(unsigned *bar /*[2]: arrivals, gener
 
 template <int kMinBlocks>
 __global__ void __launch_bounds__(32 * kWarpsPerBlock, kMinBlocks)
-ecsFusedStepKernel(const EcsDev *__restrict__ E, int first, int last, unsigned *bar, int steps)
+ecsFusedStepKernel(const EcsDev *__restrict__ E, int first, int last, unsigned *bar, int steps, int align)
 {
     __shared__ WarpShared shared[kWarpsPerBlock];
     __shared__ BlockDescriptors descriptors;
@@ -302,9 +302,10 @@ ecsFusedStepKernel(const EcsDev *__restrict__ E, int first, int last, unsigned *
         // 2. TaskGraph::run, `steps` times (a batch: the staged exports are observable only at its end, so
         //    copy-in happens once before and offsets + copy-out once after; nothing else crosses worlds)
         loadWorld(ctx, E, &shared[warp], w);
+        const bool aligned = align && (W % kWarpsPerBlock) == 0;       // no idle warp in any block
         for (int k = 0; k < steps; k++) {
             if (k) beginStep(ctx);
-            runNodes(ctx, nodes, last - first, AppsBuiltin());
+            runNodes(ctx, nodes, last - first, AppsBuiltin(), aligned);
         }
         storeWorld(ctx);
     }
@@ -383,7 +384,9 @@ struct mdr_ecs {
     bool exports_dirty = true;
     int blocks = 0;
     void (*step_kernel)(const EcsDev *, int, int, int) = nullptr;
-    void (*fused_kernel)(const EcsDev *, int, int, unsigned *, int) = nullptr;   // the whole step in one launch, when it applies
+    void (*fused_kernel)(const EcsDev *, int, int, unsigned *, int, int) = nullptr;
+    int align_nodes = -1;           // the warps of a block enter each node together (fused kernel): -1 = by policy,
+                                    // MDR_ECS_ALIGN_NODES=0 / 1 force it   // the whole step in one launch, when it applies
     bool all_resident = false;      // every world fits the fused kernel's resident grid (and MDR_ECS_NO_FUSED is not set)
     bool batch_ok = true;           // n > 1 steps of one call run inside one launch (MDR_ECS_NO_BATCH=1: n graph launches)
     int last_call_launches = 0;     // kernels launched by the last mdr_ecs_step_async call
@@ -919,6 +922,8 @@ static int32_t buildImpl(mdr_ecs *e)
     const char *nf = getenv("MDR_ECS_NO_FUSED"), *ff = getenv("MDR_ECS_FUSED");
     e->all_resident = need <= (long long)fused_per_sm * prop.multiProcessorCount && !(nf && *nf == '1');
     e->fused_ok = !(nf && *nf == '1') && (W >= 2048 || (ff && *ff == '1')) && e->all_resident;
+    const char *an = getenv("MDR_ECS_ALIGN_NODES");
+    e->align_nodes = an && *an ? (*an == '1') : -1;
     const char *nb = getenv("MDR_ECS_NO_BATCH");
     e->batch_ok = !(nb && *nb == '1');
     e->built = true;
@@ -1084,7 +1089,12 @@ int32_t mdr_ecs_step_async(mdr_ecs *e, int32_t num_steps)
         if (!extend) REQ_CUDA(cudaEventRecord(e->ev0, e->stream));
         const int W = e->host.num_worlds, N = e->host.num_nodes;
         if (staged && e->all_resident) {
-            e->fused_kernel<<<(W + kWarpsPerBlock - 1) / kWarpsPerBlock, 32 * kWarpsPerBlock, 0, e->stream>>>(e->dev, 0, N, e->grid_bar, num_steps);
+            // Measured (profiles/r02_summary.md section 11): with 64 warps per SM each at its own node, a long graph stalls on
+            // instruction fetch (fantasy_vs, 13 nodes: `no_instruction` 13.5 cycles per issue); a block barrier per node
+            // keeps the 8 warps of a block on the same code: +12 % for fantasy_vs batches, a loss for short graphs
+            // (barriers with nothing to gain) and for single steps.
+            const int align = e->align_nodes >= 0 ? e->align_nodes : (N >= 8);
+            e->fused_kernel<<<(W + kWarpsPerBlock - 1) / kWarpsPerBlock, 32 * kWarpsPerBlock, 0, e->stream>>>(e->dev, 0, N, e->grid_bar, num_steps, align);
         } else {
             if (staged) ecsExportCopy<<<(W + 7) / 8, 256, 0, e->stream>>>(e->dev, 0);
             e->step_kernel<<<e->blocks, 32 * kWarpsPerBlock, 0, e->stream>>>(e->dev, 0, N, num_steps);
@@ -1111,7 +1121,7 @@ int32_t mdr_ecs_step_async(mdr_ecs *e, int32_t num_steps)
         e->fused_in_graph = fused;
         if (fused) {
             const int blocks = (e->host.num_worlds + kWarpsPerBlock - 1) / kWarpsPerBlock;
-            e->fused_kernel<<<blocks, 32 * kWarpsPerBlock, 0, e->stream>>>(e->dev, 0, e->host.num_nodes, e->grid_bar, 1);
+            e->fused_kernel<<<blocks, 32 * kWarpsPerBlock, 0, e->stream>>>(e->dev, 0, e->host.num_nodes, e->grid_bar, 1, e->align_nodes > 0);
         }
         if (staged && !fused) ecsExportCopy<<<(e->host.num_worlds + 7) / 8, 256, 0, e->stream>>>(e->dev, 0);
         // The megakernel walks maximal runs of in-kernel nodes; a physics node is a launch of the

@@ -891,13 +891,18 @@ __device__ __forceinline__ const NodeDev *loadDescriptors(BlockDescriptors *bd, 
 __device__ unsigned long long g_node_clocks[kMaxNodes + 2];     // profiling builds: clock64 per node, summed over warps
 #endif
 
+// block_aligned: every warp of the block walks a world (none idles) and the caller wants the block's warps to enter
+// each node together: the 8 warps then fetch the same instructions at the same time instead of 8 different nodes'
+// worth (with 64 warps per SM at 64 different places the step stalls on instruction fetch: ncu `no_instruction`).
 template <typename Builtin>
-__device__ __forceinline__ void runNodes(Context &ctx, const NodeDev *nodes, int count, Builtin builtin)
+__device__ __forceinline__ void runNodes(Context &ctx, const NodeDev *nodes, int count, Builtin builtin,
+                                         bool block_aligned = false)
 {
 #ifdef MDR_ECS_NODE_CLOCKS
     long long t_last = clock64();
 #endif
     for (int ni = 0; ni < count; ni++) {
+        if (block_aligned) __syncthreads();
 #ifdef MDR_ECS_NODE_CLOCKS
         if (ni > 0 && laneId() == 0) { const long long now = clock64(); atomicAdd(&g_node_clocks[ni - 1], (unsigned long long)(now - t_last)); t_last = now; }
 #endif
