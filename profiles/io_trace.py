@@ -1,12 +1,11 @@
 #!/usr/bin/env python
-"""Device timeline of one end-to-end step (mdr_phys_step_io_async): MDR_PHYS_IO_TRACE=1 MDR_PHYS_IO_NO_GRAPH=1
-python profiles/io_trace.py [--chunks 6] [--no-in] [--no-out]"""
+"""Device timeline of one end-to-end step (mdr_phys_step_io_async) through MDR_PHYS_IO_TRACE=1: per world range, when
+its copy-in landed, its kernel ended and its copy-out ended.  python profiles/io_trace.py [--chunks 6] [--no-in] [--no-out]"""
 import argparse
 import os
 import sys
 
 os.environ.setdefault("MDR_PHYS_IO_TRACE", "1")
-os.environ.setdefault("MDR_PHYS_IO_NO_GRAPH", "1")
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from gpu_ecs_madrona_b200 import phys, scenes  # noqa: E402
 
