@@ -8,7 +8,7 @@
 #ifdef MDR_EXP_FIXED
 #define MDR_STEP_VARIANT(T, B) { T, B, mdr::physStepKernel<T, B, false>, mdr::physStepKernel<T, B, false>, \
                                  mdr::physStepKernel<T, B, false>, mdr::physStepKernel<T, B, false, 1, mdr::Collisions64Layout>, \
-                                 68, 640, 72, 64 }
+                                 68, 640, 71, 64 }
 #else
 #define MDR_STEP_VARIANT(T, B) { T, B, mdr::physStepKernel<T, B, false>, mdr::physStepKernel<T, B, false>, \
                                  mdr::physStepKernel<T, B, false>, nullptr, 0, 0, 0, 0 }
