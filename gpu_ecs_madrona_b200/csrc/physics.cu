@@ -363,8 +363,13 @@ static int32_t createImpl(const mdr_phys_config *cfg, const mdr_object *objs, in
             cudaFuncAttributes fa;
             REQ_CUDA(cudaFuncGetAttributes(&fa, k));
             const long long need = (long long)per_sm * ((long long)p->smem_bytes + (long long)fa.sharedSizeBytes + reserved);
-            int hint = max_sm > 0 ? (int)(need * 100 / max_sm) : 100;
-            if (hint > 100) hint = 100;
+            // the carve-outs of compute capability 9.0 / 10.0; the smallest one that holds the resident blocks, asked for
+            // as the percentage just below it (never one that the round-up could land under the need)
+            static const int kCarveKB[] = { 0, 8, 16, 32, 64, 100, 132, 164, 196, 228 };
+            long long pick = max_sm;
+            for (int kb : kCarveKB) if ((long long)kb * 1024 >= need && (long long)kb * 1024 <= max_sm) { pick = (long long)kb * 1024; break; }
+            int hint = max_sm > 0 ? (int)(pick * 100 / max_sm) : 100;
+            if (hint > 100 || pick >= max_sm) hint = 100;
             hint = envInt("MDR_CARVEOUT", hint);
             REQ_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributePreferredSharedMemoryCarveout, hint));
         }
